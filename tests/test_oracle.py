@@ -1,0 +1,139 @@
+"""CPU tests: the oracle restatement (oracle/loner_oracle.py) against golden vectors produced by the
+reference's own, unmodified Python (oracle/make_golden.py).  No GPU, no /root/reference needed."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, golden_params
+from oracle import loner_oracle as O
+
+OGM_CASES = ["c1_ogm_l1js", "s128_ogm_l2js"]
+ALL_CASES = OGM_CASES + ["c1_uniform_l2los"]
+
+
+def ulp_diff(a, b):
+    ai = a.contiguous().view(torch.int32).long()
+    bi = b.contiguous().view(torch.int32).long()
+    return (ai - bi).abs()
+
+
+def test_grid_sample_restatement():
+    torch.manual_seed(3)
+    occ = torch.randn(1, 1, 20, 20, 20) * 0.01
+    pts = torch.rand(500, 9, 3) * 2.2 - 1.1
+    assert torch.equal(O.occ_interpolate_explicit(occ, pts), O.occ_interpolate(occ, pts))
+
+
+@pytest.mark.parametrize("name", OGM_CASES)
+def test_sampler_against_reference(name):
+    g = load_golden(name)
+    s = O.sample_occ(g["rays"], g["occ"], g["u1"], g["u2"], g["n_samples"], 1.0)
+    # occupancy logits: identical op sequence -> bit-exact
+    assert torch.equal(s["logits"], g["occ_logits"])
+    # bits: the oracle's exp is correctly rounded, torch-CPU's is 1-ulp Sleef; a flip needs a logit in (2^-24, 2^-23)
+    flips = (s["occ_bits"] != g["occ_bits"])
+    assert flips.sum().item() == 0 or (g["occ_logits"][flips].abs() < 2.0 ** -22).all()
+    assert ulp_diff(s["probs"], g["occ_probs"]).max().item() <= 4 or torch.allclose(s["probs"], g["occ_probs"], atol=3e-7)
+    # searchsorted indices: equal except where u sits within a few ulp of a cdf knot (sum order differs, see oracle header)
+    mism = (s["inds"] != g["inds"])
+    assert mism.float().mean().item() < 1e-3
+    assert (s["inds"] - g["inds"]).abs().max().item() <= 1
+    # a fine sample inside a near-empty bin divides by denom ~1e-5: ulp-level cdf differences are
+    # amplified there, so compare the bulk tightly and bound the rare ill-conditioned element by a bin width
+    dz = (s["z"] - g["z"]).abs()
+    assert (dz > 1e-6).float().mean().item() < 1e-3
+    assert dz.max().item() < 1e-3
+    assert (s["z"][:, 1:] >= s["z"][:, :-1]).all()
+
+
+def test_uniform_sampler_against_reference():
+    g = load_golden("c1_uniform_l2los")
+    z = O.sample_uniform(g["rays"], g["u1"], g["n_samples"], 1.0)
+    assert torch.equal(z, g["z"])
+
+
+@pytest.mark.parametrize("name", ALL_CASES)
+def test_field_and_composite_against_reference(name):
+    g = load_golden(name)
+    p = golden_params(g)
+    rays, z = g["rays"], g["z"]
+    xyz = rays[:, None, 0:3] + rays[:, None, 3:6] * z[..., None]
+    sigma = O.sigma_field(xyz.reshape(-1, 3), p, g["log2_T"]).view(z.shape)
+    torch.testing.assert_close(sigma, g["sigma"], rtol=1e-5, atol=1e-6)
+    c = O.composite(g["sigma"], z, rays[:, 3:6], rays[:, -1:], g["noise"])
+    for k, gk in (("weights", "weights"), ("depth", "depth"), ("opacity", "opacity"), ("variance", "variance")):
+        torch.testing.assert_close(c[k], g[gk], rtol=1e-6, atol=1e-7)
+    if "adj_depth" in g:
+        a = O.composite_adjusted(g["sigma"], z, rays[:, 3:6])
+        assert torch.equal(a["depth"], g["adj_depth"])
+        torch.testing.assert_close(a["variance"], g["adj_variance"], rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("name", ALL_CASES)
+def test_loss_and_gradients_against_reference(name):
+    g = load_golden(name)
+    p = golden_params(g).requires_grad_(True)
+    rays = g["rays"].clone().requires_grad_(True)
+    cfg = dict(loss_selection=g["loss_selection"], min_js_score=g["min_js"])
+    # feed the reference's own z so that gradients are compared on identical samples
+    z = g["z"]
+    xyz = rays[:, None, 0:3] + rays[:, None, 3:6] * z[..., None]
+    sigma = O.sigma_field(xyz.reshape(-1, 3), p, g["log2_T"]).view(z.shape)
+    c = O.composite(sigma, z, rays[:, 3:6], rays[:, -1:], g["noise"])
+    ls = O.depth_loss(c["weights"], c["depth"], c["opacity"], z, rays[:, -1:], g["depths"], g["scale"], cfg)
+    torch.testing.assert_close(ls["loss"].detach(), g["loss"], rtol=1e-5, atol=1e-6)
+    assert abs(float(ls["eps"].mean()) - g["depth_eps"]) < 1e-5 * max(1.0, g["depth_eps"])
+    ls["loss"].backward()
+    torch.testing.assert_close(p.grad[:3072], g["mlp_grad"], rtol=1e-4, atol=1e-7)
+    tg = p.grad[3072:]
+    torch.testing.assert_close(tg[g["table_grad_idx"]], g["table_grad_val"], rtol=1e-4, atol=1e-8)
+    assert abs(tg.double().norm().item() - g["table_grad_norm"]) < 1e-4 * g["table_grad_norm"]
+    assert int((tg != 0).sum()) == g["table_grad_nnz"]
+    if "rays_grad" in g:
+        torch.testing.assert_close(rays.grad, g["rays_grad"], rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ALL_CASES)
+def test_ray_builder_and_pose_gradient(name):
+    g = load_golden(name)
+    n_l = g["kf_directions"].shape[1]
+    pose = g["kf_pose"].clone().requires_grad_(True)
+    rays, depths = O.build_lidar_rays(g["kf_directions"], g["kf_distances"], pose, g["shift"], g["scale"],
+                                      torch.tensor(g["ray_range"]))
+    n = rays.shape[0]                                   # lidar rays come first; sky rays (detached pose) follow
+    torch.testing.assert_close(rays.detach(), g["rays"][:n], rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(depths, g["depths"][:n], rtol=1e-6, atol=1e-7)
+    if "pose_grad" in g and "rays_grad" in g:
+        rays.backward(g["rays_grad"][:n])
+        torch.testing.assert_close(pose.grad, g["pose_grad"], rtol=1e-3, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", OGM_CASES)
+def test_occ_update_against_reference(name):
+    g = load_golden(name)
+    rays, z = g["rays"], g["z"]
+    xyz = rays[:, None, 0:3] + rays[:, None, 3:6] * z[..., None]
+    occ = O.occ_update(g["occ"], xyz, z * g["scale"], (g["depths"] * g["scale"]).reshape(-1, 1), lr=1e-4)
+    torch.testing.assert_close(occ, g["occ_after"], rtol=1e-6, atol=1e-9)
+    assert (occ != g["occ"]).any()
+
+
+def test_adam_matches_torch():
+    torch.manual_seed(0)
+    p = torch.randn(1000); p0 = p.clone().requires_grad_(True)
+    opt = torch.optim.Adam([p0], lr=0.01)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    for step in range(1, 4):
+        gr = torch.randn(1000)
+        p0.grad = gr.clone(); opt.step()
+        O.adam_step(p, gr, m, v, step, 0.01)
+    torch.testing.assert_close(p, p0.detach(), rtol=1e-6, atol=1e-7)
+
+
+def test_level_table_matches_survey_counts():
+    from oracle import tinycudann as T
+    for log2T, n in ((18, 7413760), (19, 14229504), (22, 105455616)):
+        lv, entries = T.level_table(16, 16, log2T)
+        assert entries * 2 == n
+        assert [l["res"] for l in lv[:3]] == [16, 32, 64]
+        assert lv[0]["dense"] and lv[1]["dense"]
