@@ -1,0 +1,176 @@
+/*
+ * loner_b200.h -- C-ABI of libloner_b200.so: hand-written sm_100a CUDA kernels for LONER's mapping
+ * hot path.  Plain pointers and sizes only; no torch/ATen types cross this boundary.
+ *
+ * The reference (esulimma/LONER) is 100% Python and has no FFI layer of its own; the seam this
+ * library replaces is (a) the Python API of the third-party `tinycudann` extension and (b) the
+ * torch-op bodies of src/models/{ray_sampling,rendering_tcnn,losses}.py and
+ * src/mapping/optimizer.py::compute_loss.  Each entry point cites the reference code it replaces
+ * (paths relative to the reference root).  The Python binding (ctypes) is loner_b200/_lib.py; the
+ * binding a reference maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every device buffer is allocated by the caller (PyTorch) and passed as a raw device pointer;
+ *     the library never frees or retains caller memory.  The plan handle is the only library-owned
+ *     object and owns no device memory.
+ *   - all calls are asynchronous on `stream` (a cudaStream_t passed as void*; NULL = default stream).
+ *   - return 0 on success, negative lb_status on failure; lb_last_error() gives the message of the
+ *     last failure on the calling thread.  There is no CPU fallback and no backend dispatch.
+ *   - layouts are row-major and contiguous: rays [N,13] = [o(3), d(3), viewdir(3), 0, 0, near, far]
+ *     (reference src/common/ray_utils.py:313-315), per-sample arrays [N,S].
+ *   - a plan is immutable and may be shared between threads; calls are not re-entrant on the same
+ *     output buffers.
+ */
+#ifndef LONER_B200_H
+#define LONER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define LB_API __attribute__((visibility("default")))
+#else
+#define LB_API
+#endif
+
+#define LB_VERSION 100
+#define LB_MAX_LEVELS 32
+#define LB_RAY_STRIDE 13
+
+typedef enum {
+    LB_OK = 0,
+    LB_ERR_BAD_ARGUMENT = -1,
+    LB_ERR_UNSUPPORTED = -2,
+    LB_ERR_CUDA = -3,
+} lb_status;
+
+/* Hash-grid + MLP configuration: the keys of the reference's tcnn config dicts
+ * (cfg/nerf_config/default_nerf_hash.yaml:14-31). */
+typedef struct {
+    int32_t n_levels;            /* 16 */
+    int32_t n_features_per_level;/* 2 (only 2 is supported) */
+    int32_t log2_hashmap_size;   /* 18 / 19 / 22 */
+    int32_t base_resolution;     /* 16 */
+    float   per_level_scale;     /* 2.0 (tcnn default when the YAML omits it) */
+    int32_t mlp_width;           /* n_neurons: 64 (only 64 is supported) */
+    int32_t mlp_hidden_layers;   /* 1 for the sigma head */
+} lb_grid_config;
+
+typedef struct lb_plan lb_plan;
+
+/* Loss configuration: cfg/model_config/default_model_config.yaml:39-58 as read by
+ * src/mapping/optimizer.py:711-848. */
+typedef enum { LB_LOSS_L1_JS = 0, LB_LOSS_L2_JS = 1, LB_LOSS_L1_LOS = 2, LB_LOSS_L2_LOS = 3 } lb_loss_kind;
+
+typedef struct {
+    int32_t kind;             /* lb_loss_kind */
+    float   scale_factor;     /* world_cube.scale_factor: metres per cube unit */
+    float   min_js_score;     /* JS_loss.min_js_score */
+    float   max_js_score;     /* JS_loss.max_js_score */
+    float   js_alpha;         /* JS_loss.alpha */
+    float   min_depth_eps;    /* loss.min_depth_eps (eps_min) */
+    float   depth_eps;        /* fixed / decayed eps for the *_LOS kinds (caller applies the decay) */
+    float   los_lambda;       /* loss.los_lambda (caller applies decay_los_lambda) */
+    float   depthloss_lambda; /* loss.depthloss_lambda */
+    float   n_opaque;         /* GLOBAL count of opaque rays (all ranks); <=0: use the local count */
+    float   n_total_samples;  /* GLOBAL N*S for the mean over all samples; <=0: use local N*S */
+} lb_loss_config;
+
+/* ------------------------------------------------------------------------------------------ */
+LB_API int         lb_version(void);
+LB_API const char* lb_last_error(void);
+
+/* Immutable level table (scale, resolution, offset, size, dense|hash) following tiny-cuda-nn's
+ * GridEncoding constructor; replaces tcnn.Encoding/NetworkWithInputEncoding construction
+ * (src/models/nerf_tcnn.py:35-40). */
+LB_API int  lb_plan_create(const lb_grid_config* cfg, lb_plan** out);
+LB_API void lb_plan_destroy(lb_plan* plan);
+/* number of fp32 scalars: MLP matrices (W1[64,32] then W2[16,64], row-major [out,in]) and tables */
+LB_API int  lb_plan_param_counts(const lb_plan* plan, int64_t* n_mlp, int64_t* n_table);
+LB_API int  lb_plan_level(const lb_plan* plan, int level, float* scale, uint32_t* resolution,
+                   uint32_t* offset, uint32_t* size, int32_t* is_dense);
+
+/* ---- R2: sampling ------------------------------------------------------------------------ */
+/* OccGridRaySampler.get_samples (src/models/ray_sampling.py:53-92) incl. OccupancyGridModel.interpolate
+ * (src/models/model_tcnn.py:126-134) and sample_pdf (src/models/rendering_tcnn.py:19-68).
+ * occ [D,D,D] fp32 logits (x -> last dim); t_steps [S/2] = linspace(0,1,S/2); u1,u2 [N,S/2] uniform.
+ * z_out [N,S] sorted.  Optional debug outputs (may be NULL): occ_bits [N,S/2] (prob>0),
+ * inds [N,S/2] int64 searchsorted indices -- both bit-exact w.r.t. oracle/loner_oracle.py. */
+LB_API int lb_sample_occ(const float* rays, const float* occ, int occ_dim, const float* t_steps,
+                  const float* u1, const float* u2, int n_rays, int n_samples, float perturb,
+                  float* z_out, uint8_t* occ_bits, int64_t* inds, void* stream);
+/* UniformRaySampler.get_samples (src/models/ray_sampling.py:22-43). t_steps [S], u [N,S]. */
+LB_API int lb_sample_uniform(const float* rays, const float* t_steps, const float* u, int n_rays,
+                      int n_samples, float perturb, float* z_out, void* stream);
+
+/* ---- R4: sigma field (tcnn NetworkWithInputEncoding / Encoding) -------------------------- */
+/* tcnn.Encoding(HashGrid).forward (src/models/nerf_tcnn.py:40,64): x01 [P,3] in [0,1] -> enc [P,L*2]. */
+LB_API int lb_encode_fwd(const lb_plan* plan, const float* x01, const float* table, int64_t n_points,
+                  float* enc, void* stream);
+/* its backward: d_enc [P,L*2] -> grad_table += scatter; d_x01 [P,3] (NULL to skip) */
+LB_API int lb_encode_bwd(const lb_plan* plan, const float* x01, const float* table, const float* d_enc,
+                  int64_t n_points, float* grad_table, float* d_x01, void* stream);
+
+/* Fused sigma head: tcnn.NetworkWithInputEncoding(3->1) forward (src/models/nerf_tcnn.py:35-38,71-72)
+ * fused with xyz = o + d*z and pos01 = (xyz+1)/2 (src/models/rendering_tcnn.py:390, nerf_tcnn.py:63).
+ * Point source: either (rays,z) with P = n_rays*n_samples, or x01 [P,3] when rays == NULL
+ * (then n_rays = P, n_samples = 1).  params = [mlp | table] flat fp32 (tcnn layout).
+ * sigma [P]; enc_save [P,32] (NULL to skip) keeps the encodings for the backward pass. */
+LB_API int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
+                 const float* params, int n_rays, int n_samples, float* sigma, float* enc_save,
+                 void* stream);
+/* Backward of the above: d_sigma [P] -> grad_params += (MLP grads, table scatter-add);
+ * d_rays [N,13] += (origin/direction gradients through the grid input) when non-NULL
+ * (or d_x01 [P,3] when the point source is x01).  enc_save as written by lb_sigma_fwd. */
+LB_API int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
+                 const float* params, const float* enc_save, const float* d_sigma, int n_rays,
+                 int n_samples, float* grad_params, float* d_rays, float* d_x01, void* stream);
+
+/* ---- R5/R6: compositing ------------------------------------------------------------------ */
+/* raw2outputs, sigma-only (src/models/rendering_tcnn.py:219-295).  noise [N,S] already scaled by
+ * raw_noise_std (NULL: none).  Outputs: weights [N,S], depth/opacity/variance [N] (variance may be NULL).
+ * strategy 0 = 'default' (expected depth incl. far term), 1 = 'adjusted' (median-transmittance depth,
+ * noise ignored; rendering_tcnn.py:70-214 effective semantics). */
+LB_API int lb_composite_fwd(const float* sigma, const float* z, const float* rays, const float* noise,
+                     int n_rays, int n_samples, int strategy, float* weights, float* depth,
+                     float* opacity, float* variance, void* stream);
+/* autograd backward of raw2outputs('default') for upstream grads g_w [N,S] (NULL=0), g_depth,
+ * g_opacity, g_variance [N] (NULL=0): d_sigma [N,S]; d_rays [N,13] += (|d| and far terms) if non-NULL. */
+LB_API int lb_composite_bwd(const float* sigma, const float* z, const float* rays, const float* noise,
+                     const float* g_w, const float* g_depth, const float* g_opacity,
+                     const float* g_variance, int n_rays, int n_samples, float* d_sigma,
+                     float* d_rays, void* stream);
+
+/* ---- L1-L5: fused compositing + JS dynamic-margin depth loss + analytic gradient ---------- */
+/* Optimizer.compute_loss lidar branch (src/mapping/optimizer.py:719-848) with get_weights_gt
+ * (src/models/losses.py:29-51), fused with raw2outputs and its backward.
+ * Outputs: weights [N,S], depth/opacity/variance [N], per-ray js [N] (clamped score), eps [N],
+ * loss_parts [4] += {sum_opaque (s*D-g)^2, sum_all |w-w_gt| (or squared), sum_opaque |A-1|, n_opaque_local},
+ * d_sigma [N,S] = dL/dsigma for grad_output 1, d_rays [N,13] (overwritten; |d| and far terms).
+ * cfg->n_opaque / n_total_samples carry the GLOBAL normalisers (see lb_count_opaque). */
+LB_API int lb_composite_loss(const float* sigma, const float* z, const float* rays, const float* noise,
+                      const float* depth_gt, const lb_loss_config* cfg, int n_rays, int n_samples,
+                      float* weights, float* depth, float* opacity, float* variance, float* js,
+                      float* eps, float* loss_parts, float* d_sigma, float* d_rays, void* stream);
+/* count of opaque rays (depth_gt > 0 and depth_gt <= far; optimizer.py:724-727) -> count[0] (float, +=) */
+LB_API int lb_count_opaque(const float* rays, const float* depth_gt, int n_rays, float* count, void* stream);
+
+/* ---- O1/O2: optimiser step and occupancy update ------------------------------------------ */
+/* torch.optim.Adam defaults, no weight decay (src/mapping/optimizer.py:255-265): in-place on p, m, v.
+ * step is 1-based.  grad_scale multiplies g first (e.g. 1/world for averaged DP); zero_grad != 0 clears g. */
+LB_API int lb_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1,
+                 float beta2, float eps, int step, float grad_scale, int zero_grad, void* stream);
+/* _step_occupancy_grid (src/mapping/optimizer.py:897-908) with get_logits_grad (losses.py:54-62):
+ * occ_grad [D,D,D] += trilinear scatter of the log-odds update at xyz = o + d*z; the caller applies
+ * occ -= lr * occ_grad (lb_sgd_step) so that DP ranks can all-reduce occ_grad first. */
+LB_API int lb_occ_grad(const float* rays, const float* z, const float* depth_gt, float scale_factor,
+                int n_rays, int n_samples, int occ_dim, float* occ_grad, void* stream);
+LB_API int lb_sgd_step(float* p, float* g, int64_t n, float lr, int zero_grad, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LONER_B200_H */

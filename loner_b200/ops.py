@@ -1,0 +1,220 @@
+"""Tensor-level wrappers over the C-ABI (loner_b200/_lib.py).  PyTorch is used only for device
+memory and streams: every function takes CUDA fp32 tensors, passes raw pointers to
+libloner_b200.so on the current stream, and returns torch tensors.  No autograd here (see
+loner_b200/functional.py) and no fallback: a CPU tensor is an error.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import GridConfig, LossConfig, LOSS_KINDS, LonerB200Error
+
+MLP_PARAMS = 64 * 32 + 16 * 64
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t, dtype=torch.float32, name="tensor"):
+    """Raw device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise LonerB200Error(f"{name} must be a CUDA tensor: loner_b200 has no CPU path")
+    if t.dtype != dtype:
+        raise LonerB200Error(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise LonerB200Error(f"{name} must be contiguous")
+    return C.c_void_p(t.data_ptr())
+
+
+class Plan:
+    """Immutable hash-grid level table + MLP dims (lb_plan). Mirrors the tcnn config dict keys
+    (reference cfg/nerf_config/default_nerf_hash.yaml:14-31)."""
+
+    def __init__(self, n_levels=16, n_features_per_level=2, log2_hashmap_size=18, base_resolution=16,
+                 per_level_scale=2.0, mlp_width=64, mlp_hidden_layers=1):
+        self.cfg = GridConfig(n_levels, n_features_per_level, log2_hashmap_size, base_resolution,
+                              per_level_scale, mlp_width, mlp_hidden_layers)
+        self._h = C.c_void_p()
+        _lib.call("lb_plan_create", C.byref(self.cfg), C.byref(self._h))
+        a, b = C.c_int64(), C.c_int64()
+        _lib.call("lb_plan_param_counts", self._h, C.byref(a), C.byref(b))
+        self.n_mlp_params, self.n_table_params = a.value, b.value
+        self.n_params = a.value + b.value
+        self.n_levels = n_levels
+        self.n_enc = n_levels * n_features_per_level
+
+    @classmethod
+    def from_tcnn_config(cls, encoding_config, network_config=None):
+        if encoding_config.get("otype") != "HashGrid":
+            raise LonerB200Error(f"unsupported encoding {encoding_config.get('otype')}")
+        kw = dict(n_levels=int(encoding_config["n_levels"]),
+                  n_features_per_level=int(encoding_config["n_features_per_level"]),
+                  log2_hashmap_size=int(encoding_config["log2_hashmap_size"]),
+                  base_resolution=int(encoding_config["base_resolution"]),
+                  per_level_scale=float(encoding_config.get("per_level_scale", 2.0)))
+        if network_config is not None:
+            kw.update(mlp_width=int(network_config["n_neurons"]),
+                      mlp_hidden_layers=int(network_config["n_hidden_layers"]))
+        return cls(**kw)
+
+    def level(self, l):
+        s, r, o, n, d = C.c_float(), C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_int32()
+        _lib.call("lb_plan_level", self._h, l, C.byref(s), C.byref(r), C.byref(o), C.byref(n), C.byref(d))
+        return dict(scale=s.value, res=r.value, offset=o.value, size=n.value, dense=bool(d.value))
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib.load().lb_plan_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+
+_T_STEPS = {}
+
+
+def t_steps(n, device):
+    """linspace(0,1,n) computed on the CPU (so every device consumes identical bits), cached."""
+    key = (n, str(device))
+    if key not in _T_STEPS:
+        _T_STEPS[key] = torch.linspace(0, 1, n).to(device)
+    return _T_STEPS[key]
+
+
+def sample_occ(rays, occ, u1, u2, n_samples, perturb, debug=False):
+    """OccGridRaySampler.get_samples. rays [N,13], occ [..,D,D,D], u1/u2 [N,S/2] -> z [N,S] sorted.
+    debug=True also returns (occ_bits uint8 [N,S/2], inds int64 [N,S/2])."""
+    n = rays.shape[0]
+    s2 = n_samples // 2
+    D = occ.shape[-1]
+    z = torch.empty(n, n_samples, device=rays.device, dtype=torch.float32)
+    bits = torch.empty(n, s2, device=rays.device, dtype=torch.uint8) if debug else None
+    inds = torch.empty(n, s2, device=rays.device, dtype=torch.int64) if debug else None
+    _lib.call("lb_sample_occ", _p(rays, name="rays"), _p(occ, name="occ"), D, _p(t_steps(s2, rays.device)),
+              _p(u1, name="u1"), _p(u2, name="u2"), n, n_samples, float(perturb), _p(z),
+              _p(bits, torch.uint8), _p(inds, torch.int64), _stream())
+    return (z, bits, inds) if debug else z
+
+
+def sample_uniform(rays, u, n_samples, perturb):
+    n = rays.shape[0]
+    z = torch.empty(n, n_samples, device=rays.device, dtype=torch.float32)
+    _lib.call("lb_sample_uniform", _p(rays, name="rays"), _p(t_steps(n_samples, rays.device)), _p(u, name="u"),
+              n, n_samples, float(perturb), _p(z), _stream())
+    return z
+
+
+def encode_fwd(plan, x01, table):
+    P = x01.shape[0]
+    enc = torch.empty(P, plan.n_enc, device=x01.device, dtype=torch.float32)
+    _lib.call("lb_encode_fwd", plan._h, _p(x01, name="x01"), _p(table, name="table"), P, _p(enc), _stream())
+    return enc
+
+
+def encode_bwd(plan, x01, table, d_enc, grad_table, need_dx):
+    P = x01.shape[0]
+    dx = torch.empty(P, 3, device=x01.device, dtype=torch.float32) if need_dx else None
+    _lib.call("lb_encode_bwd", plan._h, _p(x01, name="x01"), _p(table, name="table"), _p(d_enc, name="d_enc"), P,
+              _p(grad_table, name="grad_table"), _p(dx), _stream())
+    return dx
+
+
+def sigma_fwd(plan, params, rays=None, z=None, x01=None, save_enc=True):
+    """Fused xyz -> hash grid -> MLP. Returns (sigma [N,S] or [P], enc_save or None)."""
+    if rays is not None:
+        n, s = z.shape
+        shape = (n, s)
+    else:
+        n, s = x01.shape[0], 1
+        shape = (n,)
+    sigma = torch.empty(shape, device=params.device, dtype=torch.float32)
+    enc = torch.empty(n * s, plan.n_enc, device=params.device, dtype=torch.float32) if save_enc else None
+    _lib.call("lb_sigma_fwd", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
+              _p(params, name="params"), n, s, _p(sigma), _p(enc), _stream())
+    return sigma, enc
+
+
+def sigma_bwd(plan, params, enc, d_sigma, rays=None, z=None, x01=None, grad_params=None, d_rays=None, need_dx=False):
+    """Accumulates into grad_params / d_rays (caller zero-fills); returns d_x01 when asked."""
+    if rays is not None:
+        n, s = z.shape
+    else:
+        n, s = x01.shape[0], 1
+    dx = torch.empty(n, 3, device=params.device, dtype=torch.float32) if (need_dx and rays is None) else None
+    _lib.call("lb_sigma_bwd", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
+              _p(params, name="params"), _p(enc, name="enc"), _p(d_sigma, name="d_sigma"), n, s,
+              _p(grad_params, name="grad_params"), _p(d_rays, name="d_rays"), _p(dx), _stream())
+    return dx
+
+
+def composite_fwd(sigma, z, rays, noise=None, strategy="default", want_variance=True):
+    n, s = z.shape
+    dev = z.device
+    w = torch.empty(n, s, device=dev, dtype=torch.float32)
+    depth = torch.empty(n, device=dev, dtype=torch.float32)
+    opac = torch.empty(n, device=dev, dtype=torch.float32)
+    var = torch.empty(n, device=dev, dtype=torch.float32) if want_variance else None
+    strat = {"default": 0, "adjusted": 1}[strategy]
+    _lib.call("lb_composite_fwd", _p(sigma, name="sigma"), _p(z, name="z"), _p(rays, name="rays"), _p(noise, name="noise"),
+              n, s, strat, _p(w), _p(depth), _p(opac), _p(var), _stream())
+    return w, depth, opac, var
+
+
+def composite_bwd(sigma, z, rays, noise, g_w, g_depth, g_opacity, g_variance, d_rays=None):
+    n, s = z.shape
+    ds = torch.empty(n, s, device=z.device, dtype=torch.float32)
+    _lib.call("lb_composite_bwd", _p(sigma, name="sigma"), _p(z, name="z"), _p(rays, name="rays"), _p(noise, name="noise"),
+              _p(g_w, name="g_w"), _p(g_depth, name="g_depth"), _p(g_opacity, name="g_opacity"),
+              _p(g_variance, name="g_variance"), n, s, _p(ds), _p(d_rays, name="d_rays"), _stream())
+    return ds
+
+
+def count_opaque(rays, depth_gt):
+    c = torch.zeros(1, device=rays.device, dtype=torch.float32)
+    _lib.call("lb_count_opaque", _p(rays, name="rays"), _p(depth_gt, name="depth_gt"), rays.shape[0], _p(c), _stream())
+    return c
+
+
+def make_loss_config(kind, scale_factor, n_opaque, n_total_samples, min_js_score=1.0, max_js_score=10.0,
+                     js_alpha=1.0, min_depth_eps=0.5, depth_eps=3.0, los_lambda=1000.0, depthloss_lambda=0.005):
+    return LossConfig(LOSS_KINDS[kind], float(scale_factor), float(min_js_score), float(max_js_score),
+                      float(js_alpha), float(min_depth_eps), float(depth_eps), float(los_lambda),
+                      float(depthloss_lambda), float(n_opaque), float(n_total_samples))
+
+
+def composite_loss(sigma, z, rays, noise, depth_gt, cfg, loss_parts, want_grad=True):
+    """Fused compositing + loss (+ analytic gradient). loss_parts [4] is accumulated into.
+    Returns dict(weights, depth, opacity, variance, js, eps, d_sigma, d_rays)."""
+    n, s = z.shape
+    dev = z.device
+    f = lambda *shape: torch.empty(*shape, device=dev, dtype=torch.float32)
+    out = dict(weights=f(n, s), depth=f(n), opacity=f(n), variance=f(n), js=f(n), eps=f(n),
+               d_sigma=f(n, s) if want_grad else None, d_rays=f(n, 13) if want_grad else None)
+    _lib.call("lb_composite_loss", _p(sigma, name="sigma"), _p(z, name="z"), _p(rays, name="rays"), _p(noise, name="noise"),
+              _p(depth_gt, name="depth_gt"), C.byref(cfg), n, s, _p(out["weights"]), _p(out["depth"]),
+              _p(out["opacity"]), _p(out["variance"]), _p(out["js"]), _p(out["eps"]), _p(loss_parts, name="loss_parts"),
+              _p(out["d_sigma"]), _p(out["d_rays"]), _stream())
+    return out
+
+
+def adam_step(p, g, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, grad_scale=1.0, zero_grad=False):
+    _lib.call("lb_adam_step", _p(p, name="p"), _p(g, name="g"), _p(m, name="m"), _p(v, name="v"), p.numel(),
+              float(lr), float(beta1), float(beta2), float(eps), int(step), float(grad_scale), int(zero_grad), _stream())
+
+
+def sgd_step(p, g, lr, zero_grad=False):
+    _lib.call("lb_sgd_step", _p(p, name="p"), _p(g, name="g"), p.numel(), float(lr), int(zero_grad), _stream())
+
+
+def occ_grad(rays, z, depth_gt, scale_factor, occ_dim, out=None):
+    n, s = z.shape
+    if out is None:
+        out = torch.zeros(occ_dim, occ_dim, occ_dim, device=z.device, dtype=torch.float32)
+    _lib.call("lb_occ_grad", _p(rays, name="rays"), _p(z, name="z"), _p(depth_gt, name="depth_gt"), float(scale_factor),
+              n, s, occ_dim, _p(out, name="occ_grad"), _stream())
+    return out

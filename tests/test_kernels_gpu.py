@@ -1,0 +1,239 @@
+"""GPU parity tests: every C-ABI kernel (through loner_b200.ops) against the CPU oracle
+(oracle/loner_oracle.py) and the golden vectors produced by the reference's own Python.
+
+Bars (BASELINE.json north_star): occupancy bits and sample indices bit-exact; everything
+floating-point within 1e-3 relative (we assert much tighter where fp32 allows).
+"""
+import pytest
+import torch
+
+from conftest import load_golden, golden_params
+
+pytestmark = pytest.mark.gpu
+
+OGM_CASES = ["c1_ogm_l1js", "s128_ogm_l2js"]
+ALL_CASES = OGM_CASES + ["c1_uniform_l2los"]
+REL = 1e-3  # north_star tolerance
+
+
+def rel_err(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from loner_b200 import ops as _ops
+    return _ops
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import loner_oracle
+    return loner_oracle
+
+
+# ------------------------------------------------------------------------------------------ sampling
+@pytest.mark.parametrize("name", OGM_CASES)
+def test_sample_occ_bit_exact_golden(name, dev, ops, O):
+    g = load_golden(name)
+    ref = O.sample_occ(g["rays"], g["occ"], g["u1"], g["u2"], g["n_samples"], 1.0)
+    z, bits, inds = ops.sample_occ(g["rays"].to(dev), g["occ"].to(dev).contiguous(), g["u1"].to(dev), g["u2"].to(dev),
+                                   g["n_samples"], 1.0, debug=True)
+    assert torch.equal(bits.cpu().bool(), ref["occ_bits"]), "occupancy bits differ from oracle"
+    assert torch.equal(inds.cpu(), ref["inds"]), "searchsorted indices differ from oracle"
+    assert torch.equal(z.cpu(), ref["z"]), "sorted depths differ from oracle"
+    # and against the reference's own run (same tolerance the oracle is pinned with)
+    assert torch.equal(bits.cpu().bool(), g["occ_bits"])
+    assert (inds.cpu() != g["inds"]).float().mean().item() < 1e-3
+
+
+@pytest.mark.parametrize("S,N,D,perturb", [(512, 1024, 100, 1.0), (64, 777, 33, 1.0), (256, 300, 50, 0.0), (2048, 64, 100, 0.0)])
+def test_sample_occ_bit_exact_seeded(S, N, D, perturb, dev, ops, O):
+    gen = torch.Generator().manual_seed(S + N)
+    o = (torch.rand(N, 3, generator=gen) - 0.5) * 0.6
+    d = torch.nn.functional.normalize(torch.randn(N, 3, generator=gen), dim=1)
+    near = torch.full((N, 1), 0.02)
+    far = near + 0.05 + 0.3 * torch.rand(N, 1, generator=gen)
+    rays = torch.cat([o, d, -d, torch.zeros(N, 2), near, far], 1)
+    occ = torch.randn(1, 1, D, D, D, generator=gen) * 0.5
+    occ[occ.abs() < 0.2] = 0.0        # exact-zero logits exercise the prob == 0 branch
+    u1 = torch.rand(N, S // 2, generator=gen)
+    u2 = torch.rand(N, S // 2, generator=gen)
+    u2[0, :4] = torch.tensor([0.0, 1.0 - 2 ** -24, 0.5, 2 ** -30])
+    ref = O.sample_occ(rays, occ, u1, u2, S, perturb)
+    z, bits, inds = ops.sample_occ(rays.to(dev), occ.to(dev), u1.to(dev) if perturb > 0 else None, u2.to(dev), S, perturb, debug=True)
+    assert torch.equal(bits.cpu().bool(), ref["occ_bits"])
+    assert torch.equal(inds.cpu(), ref["inds"])
+    assert torch.equal(z.cpu(), ref["z"])
+    assert (z[:, 1:] >= z[:, :-1]).all()
+
+
+def test_sample_uniform_exact(dev, ops, O):
+    g = load_golden("c1_uniform_l2los")
+    z = ops.sample_uniform(g["rays"].to(dev), g["u1"].to(dev), g["n_samples"], 1.0)
+    assert torch.equal(z.cpu(), g["z"])
+    z0 = ops.sample_uniform(g["rays"].to(dev), None, 96, 0.0)
+    assert torch.equal(z0.cpu(), O.sample_uniform(g["rays"], None, 96, 0.0))
+
+
+# ------------------------------------------------------------------------------------------ field
+@pytest.mark.parametrize("log2T", [14, 19])
+def test_encode_fwd_bwd(log2T, dev, ops, O):
+    gen = torch.Generator().manual_seed(log2T)
+    plan = ops.Plan(log2_hashmap_size=log2T)
+    P = 5000
+    x = torch.rand(P, 3, generator=gen)
+    x[:8] = torch.tensor([[0, 0, 0], [1, 1, 1], [0.5, 0.5, 0.5], [1, 0, 0], [0, 1, 0.25], [0.999999, 0.5, 0], [1e-7, 1e-7, 1e-7], [0.25, 0.75, 1]])
+    table = (torch.rand(plan.n_table_params, generator=gen) * 2 - 1) * 0.3
+    de = torch.randn(P, 32, generator=gen)
+    xr, tr = x.clone().requires_grad_(True), table.clone().requires_grad_(True)
+    ref = O.hash_encode(xr, tr, log2T)
+    ref.backward(de)
+    enc = ops.encode_fwd(plan, x.to(dev), table.to(dev))
+    assert rel_err(enc, ref) < 1e-5
+    gt = torch.zeros_like(table, device=dev)
+    dx = ops.encode_bwd(plan, x.to(dev), table.to(dev), de.to(dev), gt, need_dx=True)
+    assert rel_err(gt, tr.grad) < 1e-4
+    # positions exactly on cell faces have one-sided derivatives; compare the generic points
+    assert rel_err(dx[8:], xr.grad[8:]) < 1e-4
+
+
+@pytest.mark.parametrize("name", ALL_CASES)
+def test_sigma_fwd_bwd_golden(name, dev, ops, O):
+    g = load_golden(name)
+    p = golden_params(g)
+    plan = ops.Plan(log2_hashmap_size=g["log2_T"])
+    assert plan.n_params == p.numel()
+    rays, z = g["rays"].to(dev), g["z"].to(dev)
+    sigma, enc = ops.sigma_fwd(plan, p.to(dev), rays=rays, z=z)
+    assert rel_err(sigma, g["sigma"]) < 1e-4
+    # backward against oracle autograd for a random upstream gradient
+    gen = torch.Generator().manual_seed(1)
+    ds = torch.randn(z.shape, generator=gen)
+    pr, rr = p.clone().requires_grad_(True), g["rays"].clone().requires_grad_(True)
+    xyz = rr[:, None, 0:3] + rr[:, None, 3:6] * g["z"][..., None]
+    O.sigma_field(xyz.reshape(-1, 3), pr, g["log2_T"]).view(z.shape).backward(ds)
+    gp = torch.zeros_like(p, device=dev)
+    dr = torch.zeros(rays.shape, device=dev)
+    ops.sigma_bwd(plan, p.to(dev), enc, ds.to(dev), rays=rays, z=z, grad_params=gp, d_rays=dr)
+    assert rel_err(gp[:3072], pr.grad[:3072]) < 1e-4
+    assert rel_err(gp[3072:], pr.grad[3072:]) < 1e-4
+    assert rel_err(dr[:, :6], rr.grad[:, :6]) < 1e-3
+    assert (dr[:, 6:] == 0).all()
+    # x01 point source (tcnn module path) gives the same numbers
+    x01 = ((xyz.detach().reshape(-1, 3) + 1) / 2).to(dev).contiguous()
+    s2, enc2 = ops.sigma_fwd(plan, p.to(dev), x01=x01)
+    assert rel_err(s2.view(z.shape), g["sigma"]) < 1e-4
+    gp2 = torch.zeros_like(gp)
+    dx = ops.sigma_bwd(plan, p.to(dev), enc2, ds.to(dev).reshape(-1), x01=x01, grad_params=gp2, need_dx=True)
+    assert rel_err(gp2, pr.grad) < 1e-4
+    assert dx.shape == (x01.shape[0], 3)
+    # frozen sigma head (tracking phase): ray gradients only
+    dr3 = torch.zeros(rays.shape, device=dev)
+    ops.sigma_bwd(plan, p.to(dev), enc, ds.to(dev), rays=rays, z=z, grad_params=None, d_rays=dr3)
+    assert rel_err(dr3, dr) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------ compositing
+@pytest.mark.parametrize("name", ALL_CASES)
+def test_composite_fwd_golden(name, dev, ops, O):
+    g = load_golden(name)
+    w, depth, opac, var = ops.composite_fwd(g["sigma"].to(dev), g["z"].to(dev), g["rays"].to(dev), g["noise"].to(dev))
+    assert rel_err(w, g["weights"]) < 1e-5
+    assert rel_err(depth, g["depth"]) < 1e-5
+    assert rel_err(opac, g["opacity"]) < 1e-5
+    assert rel_err(var, g["variance"]) < 1e-4
+    if "adj_depth" in g:
+        w2, d2, _, v2 = ops.composite_fwd(g["sigma"].to(dev), g["z"].to(dev), g["rays"].to(dev), g["noise"].to(dev), strategy="adjusted")
+        assert (d2.cpu() != g["adj_depth"]).float().mean().item() < 0.01     # a crossing within 1 ulp of 0.5 may move one sample
+        assert rel_err(w2, g["adj_weights"]) < 1e-5
+        same = d2.cpu() == g["adj_depth"]
+        assert rel_err(v2.cpu()[same], g["adj_variance"][same]) < 1e-4
+
+
+@pytest.mark.parametrize("S,N", [(64, 130), (512, 257), (100, 33), (2048, 9)])
+def test_composite_bwd_matches_autograd(S, N, dev, ops, O):
+    gen = torch.Generator().manual_seed(S * 7 + N)
+    z = torch.sort(torch.rand(N, S, generator=gen) * 0.4 + 0.01, dim=1).values
+    sigma = torch.randn(N, S, generator=gen) * 30
+    noise = torch.randn(N, S, generator=gen)
+    d = torch.randn(N, 3, generator=gen)
+    far = torch.rand(N, 1, generator=gen) * 0.3 + 0.45
+    rays = torch.cat([torch.zeros(N, 3), d, -d, torch.zeros(N, 2), torch.full((N, 1), 0.01), far], 1)
+    gw, gd, go, gv = (torch.randn(N, S, generator=gen), torch.randn(N, generator=gen),
+                      torch.randn(N, generator=gen), torch.randn(N, generator=gen))
+    sr, rr = sigma.clone().requires_grad_(True), rays.clone().requires_grad_(True)
+    c = O.composite(sr, z, rr[:, 3:6], rr[:, -1:], noise)
+    ((c["weights"] * gw).sum() + (c["depth"] * gd).sum() + (c["opacity"] * go).sum() + (c["variance"] * gv).sum()).backward()
+    w, depth, opac, var = ops.composite_fwd(sigma.to(dev), z.to(dev), rays.to(dev), noise.to(dev))
+    assert rel_err(w, c["weights"]) < 1e-5 and rel_err(depth, c["depth"]) < 1e-5 and rel_err(var, c["variance"]) < 1e-4
+    dr = torch.zeros(N, 13, device=dev)
+    ds = ops.composite_bwd(sigma.to(dev), z.to(dev), rays.to(dev), noise.to(dev), gw.to(dev), gd.to(dev), go.to(dev), gv.to(dev), d_rays=dr)
+    assert rel_err(ds, sr.grad) < 1e-4
+    assert rel_err(dr, rr.grad) < 1e-4
+
+
+# ------------------------------------------------------------------------------------------ loss
+@pytest.mark.parametrize("name", ALL_CASES)
+def test_composite_loss_golden(name, dev, ops, O):
+    g = load_golden(name)
+    rays, z, sig, noise, dgt = (g[k].to(dev) for k in ("rays", "z", "sigma", "noise", "depths"))
+    n_op = ops.count_opaque(rays, dgt)
+    far = g["rays"][:, -1]
+    assert n_op.item() == float(((g["depths"] > 0) & ~(g["depths"] > far)).sum())
+    cfg = ops.make_loss_config(g["loss_selection"], float(g["scale"]), n_op.item(), z.numel(), min_js_score=g["min_js"])
+    parts = torch.zeros(4, device=dev)
+    out = ops.composite_loss(sig, z, rays, noise, dgt, cfg, parts)
+    pc = parts.cpu()
+    loss = 0.005 * pc[0] / pc[3] + 1000.0 * pc[1] / z.numel() + pc[2] / pc[3]
+    assert abs(loss.item() - g["loss"].item()) < 1e-4 * abs(g["loss"].item())
+    assert rel_err(out["weights"], g["weights"]) < 1e-5
+    assert abs(out["eps"].mean().item() - g["depth_eps"]) < 1e-4 * g["depth_eps"]
+    # gradients: oracle autograd from sigma on the same samples
+    sr, rr = g["sigma"].clone().requires_grad_(True), g["rays"].clone().requires_grad_(True)
+    c = O.composite(sr, g["z"], rr[:, 3:6], rr[:, -1:], g["noise"])
+    ls = O.depth_loss(c["weights"], c["depth"], c["opacity"], g["z"], rr[:, -1:], g["depths"], g["scale"],
+                      dict(loss_selection=g["loss_selection"], min_js_score=g["min_js"]))
+    ls["loss"].backward()
+    assert rel_err(out["js"], ls["js"]) < 1e-3
+    assert rel_err(out["eps"], ls["eps"]) < 1e-4
+    assert rel_err(out["d_sigma"], sr.grad) < 1e-3
+    assert rel_err(out["d_rays"], rr.grad) < 1e-3
+
+
+# ------------------------------------------------------------------------------------------ optimiser / occupancy
+def test_adam_and_sgd(dev, ops, O):
+    gen = torch.Generator().manual_seed(0)
+    n = 100003
+    p = torch.randn(n, generator=gen); m = torch.zeros(n); v = torch.zeros(n)
+    pd, md, vd = p.to(dev), m.to(dev), v.to(dev)
+    for step in range(1, 5):
+        gr = torch.randn(n, generator=gen) * 0.1
+        gr[::3] = 0
+        O.adam_step(p, gr, m, v, step, 0.01)
+        gd = gr.to(dev)
+        ops.adam_step(pd, gd, md, vd, step, 0.01, zero_grad=(step == 4))
+    assert rel_err(pd, p) < 1e-5 and rel_err(md, m) < 1e-5 and rel_err(vd, v) < 1e-5
+    assert (gd == 0).all()
+    q = torch.randn(1000, generator=gen); gq = torch.randn(1000, generator=gen)
+    qd, gqd = q.to(dev), gq.to(dev)
+    ops.sgd_step(qd, gqd, 1e-2)
+    assert rel_err(qd, q - 1e-2 * gq) < 1e-6
+
+
+@pytest.mark.parametrize("name", OGM_CASES)
+def test_occ_update_golden(name, dev, ops, O):
+    g = load_golden(name)
+    D = g["occ"].shape[-1]
+    grad = ops.occ_grad(g["rays"].to(dev), g["z"].to(dev), g["depths"].to(dev), float(g["scale"]), D)
+    occ = g["occ"].to(dev).clone().contiguous()
+    ops.sgd_step(occ.view(-1), grad.view(-1), 1e-4)
+    assert rel_err(occ - g["occ"].to(dev), g["occ_after"] - g["occ"]) < 1e-4
+    assert rel_err(occ, g["occ_after"]) < 1e-6
