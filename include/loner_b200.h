@@ -161,8 +161,8 @@ LB_API int lb_count_opaque(const float* rays, const float* depth_gt, int n_rays,
 /* ---- O1/O2: optimiser step and occupancy update ------------------------------------------ */
 /* torch.optim.Adam defaults, no weight decay (src/mapping/optimizer.py:255-265): in-place on p, m, v.
  * step is 1-based.  grad_scale multiplies g first (e.g. 1/world for averaged DP); zero_grad != 0 clears g. */
-LB_API int lb_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1,
-                 float beta2, float eps, int step, float grad_scale, int zero_grad, void* stream);
+LB_API int lb_adam_step(float* p, float* g, float* m, float* v, int64_t n, double lr, double beta1,
+                 double beta2, double eps, int step, float grad_scale, int zero_grad, void* stream);
 /* _step_occupancy_grid (src/mapping/optimizer.py:897-908) with get_logits_grad (losses.py:54-62):
  * occ_grad [D,D,D] += trilinear scatter of the log-odds update at xyz = o + d*z; the caller applies
  * occ -= lr * occ_grad (lb_sgd_step) so that DP ranks can all-reduce occ_grad first. */

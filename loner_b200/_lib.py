@@ -53,7 +53,7 @@ SIGNATURES = {
     "lb_composite_loss": (_I, [_P, _P, _P, _P, _P, C.POINTER(LossConfig), _I, _I,
                                _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "lb_count_opaque": (_I, [_P, _P, _I, _P, _P]),
-    "lb_adam_step": (_I, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _I, _F, _I, _P]),
+    "lb_adam_step": (_I, [_P, _P, _P, _P, _L, C.c_double, C.c_double, C.c_double, C.c_double, _I, _F, _I, _P]),
     "lb_occ_grad": (_I, [_P, _P, _P, _F, _I, _I, _I, _P, _P]),
     "lb_sgd_step": (_I, [_P, _P, _L, _F, _I, _P]),
 }

@@ -26,9 +26,11 @@ __device__ __forceinline__ Point load_point(const float* __restrict__ rays, cons
         const size_t r = p / (size_t)n_samples;
         const float* ray = rays + r * LB_RAY_STRIDE;
         const float z = __ldg(zv + p);
-        q.x = (fmaf(__ldg(ray + 3), z, __ldg(ray + 0)) + 1.0f) * 0.5f;
-        q.y = (fmaf(__ldg(ray + 4), z, __ldg(ray + 1)) + 1.0f) * 0.5f;
-        q.z = (fmaf(__ldg(ray + 5), z, __ldg(ray + 2)) + 1.0f) * 0.5f;
+        // same roundings as the reference's torch ops (o + d*z, then (xyz+1)/2): at the finest level one
+        // ulp of x01 is 3 % of a cell, so the sample position must match bit for bit
+        q.x = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 0), __fmul_rn(__ldg(ray + 3), z)), 1.0f), 0.5f);
+        q.y = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 1), __fmul_rn(__ldg(ray + 4), z)), 1.0f), 0.5f);
+        q.z = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 2), __fmul_rn(__ldg(ray + 5), z)), 1.0f), 0.5f);
         if (z_out) *z_out = z;
     } else {
         q.x = __ldg(x01 + 3 * p + 0);

@@ -10,7 +10,8 @@ namespace {
 
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, size_t n,
-            float lr_over_bc1, float inv_sqrt_bc2, float b1, float b2, float eps, float gscale, int zero_grad) {
+            float lr_over_bc1, float inv_sqrt_bc2, float b1, float b2, float omb1, float omb2, float eps,
+            float gscale, int zero_grad) {
     const size_t n4 = n / 4;
     float4* p4 = reinterpret_cast<float4*>(p);
     float4* g4 = reinterpret_cast<float4*>(g);
@@ -19,8 +20,8 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     auto upd = [&](float& pp, float gg, float& mm, float& vv) {
         gg *= gscale;
-        mm = b1 * mm + (1.0f - b1) * gg;
-        vv = b2 * vv + (1.0f - b2) * gg * gg;
+        mm = b1 * mm + omb1 * gg;
+        vv = b2 * vv + omb2 * gg * gg;
         const float denom = sqrtf(vv) * inv_sqrt_bc2 + eps;
         pp -= lr_over_bc1 * (mm / denom);
     };
@@ -90,16 +91,19 @@ int blocks_for(size_t n, int per_block) {
 
 }  // namespace
 
-extern "C" int lb_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1,
-                            float beta2, float eps, int step, float grad_scale, int zero_grad, void* stream) {
+extern "C" int lb_adam_step(float* p, float* g, float* m, float* v, int64_t n, double lr, double beta1,
+                            double beta2, double eps, int step, float grad_scale, int zero_grad, void* stream) {
     LB_REQUIRE(p && g && m && v, "null pointer");
     LB_REQUIRE(n >= 0 && step >= 1, "bad size / step");
     LB_REQUIRE((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "buffers must be 16-byte aligned");
     if (n == 0) return LB_OK;
-    const double bc1 = 1.0 - pow((double)beta1, (double)step);
-    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    // hyper-parameters arrive as doubles (Python floats) so that 1-beta, lr/bc1, sqrt(bc2) round once,
+    // exactly like torch.optim.Adam's host-side scalar arithmetic
+    const double bc1 = 1.0 - pow(beta1, (double)step);
+    const double bc2 = 1.0 - pow(beta2, (double)step);
     adam_kernel<<<blocks_for((size_t)n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(
-        p, g, m, v, (size_t)n, (float)((double)lr / bc1), (float)(1.0 / sqrt(bc2)), beta1, beta2, eps, grad_scale, zero_grad);
+        p, g, m, v, (size_t)n, (float)(lr / bc1), (float)(1.0 / sqrt(bc2)), (float)beta1, (float)beta2,
+        (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps, grad_scale, zero_grad);
     LB_LAUNCH_CHECK("lb_adam_step");
     return LB_OK;
 }

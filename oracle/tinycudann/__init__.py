@@ -86,8 +86,10 @@ class _HashGridFn:
         table = table_flat.view(self.n_entries, self.F)
         outs = []
         for lvl in self.levels:
-            scale = torch.tensor(lvl["scale"], dtype=torch.float32, device=x.device)
-            p = x * scale + 0.5
+            # tcnn pos_fract: fmaf(scale, x, 0.5f) -- ONE rounding.  At the finest levels p ~ 5e5 has an
+            # ulp of 2^-5, so a doubly-rounded x*scale+0.5 would move the fractional position by up to
+            # 3 % of a cell; fp64 evaluation rounded once to fp32 reproduces the fused op exactly.
+            p = (x.double() * lvl["scale"] + 0.5).float()
             cell = torch.floor(p)
             frac = p - cell
             ci = cell.detach().to(torch.int64)
