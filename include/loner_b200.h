@@ -150,9 +150,11 @@ LB_API int lb_composite_bwd(const float* sigma, const float* z, const float* ray
  * Outputs: weights [N,S], depth/opacity/variance [N], per-ray js [N] (clamped score), eps [N],
  * loss_parts [4] += {sum_opaque (s*D-g)^2, sum_all |w-w_gt| (or squared), sum_opaque |A-1|, n_opaque_local},
  * d_sigma [N,S] = dL/dsigma for grad_output 1, d_rays [N,13] (overwritten; |d| and far terms).
- * cfg->n_opaque / n_total_samples carry the GLOBAL normalisers (see lb_count_opaque). */
+ * cfg->n_opaque / n_total_samples carry the GLOBAL normalisers (see lb_count_opaque); when
+ * n_opaque_dev (device float[1]) is non-NULL it overrides cfg->n_opaque without a host round trip. */
 LB_API int lb_composite_loss(const float* sigma, const float* z, const float* rays, const float* noise,
-                      const float* depth_gt, const lb_loss_config* cfg, int n_rays, int n_samples,
+                      const float* depth_gt, const lb_loss_config* cfg, const float* n_opaque_dev,
+                      int n_rays, int n_samples,
                       float* weights, float* depth, float* opacity, float* variance, float* js,
                       float* eps, float* loss_parts, float* d_sigma, float* d_rays, void* stream);
 /* count of opaque rays (depth_gt > 0 and depth_gt <= far; optimizer.py:724-727) -> count[0] (float, +=) */

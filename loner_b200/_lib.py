@@ -50,7 +50,7 @@ SIGNATURES = {
     "lb_sigma_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "lb_composite_fwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P]),
     "lb_composite_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P]),
-    "lb_composite_loss": (_I, [_P, _P, _P, _P, _P, C.POINTER(LossConfig), _I, _I,
+    "lb_composite_loss": (_I, [_P, _P, _P, _P, _P, C.POINTER(LossConfig), _P, _I, _I,
                                _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "lb_count_opaque": (_I, [_P, _P, _I, _P, _P]),
     "lb_adam_step": (_I, [_P, _P, _P, _P, _L, C.c_double, C.c_double, C.c_double, C.c_double, _I, _F, _I, _P]),
@@ -87,6 +87,43 @@ def check(rc, what=""):
         raise LonerB200Error(f"{what} failed with status {rc}: {msg}")
 
 
+# Launch accounting: every compute entry point launches exactly one kernel of ours.  `LAUNCHES` counts
+# them; with `TIMING` on, each call is bracketed by CUDA events on the launching stream (bench.py reads
+# the per-kernel device time for the roofline figures).
+LAUNCHES = {}
+TIMING = {"on": False, "events": []}
+_HOST_ONLY = {"lb_plan_create", "lb_plan_param_counts", "lb_plan_level"}
+
+
 def call(name, *args):
     """Calls an int-returning entry point and raises on a non-zero status."""
-    check(getattr(load(), name)(*args), name)
+    fn = getattr(load(), name)
+    if name in _HOST_ONLY:
+        check(fn(*args), name)
+        return
+    LAUNCHES[name] = LAUNCHES.get(name, 0) + 1
+    if TIMING["on"]:
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        check(fn(*args), name)
+        e1.record()
+        TIMING["events"].append((name, e0, e1))
+    else:
+        check(fn(*args), name)
+
+
+def reset_counters():
+    LAUNCHES.clear()
+    TIMING["events"].clear()
+
+
+def kernel_times():
+    """{name: (launches, total_ms)} for calls made while TIMING was on (synchronises)."""
+    import torch
+    torch.cuda.synchronize()
+    out = {}
+    for name, e0, e1 in TIMING["events"]:
+        n, t = out.get(name, (0, 0.0))
+        out[name] = (n + 1, t + e0.elapsed_time(e1))
+    return out

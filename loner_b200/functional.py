@@ -1,0 +1,136 @@
+"""torch.autograd.Function wrappers around the C-ABI kernels (loner_b200/ops.py).
+
+These give the drop-in modules (loner_b200/tcnn.py, loner_b200/models.py, loner_b200/mapping.py) the
+autograd edges the reference gets from tinycudann + torch ops:
+  * SigmaFromRays   rays[N,13], z[N,S], params -> sigma[N,S]        (grads: params, rays[:, 0:6])
+  * SigmaFromPoints x01[P,3], params -> sigma[P]                    (grads: params, x01)
+  * HashEncode      x01[P,3], table -> enc[P,32]                    (grads: table, x01)
+  * Composite       sigma, z, rays, noise -> weights, depth, opacity, variance  (grads: sigma, rays)
+  * RenderLoss      fused compositing + JS depth loss -> scalar loss (grads: sigma, rays)
+"""
+import torch
+
+from . import ops
+
+
+def _zeros_like_flat(t):
+    return torch.zeros(t.numel(), device=t.device, dtype=torch.float32)
+
+
+class SigmaFromRays(torch.autograd.Function):
+    """Fused xyz=o+d*z -> hash grid -> 32-64-1 MLP (reference rendering_tcnn.py:390-392, nerf_tcnn.py:63-72)."""
+
+    @staticmethod
+    def forward(ctx, plan, params, rays, z):
+        rays_c, z_c = rays.detach().contiguous(), z.detach().contiguous()
+        need_grad = params.requires_grad or rays.requires_grad
+        sigma, enc = ops.sigma_fwd(plan, params.detach(), rays=rays_c, z=z_c, save_enc=need_grad)
+        ctx.plan = plan
+        ctx.save_for_backward(params.detach(), rays_c, z_c, enc)
+        ctx.need = (params.requires_grad, rays.requires_grad)
+        return sigma
+
+    @staticmethod
+    def backward(ctx, d_sigma):
+        params, rays, z, enc = ctx.saved_tensors
+        need_p, need_r = ctx.need
+        gp = torch.zeros_like(params) if need_p else None
+        dr = torch.zeros_like(rays) if need_r else None
+        if need_p or need_r:
+            ops.sigma_bwd(ctx.plan, params, enc, d_sigma.contiguous(), rays=rays, z=z, grad_params=gp, d_rays=dr)
+        return None, gp, dr, None
+
+
+class SigmaFromPoints(torch.autograd.Function):
+    """tcnn.NetworkWithInputEncoding.__call__(x) (reference nerf_tcnn.py:68,71)."""
+
+    @staticmethod
+    def forward(ctx, plan, params, x01):
+        x_c = x01.detach().contiguous()
+        need_grad = params.requires_grad or x01.requires_grad
+        sigma, enc = ops.sigma_fwd(plan, params.detach(), x01=x_c, save_enc=need_grad)
+        ctx.plan = plan
+        ctx.save_for_backward(params.detach(), x_c, enc)
+        ctx.need = (params.requires_grad, x01.requires_grad)
+        return sigma
+
+    @staticmethod
+    def backward(ctx, d_sigma):
+        params, x01, enc = ctx.saved_tensors
+        need_p, need_x = ctx.need
+        gp = torch.zeros_like(params) if need_p else None
+        dx = None
+        if need_p or need_x:
+            dx = ops.sigma_bwd(ctx.plan, params, enc, d_sigma.contiguous(), x01=x01, grad_params=gp, need_dx=need_x)
+        return None, gp, dx
+
+
+class HashEncode(torch.autograd.Function):
+    """tcnn.Encoding(HashGrid).__call__(x) (reference nerf_tcnn.py:40,64)."""
+
+    @staticmethod
+    def forward(ctx, plan, table, x01):
+        x_c = x01.detach().contiguous()
+        ctx.plan = plan
+        ctx.save_for_backward(table.detach(), x_c)
+        ctx.need = (table.requires_grad, x01.requires_grad)
+        return ops.encode_fwd(plan, x_c, table.detach())
+
+    @staticmethod
+    def backward(ctx, d_enc):
+        table, x01 = ctx.saved_tensors
+        need_t, need_x = ctx.need
+        gt = torch.zeros_like(table) if need_t else None
+        dx = None
+        if need_t or need_x:
+            dx = ops.encode_bwd(ctx.plan, x01, table, d_enc.contiguous(), gt, need_dx=need_x)
+        return None, gt, dx
+
+
+class Composite(torch.autograd.Function):
+    """raw2outputs, sigma-only, 'default' strategy (reference rendering_tcnn.py:219-295)."""
+
+    @staticmethod
+    def forward(ctx, sigma, z, rays, noise):
+        s_c, z_c, r_c = sigma.detach().contiguous(), z.detach().contiguous(), rays.detach().contiguous()
+        n_c = noise.detach().contiguous() if noise is not None else None
+        w, depth, opac, var = ops.composite_fwd(s_c, z_c, r_c, n_c, "default", True)
+        ctx.save_for_backward(s_c, z_c, r_c, n_c)
+        ctx.need_rays = rays.requires_grad
+        return w, depth, opac, var
+
+    @staticmethod
+    def backward(ctx, g_w, g_depth, g_opacity, g_var):
+        s, z, r, n = ctx.saved_tensors
+        c = lambda t: t.contiguous() if t is not None else None
+        dr = torch.zeros_like(r) if ctx.need_rays else None
+        ds = ops.composite_bwd(s, z, r, n, c(g_w), c(g_depth), c(g_opacity), c(g_var), d_rays=dr)
+        return ds, None, dr, None
+
+
+class RenderLoss(torch.autograd.Function):
+    """Fused raw2outputs + Optimizer.compute_loss lidar branch (reference optimizer.py:719-848).
+    The analytic gradient is produced in the forward kernel; backward only scales it."""
+
+    @staticmethod
+    def forward(ctx, sigma, z, rays, noise, depth_gt, cfg, n_opaque_dev, weights_lambda):
+        s_c, z_c, r_c = sigma.detach().contiguous(), z.detach().contiguous(), rays.detach().contiguous()
+        n_c = noise.detach().contiguous() if noise is not None else None
+        parts = torch.zeros(4, device=z.device, dtype=torch.float32)
+        want_grad = sigma.requires_grad or rays.requires_grad
+        out = ops.composite_loss(s_c, z_c, r_c, n_c, depth_gt.contiguous(), cfg, parts, want_grad=want_grad,
+                                 n_opaque_dev=n_opaque_dev)
+        lam_d, lam_los, n_total = weights_lambda
+        n_op = n_opaque_dev[0]                      # device scalar: no host sync
+        loss = lam_d * parts[0] / n_op + lam_los * parts[1] / n_total + parts[2] / n_op
+        ctx.save_for_backward(out["d_sigma"], out["d_rays"])
+        ctx.need_rays = rays.requires_grad
+        ctx.mark_non_differentiable(out["weights"], out["depth"], out["opacity"], out["variance"], out["js"], out["eps"])
+        return loss, out["weights"], out["depth"], out["opacity"], out["variance"], out["js"], out["eps"]
+
+    @staticmethod
+    def backward(ctx, g_loss, *unused):
+        d_sigma, d_rays = ctx.saved_tensors
+        ds = d_sigma * g_loss if d_sigma is not None else None
+        dr = d_rays * g_loss if (ctx.need_rays and d_rays is not None) else None
+        return ds, None, dr, None, None, None, None, None

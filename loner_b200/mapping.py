@@ -1,0 +1,473 @@
+"""Host-side mirror of the reference's keyframe optimiser (src/mapping/optimizer.py) and of the thin
+ray-construction slice it needs (src/common/ray_utils.py:31-60,269-322, src/mapping/keyframe.py:75-105,
+src/common/pose_utils.py:354-368), driving the sm_100a kernels.
+
+`Optimizer` keeps the reference's constructor, `iterate_optimizer`, `compute_loss` (returns the scalar
+loss tensor; side effects `_results_lidar`, `_lidar_depth_samples_fine`, `_lidar_depths_gt`,
+`_depth_eps`) and `_step_occupancy_grid`.  Differences, all performance-motivated and listed in
+DESIGN.md: rays are built on the device (no per-iteration H2D copy / D2H gradient hop), the loss is
+one fused kernel per chunk with an analytic backward, host syncs of the reference (`.item()`,
+`np.average(eps.cpu())`, isfinite/isnan asserts) are deferred to explicit accessors, and an optional
+ray-data-parallel context all-reduces the gradients over NCCL.
+"""
+import math
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+
+from . import ops
+from ._lib import LonerB200Error
+from .functional import RenderLoss
+from .models import Model, OccupancyGridModel, OccGridRaySampler, UniformRaySampler
+from .optim import FusedAdam
+
+
+class Settings(dict):
+    """Attribute-access dict (the role of reference src/common/settings.py:51 `Settings(AttrDict)`)."""
+
+    def __getattr__(self, name):
+        try:
+            v = self[name]
+        except KeyError:
+            raise AttributeError(name)
+        return Settings(v) if isinstance(v, dict) and not isinstance(v, Settings) else v
+
+    def __setattr__(self, name, value):
+        self[name] = value
+
+
+def default_settings(n_samples_train=512, log2_hashmap_size=18, ray_range=(1.0, 50.0), lidar=512, sky=64, chunk=16384,
+                     voxel_size=100, loss_selection="L1_JS", strategy="OGM", window_size=8, num_iterations=50,
+                     freeze_poses=True, n_samples_test=2048):
+    """The values of reference cfg/defaults.yaml:37-97 + cfg/model_config/default_model_config.yaml +
+    cfg/nerf_config/default_nerf_hash.yaml, as the nested structure Optimizer reads."""
+    grid = lambda T: dict(otype="HashGrid", n_levels=16, n_features_per_level=2, log2_hashmap_size=T, base_resolution=16)
+    nerf = dict(enable_view_dependence=True,
+                dir_encoding_intensity=dict(degree=4, otype="SphericalHarmonics"),
+                intensity_network=dict(activation="ReLU", n_hidden_layers=4, n_neurons=64, otype="FullyFusedMLP",
+                                       output_activation="None"),
+                pos_encoding_intensity=grid(19), pos_encoding_sigma=grid(log2_hashmap_size),
+                sigma_network=dict(activation="ReLU", n_hidden_layers=1, n_neurons=64, otype="FullyFusedMLP",
+                                   output_activation="None"))
+    model_config = dict(
+        data=dict(ray_range=list(ray_range)),
+        model=dict(num_colors=3, model_type="nerf_decoupled", nerf_config=nerf, ray_range=list(ray_range),
+                   render=dict(N_samples_train=n_samples_train, N_samples_test=n_samples_test, retraw=True, lindisp=False,
+                               perturb=1.0, white_bkgd=False, raw_noise_std=1.0, chunk=chunk, netchunk=0),
+                   occ_model=dict(voxel_size=voxel_size, lr=1e-4, N_iters_acc=10)),
+        train=dict(lrate_sigma_mlp=0.01, lrate_rgb=0.01, lrate_pose=0.001, lrate_gamma=1.0),
+        loss=dict(loss_selection=loss_selection, JS_loss=dict(min_js_score=1.0, max_js_score=10.0, alpha=1.0),
+                  decay_los_lambda=False, los_lambda=1000.0, min_los_lambda=10.0, los_lambda_decay_rate=0.001,
+                  los_lambda_decay_steps=15000, decay_depth_eps=True, depth_eps=3.0, min_depth_eps=0.5,
+                  depth_eps_decay_rate=0.95, depth_eps_decay_steps=1, depthloss_lambda=0.005))
+    sched = [dict(num_keyframes=-1, iteration_schedule=[dict(num_iterations=num_iterations, freeze_poses=freeze_poses,
+                                                              freeze_sigma_mlp=False, freeze_rgb_mlp=True)])]
+    return Settings(dict(
+        freeze_poses=False, data_prep_on_cpu=False, enabled=True, skip_pose_refinement=True,
+        num_samples=dict(lidar=lidar, sky=sky), rays_selection=dict(strategy="RANDOM"),
+        samples_selection=dict(strategy=strategy), keyframe_schedule=sched, model_config=model_config,
+        debug=dict(log_losses=False, store_ray=False, profile_optimizer=False), window_size=window_size))
+
+
+@dataclass
+class WorldCube:
+    """reference src/common/pose_utils.py:23-57."""
+    scale_factor: torch.Tensor
+    shift: torch.Tensor
+
+    def to(self, device):
+        return WorldCube(torch.as_tensor(self.scale_factor).to(device), torch.as_tensor(self.shift).to(device))
+
+
+@dataclass
+class OptimizationSettings:
+    """reference src/mapping/optimizer.py:40-59."""
+    num_iterations: int = 1
+    freeze_poses: bool = False
+    latest_kf_only: bool = False
+    freeze_sigma_mlp: bool = False
+    freeze_rgb_mlp: bool = False
+
+
+# ------------------------------------------------------------------------------------------
+# R0: pose 6-vector -> rays (kept in torch autograd; tiny)
+# ------------------------------------------------------------------------------------------
+
+def axis_angle_to_matrix(aa):
+    """pytorch3d.transforms.axis_angle_to_matrix as used by reference pose_utils.py:360."""
+    ang = torch.norm(aa, p=2, dim=-1, keepdim=True)
+    half = ang * 0.5
+    small = ang.abs() < 1e-6
+    safe = torch.where(small, torch.ones_like(ang), ang)
+    s = torch.where(small, 0.5 - ang * ang / 48, torch.sin(half) / safe)
+    q = torch.cat([torch.cos(half), aa * s], -1)
+    r, i, j, k = torch.unbind(q, -1)
+    two_s = 2.0 / (q * q).sum(-1)
+    m = torch.stack((1 - two_s * (j * j + k * k), two_s * (i * j - k * r), two_s * (i * k + j * r),
+                     two_s * (i * j + k * r), 1 - two_s * (i * i + k * k), two_s * (j * k - i * r),
+                     two_s * (i * k - j * r), two_s * (j * k + i * r), 1 - two_s * (i * i + j * j)), -1)
+    return m.reshape(q.shape[:-1] + (3, 3))
+
+
+def get_far_val(pts_o, pts_d):
+    """reference ray_utils.py:31-60 (no_nan=True): exit distance of the [-1,1]^3 cube."""
+    d = pts_d + 1e-15
+    dirs = torch.tensor([[-1.], [1.]], device=pts_o.device)
+    t = (dirs[..., None] - pts_o) / d
+    return t.clamp(min=0).max(dim=0)[0].min(dim=1)[0].unsqueeze(1)
+
+
+def build_lidar_rays(directions, distances, pose6, world_cube, ray_range, ignore_world_cube=False):
+    """reference ray_utils.py:269-322.  directions [3,n] (already index-selected), pose6 = [t, axis-angle].
+    Returns (rays [m,13], depths [m]) in cube units; differentiable w.r.t. pose6."""
+    scale, shift = world_cube.scale_factor, world_cube.shift
+    R = axis_angle_to_matrix(pose6[3:].unsqueeze(0))[0]
+    o = ((pose6[:3] + shift) / scale).tile(directions.shape[1], 1)
+    d = (R @ directions.to(R.dtype)).T
+    d = d / torch.norm(d, dim=1, keepdim=True)
+    near = ray_range[0] / scale * torch.ones_like(o[:, :1])
+    far = torch.minimum(ray_range[1] / scale * torch.ones_like(o[:, :1]), get_far_val(o, d))
+    rays = torch.cat([o, d, -d, torch.zeros_like(o[:, :2]), near, far], 1)
+    depths = distances / scale
+    if ignore_world_cube:
+        return rays, depths
+    valid = (far > (near + 1. / scale))[..., 0]
+    return rays[valid], depths[valid]
+
+
+class PoseHandle:
+    """The slice of reference src/common/pose.py the optimiser touches: a 6-vector leaf tensor."""
+
+    def __init__(self, pose6, fixed=True):
+        self._pose_tensor = pose6.detach().clone().float().requires_grad_(not fixed)
+
+    def get_pose_tensor(self):
+        return self._pose_tensor
+
+    def set_fixed(self, fixed=True):
+        self._pose_tensor.requires_grad_(not fixed)
+
+
+class LidarScanData:
+    """Duck-type of reference src/common/sensors.py LidarScan: directions [3,n], distances [n], sky_rays [3,m]."""
+
+    def __init__(self, ray_directions, distances, sky_rays=None):
+        self.ray_directions, self.distances, self.sky_rays = ray_directions, distances, sky_rays
+
+    def __len__(self):
+        return self.distances.shape[0]
+
+
+class KeyFrame:
+    """reference src/mapping/keyframe.py: owns one scan and its (optimisable) pose, builds rays."""
+
+    def __init__(self, scan: LidarScanData, pose6, gt_pose6=None, time=0.0, device="cuda"):
+        self._scan = LidarScanData(scan.ray_directions.to(device), scan.distances.to(device),
+                                   None if scan.sky_rays is None else scan.sky_rays.to(device))
+        self._pose = PoseHandle(pose6.to(device))
+        self._gt_pose = PoseHandle((gt_pose6 if gt_pose6 is not None else pose6).to(device))
+        self._time = time
+        self.is_anchored = False
+
+    def get_lidar_scan(self):
+        return self._scan
+
+    def get_lidar_pose(self):
+        return self._pose
+
+    def get_time(self):
+        return self._time
+
+    def build_lidar_rays(self, lidar_indices, ray_range, world_cube, use_gt_poses=False, ignore_world_cube=False,
+                         sky_indices=None):
+        """reference keyframe.py:75-105: lidar rays from the (differentiable) pose, sky rays with depth
+        ray_range[1]+1 from the detached pose."""
+        pose = (self._gt_pose if use_gt_poses else self._pose).get_pose_tensor()
+        s = self._scan
+        rays, depths = build_lidar_rays(s.ray_directions[:, lidar_indices], s.distances[lidar_indices], pose,
+                                        world_cube, ray_range, ignore_world_cube)
+        if sky_indices is not None:
+            sd = s.sky_rays[:, sky_indices]
+            sky_dist = torch.full((sd.shape[1],), float(ray_range[1]) + 1.0, device=sd.device)
+            srays, sdepths = build_lidar_rays(sd, sky_dist, pose.detach(), world_cube, ray_range, ignore_world_cube)
+            rays, depths = torch.cat((rays, srays)), torch.cat((depths, sdepths))
+        return rays, depths
+
+
+class RayDataParallel:
+    """Ray data-parallel context: rays shard over ranks, parameters are replicated, and
+    one NCCL all-reduce(SUM) per iteration carries {sigma-head gradient, pose gradients}; the global
+    opaque-ray count is a 4-byte all-reduce before the loss kernel.  world_size 1 is a no-op."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist = dist
+        self.group = group
+        self.enabled = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+        self.world_size = dist.get_world_size(group) if self.enabled else 1
+        self.rank = dist.get_rank(group) if self.enabled else 0
+
+    def all_reduce_(self, t):
+        if self.enabled:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+        return t
+
+    def all_reduce_grads(self, params):
+        if not self.enabled:
+            return
+        for p in params:
+            if p.grad is not None:
+                self.dist.all_reduce(p.grad, op=self.dist.ReduceOp.SUM, group=self.group)
+
+
+class Optimizer:
+    """reference src/mapping/optimizer.py:61-925 (LiDAR path).  See module docstring."""
+
+    def __init__(self, settings, calibration, world_cube, device, use_gt_poses=False, lidar_only=True,
+                 enable_sky_segmentation=True, data_parallel: Optional[RayDataParallel] = None):
+        if not lidar_only:
+            raise LonerB200Error("Optimizer: the camera/RGB path is not built yet (SURVEY 8f row f2)")
+        self._settings = settings
+        self._calibration = calibration
+        self._device = torch.device(device if not isinstance(device, int) else f"cuda:{device}")
+        if self._device.type != "cuda":
+            raise LonerB200Error("Optimizer: loner_b200 runs on CUDA devices only (no CPU fallback)")
+        self._use_gt_poses = use_gt_poses
+        self._optimization_settings = OptimizationSettings()
+        self._lidar_only = lidar_only
+        self._model_config = settings.model_config
+        self._world_cube = world_cube.to(self._device)
+        self._scale_factor = self._world_cube.scale_factor
+        self._scale_float = float(world_cube.scale_factor)
+        self._ray_range = torch.tensor(list(self._model_config.model.ray_range), dtype=torch.float32, device=self._device)
+        self._model = Model(self._model_config.model).to(self._device)
+        self._dp = data_parallel or RayDataParallel()
+        strategy = settings.samples_selection.strategy
+        if strategy == 'OGM':
+            self._occupancy_grid_model = OccupancyGridModel(self._model_config.model.occ_model).to(self._device)
+            self._occupancy_grid = self._occupancy_grid_model()
+            self._occ_grad = torch.zeros_like(self._occupancy_grid.detach())
+            self._ray_sampler = OccGridRaySampler()
+            self._ray_sampler.update_occ_grid(self._occupancy_grid.detach())
+        elif strategy == 'UNIFORM':
+            self._ray_sampler = UniformRaySampler()
+        else:
+            raise RuntimeError(f"Can't find samples_selection strategy: {strategy}")
+        self._keyframe_count = 0
+        self._global_step = 0
+        self._keyframe_schedule = settings["keyframe_schedule"]
+        self._optimizer = None
+        self._num_lidar_samples = settings.num_samples.lidar
+        self._enable_sky_segmentation = enable_sky_segmentation
+        self._results_lidar = None
+        self._eps_dev = None
+        self.losses_log = []
+
+    # -- bookkeeping mirrors --------------------------------------------------------------
+    def should_enable_lidar(self):
+        s = self._optimization_settings
+        return not s.freeze_sigma_mlp or not s.freeze_poses
+
+    def should_enable_camera(self):
+        return False
+
+    @property
+    def _depth_eps(self):
+        """reference optimizer.py:767 computes np.average(eps.cpu()) every iteration (a host sync);
+        here the device mean is read back only when somebody asks."""
+        return float(self._eps_dev.mean().item()) if self._eps_dev is not None else float("nan")
+
+    def _los_lambda(self):
+        L = self._model_config.loss
+        if L.decay_los_lambda:
+            return max(L.los_lambda * (L.los_lambda_decay_rate ** ((self._global_step + 1) / L.los_lambda_decay_steps)),
+                       L.min_los_lambda)
+        return L.los_lambda
+
+    # -- L1-L5 -----------------------------------------------------------------------------
+    def compute_loss(self, camera_samples, lidar_samples, iteration_idx, override_enables=False, tracking=False):
+        """reference optimizer.py:701-859.  One sampler + field + fused render/loss kernel per chunk."""
+        if not ((override_enables or self.should_enable_lidar()) and lidar_samples is not None):
+            print("Warning: zero loss")
+            return 0
+        L = self._model_config.loss
+        render = self._model_config.model.render
+        rays, depths = lidar_samples
+        rays = rays.reshape(-1, rays.shape[-1]).float()
+        depths = depths.reshape(-1).float().contiguous()
+        n_rays, S = rays.shape[0], render.N_samples_train
+        sel = L.loss_selection
+        if sel not in ops.LOSS_KINDS:
+            raise ValueError(f"Can't use unknown Loss {sel}")
+        if sel in ("L1_LOS", "L2_LOS") and L.decay_depth_eps:
+            fixed_eps = max(L.depth_eps * (L.depth_eps_decay_rate ** (iteration_idx / L.depth_eps_decay_steps)), L.min_depth_eps)
+        else:
+            fixed_eps = L.depth_eps
+        los_lambda = self._los_lambda()
+        rays_d = rays.detach().contiguous()
+        # global normalisers: opaque-ray count and N*S over all ranks
+        n_op = self._dp.all_reduce_(ops.count_opaque(rays_d, depths))
+        n_total = float(n_rays * S * self._dp.world_size)
+        cfg = ops.make_loss_config(sel, self._scale_float, 0.0, n_total, L.JS_loss.min_js_score, L.JS_loss.max_js_score,
+                                   L.JS_loss.alpha, L.min_depth_eps, fixed_eps, los_lambda, L.depthloss_lambda)
+        nerf = self._model.nerf_model
+        loss, outs = 0, []
+        for i in range(0, n_rays, render.chunk):
+            r_c, d_c = rays[i:i + render.chunk], depths[i:i + render.chunk]
+            z = self._ray_sampler.get_samples(r_c, S, render.perturb)
+            sigma = nerf.sigma_from_rays(r_c, z)
+            noise = torch.randn(z.shape, device=z.device) * render.raw_noise_std if render.raw_noise_std > 0 else None
+            l_c, w, depth, opac, var, js, eps = RenderLoss.apply(
+                sigma, z, r_c, noise, d_c, cfg, n_op, (L.depthloss_lambda, los_lambda, n_total))
+            loss = loss + l_c
+            outs.append((z, w, depth, opac, var, js, eps))
+        cat = (lambda k: outs[0][k]) if len(outs) == 1 else (lambda k: torch.cat([o[k] for o in outs], 0))
+        # side effects the occupancy step and callers rely on (reference optimizer.py:730-736)
+        self._results_lidar = {'samples_fine': cat(0), 'weights_fine': cat(1), 'depth_fine': cat(2),
+                               'opacity_fine': cat(3), 'variance': cat(4), 'rays': rays_d}
+        self._js_score, self._eps_dev = cat(5), cat(6)
+        self._lidar_depths_gt_cube = depths
+        return loss
+
+    @property
+    def _lidar_depth_samples_fine(self):
+        return self._results_lidar['samples_fine'] * self._scale_factor
+
+    @property
+    def _lidar_depths_gt(self):
+        return self._lidar_depths_gt_cube.reshape(-1, 1) * self._scale_factor
+
+    # -- O2 --------------------------------------------------------------------------------
+    def _step_occupancy_grid(self):
+        """reference optimizer.py:897-908: trilinear scatter of the log-odds update + SGD, then refresh the
+        sampler's grid.  @precond: compute_loss was called."""
+        res = self._results_lidar
+        D = self._occupancy_grid.shape[-1]
+        ops.occ_grad(res['rays'], res['samples_fine'], self._lidar_depths_gt_cube, self._scale_float, D,
+                     out=self._occ_grad.view(D, D, D))
+        self._dp.all_reduce_(self._occ_grad)
+        ops.sgd_step(self._occupancy_grid.data.view(-1), self._occ_grad.view(-1),
+                     self._model_config.model.occ_model.lr, zero_grad=True)
+        self._ray_sampler.update_occ_grid(self._occupancy_grid.detach())
+
+    # -- O3 + hot loop -----------------------------------------------------------------------
+    def _select_rays(self, kf):
+        """reference optimizer.py:363-387: RANDOM / MASK index draws (+ sky rays), on the device."""
+        scan = kf.get_lidar_scan()
+        n, dev = len(scan), self._device
+        strategy = self._settings.rays_selection.strategy
+        if strategy in ('RANDOM', 'FIXED'):
+            idx = torch.randint(n, (self._num_lidar_samples,), device=dev)
+        elif strategy == 'MASK':
+            n_trunk = int(self._num_lidar_samples * 0.75)
+            zc = scan.ray_directions[2, :] * scan.distances
+            mask = (0.5 < zc) & (zc < 8)
+            allidx = torch.arange(n, device=dev)
+            t_idx, o_idx = allidx[mask], allidx[~mask]
+            idx = torch.cat((t_idx[torch.randperm(len(t_idx), device=dev)[:n_trunk]],
+                             o_idx[torch.randperm(len(o_idx), device=dev)[:self._num_lidar_samples - n_trunk]]))
+        else:
+            raise RuntimeError(f"Can't find rays_selection strategy: {strategy}")
+        sky = scan.sky_rays
+        if self._settings.num_samples.sky > 0 and self._enable_sky_segmentation and sky is not None and sky.nelement() > 0:
+            sky_idx = torch.randint(0, sky.shape[1], (self._settings.num_samples.sky,), device=dev)
+        else:
+            sky_idx = None
+        return idx, sky_idx
+
+    def build_batch(self, keyframes, ignore_world_cube=False):
+        """One iteration's ray batch: per keyframe index draw + ray construction (optimizer.py:363-424)."""
+        rays, depths = [], []
+        for kf in keyframes:
+            idx, sky_idx = self._select_rays(kf)
+            r, d = kf.build_lidar_rays(idx, self._ray_range, self._world_cube, self._use_gt_poses,
+                                       ignore_world_cube=ignore_world_cube, sky_indices=sky_idx)
+            rays.append(r)
+            depths.append(d)
+        return torch.vstack(rays), torch.cat(depths)
+
+    def iterate_optimizer(self, keyframe_window: List[KeyFrame], optimizer_settings: OptimizationSettings = None):
+        """reference optimizer.py:143-190: pick the iteration schedule for this keyframe count and run it."""
+        schedule = None
+        cumulative = 0
+        for item in self._keyframe_schedule:
+            kf_count = item["num_keyframes"]
+            cumulative += kf_count
+            if kf_count == -1 or self._keyframe_count < cumulative:
+                schedule = item["iteration_schedule"]
+                break
+        if schedule is None:
+            raise LonerB200Error("keyframe_schedule has no entry for this keyframe")
+        result = self._do_iterate_optimizer(keyframe_window, schedule, optimizer_settings)
+        self._keyframe_count += 1
+        return result
+
+    def _do_iterate_optimizer(self, keyframe_window, iteration_schedule, optimizer_settings=None):
+        """reference optimizer.py:193-511 (RANDOM / MASK ray selection)."""
+        if len(keyframe_window) == 1:
+            keyframe_window[0].is_anchored = True
+        if len(iteration_schedule) > 1 and self._settings.skip_pose_refinement:
+            iteration_schedule = iteration_schedule[1:]
+        if optimizer_settings is not None:
+            iteration_schedule = [None]
+        train = self._model_config.train
+        for it_cfg in iteration_schedule:
+            if optimizer_settings is None:
+                s = self._optimization_settings
+                s.freeze_poses = it_cfg["freeze_poses"] or self._settings.freeze_poses or self._use_gt_poses
+                s.latest_kf_only = it_cfg.get("latest_kf_only", False)
+                s.freeze_rgb_mlp = it_cfg["freeze_rgb_mlp"]
+                s.freeze_sigma_mlp = it_cfg["freeze_sigma_mlp"]
+                s.num_iterations = it_cfg["num_iterations"]
+            else:
+                self._optimization_settings = optimizer_settings
+            s = self._optimization_settings
+            s.freeze_poses = s.freeze_poses or self._settings.freeze_poses or self._use_gt_poses
+            if self._settings.samples_selection.strategy == 'OGM':
+                self._ray_sampler.update_occ_grid(self._occupancy_grid.detach())
+            self._model.freeze_sigma_head(s.freeze_sigma_mlp)
+            self._model.freeze_rgb_head(True)
+            optimize_poses = not s.freeze_poses
+            active = [max(keyframe_window, key=lambda k: k.get_time())] if s.latest_kf_only else keyframe_window
+            for kf in active:
+                if not kf.is_anchored:
+                    kf.get_lidar_pose().set_fixed(not optimize_poses)
+            tracking = (not s.freeze_poses) and s.freeze_rgb_mlp and s.freeze_sigma_mlp
+            poses = [kf.get_lidar_pose().get_pose_tensor() for kf in active if not kf.is_anchored]
+            # a NEW Adam (zeroed moments) per phase, like optimizer.py:255-265
+            groups = []
+            if not tracking:
+                groups.append({'params': self._model.get_sigma_parameters(), 'lr': train.lrate_sigma_mlp})
+            if (tracking or optimize_poses) and poses:
+                groups.append({'params': poses, 'lr': train.lrate_pose})
+            self._optimizer = FusedAdam(groups)
+            gamma = train.lrate_gamma
+            all_params = [p for g in groups for p in g['params']]
+            for it_idx in range(s.num_iterations):
+                rays, depths = self.build_batch(active)
+                loss = self.compute_loss(None, (rays, depths), it_idx, tracking=tracking)
+                if self._settings.debug.log_losses:
+                    self.losses_log.append(float(loss.detach()))
+                loss.backward()
+                self._dp.all_reduce_grads(all_params)
+                self._optimizer.step()
+                if gamma != 1.0:
+                    for g in self._optimizer.param_groups:
+                        g['lr'] *= gamma
+                self._optimizer.zero_grad(set_to_none=True)
+                if self.should_enable_lidar() and self._settings.samples_selection.strategy == 'OGM' and \
+                        self._global_step % self._model_config.model.occ_model.N_iters_acc == 0:
+                    self._step_occupancy_grid()
+                self._global_step += 1
+        return None
+
+    def check_finite(self, keyframe_window):
+        """The reference raises on non-finite poses / pose gradients every iteration (optimizer.py:452-458,
+        two host syncs); here it is an explicit call."""
+        for kf in keyframe_window:
+            t = kf.get_lidar_pose().get_pose_tensor()
+            if not t.isfinite().all():
+                raise RuntimeError("Fatal: Encountered invalid pose tensor.")
+            if t.grad is not None and not t.grad.isfinite().all():
+                raise RuntimeError("Fatal: Encountered invalid gradient in pose.")

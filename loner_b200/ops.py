@@ -187,7 +187,7 @@ def make_loss_config(kind, scale_factor, n_opaque, n_total_samples, min_js_score
                       float(depthloss_lambda), float(n_opaque), float(n_total_samples))
 
 
-def composite_loss(sigma, z, rays, noise, depth_gt, cfg, loss_parts, want_grad=True):
+def composite_loss(sigma, z, rays, noise, depth_gt, cfg, loss_parts, want_grad=True, n_opaque_dev=None):
     """Fused compositing + loss (+ analytic gradient). loss_parts [4] is accumulated into.
     Returns dict(weights, depth, opacity, variance, js, eps, d_sigma, d_rays)."""
     n, s = z.shape
@@ -196,7 +196,7 @@ def composite_loss(sigma, z, rays, noise, depth_gt, cfg, loss_parts, want_grad=T
     out = dict(weights=f(n, s), depth=f(n), opacity=f(n), variance=f(n), js=f(n), eps=f(n),
                d_sigma=f(n, s) if want_grad else None, d_rays=f(n, 13) if want_grad else None)
     _lib.call("lb_composite_loss", _p(sigma, name="sigma"), _p(z, name="z"), _p(rays, name="rays"), _p(noise, name="noise"),
-              _p(depth_gt, name="depth_gt"), C.byref(cfg), n, s, _p(out["weights"]), _p(out["depth"]),
+              _p(depth_gt, name="depth_gt"), C.byref(cfg), _p(n_opaque_dev, name="n_opaque_dev"), n, s, _p(out["weights"]), _p(out["depth"]),
               _p(out["opacity"]), _p(out["variance"]), _p(out["js"]), _p(out["eps"]), _p(loss_parts, name="loss_parts"),
               _p(out["d_sigma"]), _p(out["d_rays"]), _stream())
     return out

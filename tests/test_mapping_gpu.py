@@ -1,0 +1,136 @@
+"""GPU parity of the drop-in layer (loner_b200.models / loner_b200.mapping) against golden vectors from
+the reference's own Model.forward / Optimizer.compute_loss / _step_occupancy_grid.  The reference drew
+its random numbers on the CPU generator; the tests feed those recorded tensors back by patching
+torch.rand / torch.randn for the duration of the call (same trick oracle/make_golden.py records with)."""
+import contextlib
+
+import pytest
+import torch
+
+from conftest import load_golden, golden_params
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def rel_err(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+@contextlib.contextmanager
+def replay_random(rands, randns):
+    orig = (torch.rand, torch.randn)
+    rq, nq = list(rands), list(randns)
+
+    def fake_rand(*shape, **kw):
+        t = rq.pop(0)
+        shp = tuple(shape[0]) if len(shape) == 1 and not isinstance(shape[0], int) else tuple(shape)
+        assert tuple(t.shape) == shp, f"RNG replay shape mismatch {tuple(t.shape)} vs {shp}"
+        return t.to(kw.get("device", "cpu"))
+
+    def fake_randn(*shape, **kw):
+        t = nq.pop(0)
+        return t.to(kw.get("device", "cpu"))
+    torch.rand, torch.randn = fake_rand, fake_randn
+    try:
+        yield
+    finally:
+        torch.rand, torch.randn = orig
+
+
+def make_optimizer(g):
+    from loner_b200 import mapping as M
+    sampler = g["sampler"]
+    s = M.default_settings(n_samples_train=g["n_samples"], log2_hashmap_size=g["log2_T"], ray_range=tuple(g["ray_range"]),
+                           voxel_size=g["voxel"], loss_selection=g["loss_selection"], strategy=sampler)
+    s["model_config"]["loss"]["JS_loss"]["min_js_score"] = g["min_js"]
+    s["model_config"]["loss"]["decay_depth_eps"] = False
+    opt = M.Optimizer(s, None, M.WorldCube(g["scale"], g["shift"]), DEV)
+    with torch.no_grad():
+        opt._model.nerf_model._model_sigma.params.copy_(golden_params(g).to(DEV))
+        if sampler == "OGM":
+            opt._occupancy_grid.copy_(g["occ"].to(DEV))
+    return opt, M
+
+
+@pytest.mark.parametrize("name", ["c1_ogm_l1js", "s128_ogm_l2js", "c1_uniform_l2los"])
+def test_compute_loss_and_backward_match_reference(name):
+    g = load_golden(name)
+    opt, M = make_optimizer(g)
+    # rays from the pose 6-vector through our ray builder so that the pose gradient is covered too
+    pose = g["kf_pose"].to(DEV).requires_grad_(True)
+    wc = M.WorldCube(g["scale"].to(DEV), g["shift"].to(DEV))
+    rr = torch.tensor(g["ray_range"], device=DEV)
+    rays_l, depths_l = M.build_lidar_rays(g["kf_directions"].to(DEV), g["kf_distances"].to(DEV), pose, wc, rr)
+    n_l = rays_l.shape[0]
+    assert rel_err(rays_l, g["rays"][:n_l]) < 1e-6
+    rays = torch.cat([rays_l, g["rays"][n_l:].to(DEV)])          # sky rays (detached pose in the reference)
+    rays.retain_grad()
+    depths = g["depths"].to(DEV)
+    rands = [g["u1"], g["u2"]] if g["sampler"] == "OGM" else [g["u1"]]
+    with replay_random(rands, [g["noise"]]):
+        loss = opt.compute_loss(None, (rays, depths), 0)
+    assert abs(loss.item() - g["loss"].item()) < 1e-4 * abs(g["loss"].item())
+    res = opt._results_lidar
+    if g["sampler"] == "OGM":
+        assert (res["samples_fine"].cpu() != g["z"]).float().mean().item() < 1e-3     # same bar the oracle is pinned with
+    else:
+        assert torch.equal(res["samples_fine"].cpu(), g["z"])
+    assert rel_err(res["weights_fine"], g["weights"]) < 1e-3
+    assert rel_err(res["depth_fine"], g["depth"]) < 1e-4
+    assert rel_err(res["opacity_fine"], g["opacity"]) < 1e-4
+    assert rel_err(res["variance"], g["variance"]) < 1e-3
+    assert abs(opt._depth_eps - g["depth_eps"]) < 1e-4 * g["depth_eps"]
+    loss.backward()
+    gp = opt._model.nerf_model._model_sigma.params.grad
+    assert rel_err(gp[:3072], g["mlp_grad"]) < 1e-3
+    tg = gp[3072:]
+    assert rel_err(tg[g["table_grad_idx"].to(DEV)], g["table_grad_val"]) < 1e-3
+    assert abs(tg.double().norm().item() - g["table_grad_norm"]) < 1e-3 * g["table_grad_norm"]
+    assert rel_err(rays.grad, g["rays_grad"]) < 1e-3
+    assert rel_err(pose.grad, g["pose_grad"]) < 1e-3
+    if g["sampler"] == "OGM":
+        opt._step_occupancy_grid()
+        assert rel_err(opt._occupancy_grid, g["occ_after"]) < 1e-5
+        assert rel_err(opt._occupancy_grid.detach().cpu() - g["occ"], g["occ_after"] - g["occ"]) < 1e-3
+
+
+def test_model_forward_dict_and_adjusted():
+    g = load_golden("c1_ogm_l1js")
+    opt, M = make_optimizer(g)
+    rays = g["rays"].to(DEV)
+    with replay_random([g["u1"], g["u2"]], [g["noise"]]):
+        out = opt._model(rays, opt._ray_sampler, opt._scale_factor, camera=False, return_variance=True)
+    assert set(out) == {"rgb_fine", "depth_fine", "weights_fine", "opacity_fine", "variance", "samples_fine",
+                        "points_fine", "raw_fine"}
+    assert out["points_fine"].shape == (rays.shape[0], g["n_samples"], 3) and out["raw_fine"].shape[-1] == 1
+    assert rel_err(out["depth_fine"], g["depth"]) < 1e-4 and rel_err(out["raw_fine"][..., 0], g["sigma"]) < 1e-3
+    if "adj_depth" in g:
+        opt._model.cfg["render"]["N_samples_test"] = g["n_samples"]
+        with replay_random([g["u2"]], [g["noise"]]):
+            adj = opt._model(rays, opt._ray_sampler, opt._scale_factor, testing=True, camera=False,
+                             return_variance=True, render_strategy="adjusted")
+        assert adj["depth_fine"].shape == (rays.shape[0],)
+    with pytest.raises(ValueError):
+        opt._model(rays, opt._ray_sampler, opt._scale_factor, camera=False, render_strategy="threshold")
+
+
+def test_iterate_optimizer_learns_and_updates_occupancy():
+    from loner_b200 import mapping as M, synth
+    torch.manual_seed(0)
+    kfs, scale, shift = synth.make_keyframes(2, ray_range=(1.0, 30.0), seed=3)
+    s = M.default_settings(n_samples_train=64, log2_hashmap_size=14, ray_range=(1.0, 30.0), lidar=256, sky=16,
+                           voxel_size=32, num_iterations=30, freeze_poses=False)
+    s["debug"]["log_losses"] = True
+    opt = M.Optimizer(s, None, M.WorldCube(scale, shift), DEV)
+    window = [M.KeyFrame(M.LidarScanData(k.directions, k.distances, k.sky_directions), k.pose, device=DEV) for k in kfs]
+    window[0].is_anchored = True
+    p1_before = window[1].get_lidar_pose().get_pose_tensor().detach().clone()
+    occ_before = opt._occupancy_grid.detach().clone()
+    opt.iterate_optimizer(window)
+    opt.check_finite(window)
+    assert len(opt.losses_log) == 30 and opt.losses_log[-1] < opt.losses_log[0]
+    assert (opt._occupancy_grid.detach() != occ_before).any()
+    assert (window[1].get_lidar_pose().get_pose_tensor().detach() != p1_before).any()
+    assert torch.equal(window[0].get_lidar_pose().get_pose_tensor().detach().cpu(), kfs[0].pose)
