@@ -118,15 +118,17 @@ LB_API int lb_encode_bwd(const lb_plan* plan, const float* x01, const float* tab
  * fused with xyz = o + d*z and pos01 = (xyz+1)/2 (src/models/rendering_tcnn.py:390, nerf_tcnn.py:63).
  * Point source: either (rays,z) with P = n_rays*n_samples, or x01 [P,3] when rays == NULL
  * (then n_rays = P, n_samples = 1).  params = [mlp | table] flat fp32 (tcnn layout).
- * sigma [P]; enc_save [P,32] (NULL to skip) keeps the encodings for the backward pass. */
+ * sigma [P]; enc [P,32] (required) receives the encodings: it is the hand-off between the encode and
+ * the MLP kernel and must be kept for lb_sigma_bwd. */
 LB_API int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
-                 const float* params, int n_rays, int n_samples, float* sigma, float* enc_save,
+                 const float* params, int n_rays, int n_samples, float* sigma, float* enc,
                  void* stream);
-/* Backward of the above: d_sigma [P] -> grad_params += (MLP grads, table scatter-add);
+/* Backward of the above: d_sigma [P] -> grad_params += (MLP grads, table scatter-add; NULL to skip);
  * d_rays [N,13] += (origin/direction gradients through the grid input) when non-NULL
- * (or d_x01 [P,3] when the point source is x01).  enc_save as written by lb_sigma_fwd. */
+ * (or d_x01 [P,3] when the point source is x01).  enc_inout = enc as written by lb_sigma_fwd; it is
+ * CONSUMED: on return it holds dL/d_enc. */
 LB_API int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
-                 const float* params, const float* enc_save, const float* d_sigma, int n_rays,
+                 const float* params, float* enc_inout, const float* d_sigma, int n_rays,
                  int n_samples, float* grad_params, float* d_rays, float* d_x01, void* stream);
 
 /* ---- R5/R6: compositing ------------------------------------------------------------------ */

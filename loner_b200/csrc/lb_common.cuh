@@ -52,6 +52,17 @@ int  lb_check_cuda(cudaError_t e, const char* what);
         if (_rc) return _rc;                                      \
     } while (0)
 
+// internal launchers (lb_encode.cu, lb_mlp.cu) used by the fused entry points in lb_field.cu
+int lb_launch_encode_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* table,
+                         size_t n_points, int n_samples, float* enc, cudaStream_t st);
+int lb_launch_encode_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* table,
+                         const float* d_enc, size_t n_points, int n_samples, float* grad_table, float* d_rays,
+                         float* d_x01, cudaStream_t st);
+int lb_launch_mlp_fwd(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
+                      cudaStream_t st);
+int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma, size_t n_points,
+                      float* grad_mlp, cudaStream_t st);
+
 static inline lb_level_table lb_make_level_table(const lb_plan* p) {
     lb_level_table t;
     memset(&t, 0, sizeof(t));

@@ -1,0 +1,337 @@
+// R4 (encoding half): multi-resolution hash-grid encode, forward and backward.
+//
+// Replaces tcnn.Encoding(HashGrid) / the encoding stage of tcnn.NetworkWithInputEncoding as used by
+// DecoupledNeRF (reference src/models/nerf_tcnn.py:35-40,63-72), fused with the sample-point
+// construction xyz = o + d*z (src/models/rendering_tcnn.py:390) and pos01 = (xyz+1)/2 (nerf_tcnn.py:63).
+// Grid semantics follow the published tiny-cuda-nn algorithm (oracle/tinycudann/__init__.py).
+//
+// Mapping: TWO lanes per sample point.  Lane parity selects the x-side of the cell (x or x+1), each lane
+// walks the 4 (y,z) corners of its side.  The hash uses prime 1 for x, so the two x-neighbours are adjacent
+// table entries: a warp-wide gather / reduction instruction then touches at most 16 cache lines instead of
+// 32 -- L1TEX line processing (~2 cycles per line per instruction) is what bounds these kernels, not HBM.
+// Points are ordered [ray, sample]; consecutive samples of a ray share cells on coarse levels, so the
+// backward merges equal-cell runs inside the warp with a segmented shuffle reduction before issuing
+// red.global.add.v2.f32 (warp-aggregated atomics).
+#include "lb_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 128;
+constexpr int kPointsPerBlock = kThreads / 2;
+constexpr unsigned kFull = 0xffffffffu;
+
+struct Point {
+    float x, y, z;
+};
+
+template <bool kFromRays>
+__device__ __forceinline__ Point load_point(const float* __restrict__ rays, const float* __restrict__ zv,
+                                            const float* __restrict__ x01, size_t p, int n_samples, float* z_out) {
+    Point q;
+    if (kFromRays) {
+        const size_t r = p / (size_t)n_samples;
+        const float* ray = rays + r * LB_RAY_STRIDE;
+        const float z = __ldg(zv + p);
+        // same roundings as the reference's torch ops (o + d*z, then (xyz+1)/2): at the finest level one
+        // ulp of x01 is 3 % of a cell, so the sample position must match bit for bit
+        q.x = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 0), __fmul_rn(__ldg(ray + 3), z)), 1.0f), 0.5f);
+        q.y = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 1), __fmul_rn(__ldg(ray + 4), z)), 1.0f), 0.5f);
+        q.z = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 2), __fmul_rn(__ldg(ray + 5), z)), 1.0f), 0.5f);
+        if (z_out) *z_out = z;
+    } else {
+        q.x = __ldg(x01 + 3 * p + 0);
+        q.y = __ldg(x01 + 3 * p + 1);
+        q.z = __ldg(x01 + 3 * p + 2);
+    }
+    return q;
+}
+
+// One lane's view of a level: its x-side index term, the two y / z index terms and the weights.
+struct Side {
+    uint32_t ix, iy[2], iz[2];   // additive (dense) or xor (hash) index terms
+    float wx, wy[2], wz[2];
+    uint32_t cx, cy, cz;         // cell (for run detection)
+    float fx, fy, fz;
+};
+
+__device__ __forceinline__ Side locate_side(const lb_level& L, const Point& q, int half) {
+    Side s;
+    const float px = fmaf(L.scale, q.x, 0.5f), py = fmaf(L.scale, q.y, 0.5f), pz = fmaf(L.scale, q.z, 0.5f);
+    const float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
+    s.cx = (uint32_t)(int)flx; s.cy = (uint32_t)(int)fly; s.cz = (uint32_t)(int)flz;
+    s.fx = px - flx; s.fy = py - fly; s.fz = pz - flz;
+    s.wx = half ? s.fx : 1.0f - s.fx;
+    s.wy[0] = 1.0f - s.fy; s.wy[1] = s.fy;
+    s.wz[0] = 1.0f - s.fz; s.wz[1] = s.fz;
+    const uint32_t x = s.cx + (uint32_t)half;
+    if (L.dense) {
+        s.ix = x;
+        s.iy[0] = s.cy * L.res; s.iy[1] = s.iy[0] + L.res;
+        s.iz[0] = s.cz * L.res * L.res; s.iz[1] = s.iz[0] + L.res * L.res;
+    } else {
+        s.ix = x;
+        s.iy[0] = s.cy * 2654435761u; s.iy[1] = (s.cy + 1u) * 2654435761u;
+        s.iz[0] = s.cz * 805459861u; s.iz[1] = (s.cz + 1u) * 805459861u;
+    }
+    return s;
+}
+
+__device__ __forceinline__ uint32_t side_index(const lb_level& L, const Side& s, int by, int bz) {
+    const uint32_t raw = L.dense ? (s.ix + s.iy[by] + s.iz[bz]) : (s.ix ^ s.iy[by] ^ s.iz[bz]);
+    return L.offset + (L.mask ? (raw & L.mask) : (raw % L.size));
+}
+
+// ------------------------------------------------------------------------------------------
+// forward: enc[p][2l+f] = sum over 8 corners of w_c * table[idx_c][f]
+// ------------------------------------------------------------------------------------------
+template <bool kFromRays>
+__global__ void __launch_bounds__(kThreads, 8)
+encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
+                  const float* __restrict__ x01, const float2* __restrict__ table, size_t n_points, int n_samples,
+                  float* __restrict__ enc) {
+    const int half = threadIdx.x & 1;
+    const int width = T.n_levels * LB_FEATS;
+    const size_t n_tiles = (n_points + kPointsPerBlock - 1) / kPointsPerBlock;
+    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const size_t p = tile * kPointsPerBlock + (threadIdx.x >> 1);
+        const bool valid = p < n_points;
+        float part[LB_MLP_IN];
+        Point q = {0.5f, 0.5f, 0.5f};
+        if (valid) q = load_point<kFromRays>(rays, zv, x01, p, n_samples, nullptr);
+#pragma unroll
+        for (int l = 0; l < 16; ++l) {
+            float a = 0.0f, b = 0.0f;
+            if (l < T.n_levels) {
+                const lb_level& L = T.lv[l];
+                const Side s = locate_side(L, q, half);
+                float2 v[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) v[k] = __ldg(table + side_index(L, s, k & 1, k >> 1));
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float w = s.wx * s.wy[k & 1] * s.wz[k >> 1];
+                    a = fmaf(w, v[k].x, a);
+                    b = fmaf(w, v[k].y, b);
+                }
+            }
+            part[2 * l] = a;
+            part[2 * l + 1] = b;
+        }
+        // pair exchange: the even lane finishes features 0-15, the odd lane features 16-31
+        float out[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float send = half ? part[i] : part[16 + i];
+            const float recv = __shfl_xor_sync(kFull, send, 1);
+            out[i] = (half ? part[16 + i] : part[i]) + recv;
+        }
+        if (valid) {
+            if (width == LB_MLP_IN) {
+                float4* dst = reinterpret_cast<float4*>(enc + p * LB_MLP_IN + half * 16);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) dst[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (half * 16 + i < width) enc[p * width + half * 16 + i] = out[i];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward: table scatter-add (warp-aggregated) and optional dL/dx01
+// ------------------------------------------------------------------------------------------
+constexpr int kAggMaxRuns = 12;   // aggregate when the warp's 16 points fall into <= 12 distinct cells
+
+template <bool kFromRays, bool kInputGrad>
+__global__ void __launch_bounds__(kThreads, 6)
+encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
+                  const float* __restrict__ x01, const float2* __restrict__ table, const float* __restrict__ d_enc,
+                  size_t n_points, int n_samples, float* __restrict__ grad_table, float* __restrict__ d_rays,
+                  float* __restrict__ d_x01) {
+    const int lane = threadIdx.x & 31;
+    const int half = lane & 1;
+    const int pair = lane >> 1;
+    const int width = T.n_levels * LB_FEATS;
+    const size_t n_tiles = (n_points + kPointsPerBlock - 1) / kPointsPerBlock;
+    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const size_t p = tile * kPointsPerBlock + (threadIdx.x >> 1);
+        const bool valid = p < n_points;
+        float de[LB_MLP_IN];
+        Point q = {0.5f, 0.5f, 0.5f};
+        float zval = 0.0f;
+        if (valid) {
+            q = load_point<kFromRays>(rays, zv, x01, p, n_samples, &zval);
+            if (width == LB_MLP_IN) {
+                const float4* src = reinterpret_cast<const float4*>(d_enc + p * LB_MLP_IN);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 v = __ldg(src + i);
+                    de[4 * i] = v.x; de[4 * i + 1] = v.y; de[4 * i + 2] = v.z; de[4 * i + 3] = v.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < LB_MLP_IN; ++i) de[i] = (i < width) ? __ldg(d_enc + p * width + i) : 0.0f;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < LB_MLP_IN; ++i) de[i] = 0.0f;
+        }
+        float gx = 0.0f, gy = 0.0f, gz = 0.0f;
+        bool all_distinct = false;     // once a level has 16 distinct cells, finer levels do too
+#pragma unroll
+        for (int l = 0; l < 16; ++l) {
+            if (l >= T.n_levels) continue;
+            const lb_level& L = T.lv[l];
+            const Side s = locate_side(L, q, half);
+            const float d0 = de[2 * l], d1 = de[2 * l + 1];
+            uint32_t idx[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) idx[k] = side_index(L, s, k & 1, k >> 1);
+            if (kInputGrad) {
+                float val[4], oth[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 v = __ldg(table + idx[k]);
+                    val[k] = fmaf(v.x, d0, v.y * d1);
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) oth[k] = __shfl_xor_sync(kFull, val[k], 1);
+                float tx = 0.0f;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) tx = fmaf(s.wy[k & 1] * s.wz[k >> 1], oth[k] - val[k], tx);
+                if (half) tx = 0.0f;                       // the even lane holds (x+1) - (x)
+                const float ty = s.wx * (s.wz[0] * (val[1] - val[0]) + s.wz[1] * (val[3] - val[2]));
+                const float tz = s.wx * (s.wy[0] * (val[2] - val[0]) + s.wy[1] * (val[3] - val[1]));
+                gx = fmaf(L.scale, tx, gx);
+                gy = fmaf(L.scale, ty, gy);
+                gz = fmaf(L.scale, tz, gz);
+            }
+            if (grad_table) {
+                float a[4], b[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float w = s.wx * s.wy[k & 1] * s.wz[k >> 1];
+                    a[k] = w * d0;
+                    b[k] = w * d1;
+                }
+                bool issue = valid;
+                if (!all_distinct) {
+                    // run detection over the warp's 16 points (previous point = lane - 2)
+                    const uint32_t pcx = __shfl_up_sync(kFull, s.cx, 2), pcy = __shfl_up_sync(kFull, s.cy, 2),
+                                   pcz = __shfl_up_sync(kFull, s.cz, 2);
+                    const int pvalid = __shfl_up_sync(kFull, (int)valid, 2);
+                    const bool same = (lane >= 2) && valid && pvalid && pcx == s.cx && pcy == s.cy && pcz == s.cz;
+                    const unsigned heads = __ballot_sync(kFull, !same) & 0x55555555u;
+                    const int runs = __popc(heads);
+                    if (runs == 16) {
+                        all_distinct = true;
+                    } else if (runs <= kAggMaxRuns) {
+                        // segmented suffix sum: the head point of each run collects the whole run
+                        const unsigned rest = (pair < 15) ? (heads >> (2 * pair + 2)) : 0u;
+                        const int dist = rest ? 1 + ((__ffs(rest) - 1) >> 1) : 16 - pair;   // points until the next head
+#pragma unroll
+                        for (int off = 1; off < 16; off <<= 1) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const float ta = __shfl_down_sync(kFull, a[k], 2 * off);
+                                const float tb = __shfl_down_sync(kFull, b[k], 2 * off);
+                                if (off < dist) { a[k] += ta; b[k] += tb; }
+                            }
+                        }
+                        issue = valid && !same;
+                    }
+                }
+                if (issue) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) red_add_f32x2(grad_table + 2 * (size_t)idx[k], a[k], b[k]);
+                }
+            }
+        }
+        if (kInputGrad) {
+            gx += __shfl_xor_sync(kFull, gx, 1);
+            gy += __shfl_xor_sync(kFull, gy, 1);
+            gz += __shfl_xor_sync(kFull, gz, 1);
+            if (kFromRays) {
+                // d_o += G/2, d_d += z*G/2; one set of atomics per warp when it sits inside one ray
+                const bool mine = valid && !half;
+                float v[6] = {0.5f * gx, 0.5f * gy, 0.5f * gz, 0.5f * zval * gx, 0.5f * zval * gy, 0.5f * zval * gz};
+                if (!mine) {
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) v[i] = 0.0f;
+                }
+                const unsigned long long ray = valid ? (unsigned long long)(p / (size_t)n_samples) : ~0ull;
+                const unsigned long long r0 = __shfl_sync(kFull, ray, 0);
+                const bool uniform = __all_sync(kFull, !valid || ray == r0) && (r0 != ~0ull);
+                if (uniform) {
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) v[i] = warp_sum(v[i]);
+                    if (lane == 0) {
+#pragma unroll
+                        for (int i = 0; i < 6; ++i) atomicAdd(d_rays + r0 * LB_RAY_STRIDE + i, v[i]);
+                    }
+                } else if (mine) {
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) atomicAdd(d_rays + ray * LB_RAY_STRIDE + i, v[i]);
+                }
+            } else if (valid && !half) {
+                d_x01[3 * p + 0] = gx; d_x01[3 * p + 1] = gy; d_x01[3 * p + 2] = gz;
+            }
+        }
+    }
+}
+
+int grid_for(int sm_count, size_t n_points, int blocks_per_sm) {
+    const size_t tiles = (n_points + kPointsPerBlock - 1) / kPointsPerBlock;
+    const size_t cap = (size_t)sm_count * blocks_per_sm;
+    return (int)(tiles < cap ? (tiles ? tiles : 1) : cap);
+}
+
+}  // namespace
+
+// internal launchers shared with lb_field.cu
+int lb_launch_encode_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* table,
+                         size_t n_points, int n_samples, float* enc, cudaStream_t st) {
+    const lb_level_table T = lb_make_level_table(plan);
+    const int grid = grid_for(plan->sm_count, n_points, 8);
+    const float2* tb = reinterpret_cast<const float2*>(table);
+    if (rays) encode_fwd_kernel<true><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, n_points, n_samples, enc);
+    else encode_fwd_kernel<false><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, n_points, 1, enc);
+    return lb_check_cuda(cudaGetLastError(), "encode_fwd launch");
+}
+
+int lb_launch_encode_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* table,
+                         const float* d_enc, size_t n_points, int n_samples, float* grad_table, float* d_rays,
+                         float* d_x01, cudaStream_t st) {
+    const lb_level_table T = lb_make_level_table(plan);
+    const int grid = grid_for(plan->sm_count, n_points, 6);
+    const float2* tb = reinterpret_cast<const float2*>(table);
+    const bool in_grad = (d_rays != nullptr) || (d_x01 != nullptr);
+    if (rays) {
+        if (in_grad) encode_bwd_kernel<true, true><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, d_rays, nullptr);
+        else encode_bwd_kernel<true, false><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, nullptr, nullptr);
+    } else {
+        if (in_grad) encode_bwd_kernel<false, true><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, d_x01);
+        else encode_bwd_kernel<false, false><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, nullptr);
+    }
+    return lb_check_cuda(cudaGetLastError(), "encode_bwd launch");
+}
+
+extern "C" int lb_encode_fwd(const lb_plan* plan, const float* x01, const float* table, int64_t n_points,
+                             float* enc, void* stream) {
+    LB_REQUIRE(plan && x01 && table && enc, "null pointer");
+    LB_REQUIRE(n_points >= 0, "negative size");
+    if (n_points == 0) return LB_OK;
+    return lb_launch_encode_fwd(plan, nullptr, nullptr, x01, table, (size_t)n_points, 1, enc, (cudaStream_t)stream);
+}
+
+extern "C" int lb_encode_bwd(const lb_plan* plan, const float* x01, const float* table, const float* d_enc,
+                             int64_t n_points, float* grad_table, float* d_x01, void* stream) {
+    LB_REQUIRE(plan && x01 && table && d_enc, "null pointer");
+    LB_REQUIRE(grad_table || d_x01, "nothing to compute");
+    LB_REQUIRE(n_points >= 0, "negative size");
+    if (n_points == 0) return LB_OK;
+    return lb_launch_encode_bwd(plan, nullptr, nullptr, x01, table, d_enc, (size_t)n_points, 1, grad_table, nullptr,
+                                d_x01, (cudaStream_t)stream);
+}

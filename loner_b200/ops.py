@@ -133,14 +133,17 @@ def sigma_fwd(plan, params, rays=None, z=None, x01=None, save_enc=True):
         n, s = x01.shape[0], 1
         shape = (n,)
     sigma = torch.empty(shape, device=params.device, dtype=torch.float32)
-    enc = torch.empty(n * s, plan.n_enc, device=params.device, dtype=torch.float32) if save_enc else None
+    # the encodings are the encode -> MLP hand-off, so the buffer always exists; `save_enc` only says whether
+    # the caller intends to keep it for lb_sigma_bwd
+    enc = torch.empty(n * s, plan.n_enc, device=params.device, dtype=torch.float32)
     _lib.call("lb_sigma_fwd", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
               _p(params, name="params"), n, s, _p(sigma), _p(enc), _stream())
-    return sigma, enc
+    return sigma, (enc if save_enc else None)
 
 
 def sigma_bwd(plan, params, enc, d_sigma, rays=None, z=None, x01=None, grad_params=None, d_rays=None, need_dx=False):
-    """Accumulates into grad_params / d_rays (caller zero-fills); returns d_x01 when asked."""
+    """Accumulates into grad_params / d_rays (caller zero-fills); returns d_x01 when asked.
+    `enc` is consumed (overwritten in place with dL/d_enc)."""
     if rays is not None:
         n, s = z.shape
     else:

@@ -137,7 +137,8 @@ def test_sigma_fwd_bwd_golden(name, dev, ops, O):
     assert dx.shape == (x01.shape[0], 3)
     # frozen sigma head (tracking phase): ray gradients only
     dr3 = torch.zeros(rays.shape, device=dev)
-    ops.sigma_bwd(plan, p.to(dev), enc, ds.to(dev), rays=rays, z=z, grad_params=None, d_rays=dr3)
+    _, enc3 = ops.sigma_fwd(plan, p.to(dev), rays=rays, z=z)      # sigma_bwd consumes its enc buffer
+    ops.sigma_bwd(plan, p.to(dev), enc3, ds.to(dev), rays=rays, z=z, grad_params=None, d_rays=dr3)
     assert rel_err(dr3, dr) < 1e-5
 
 
