@@ -56,9 +56,77 @@ def make_optimizer(g):
 
 @pytest.mark.parametrize("name", ["c1_ogm_l1js", "s128_ogm_l2js", "c1_uniform_l2los"])
 def test_compute_loss_and_backward_match_reference(name):
+    """Optimizer.compute_loss + backward on the golden rays (bit-identical inputs to the reference run).
+
+    Two checkers: (1) the oracle's whole pipeline on the same inputs -- sample depths must be BIT-exact
+    and every float output / gradient within north_star's 1e-3; (2) the reference's own recorded outputs
+    (golden), with the tolerance the oracle itself is pinned with in test_oracle.py: the reference's
+    sequential fp32 cumsum moves one ill-conditioned fine sample per ~1e5, which perturbs the strongly
+    cancelling MLP gradient by ~1e-3 of its max, so that one quantity gets 3e-3 against the golden."""
+    from oracle import loner_oracle as O
     g = load_golden(name)
     opt, M = make_optimizer(g)
-    # rays from the pose 6-vector through our ray builder so that the pose gradient is covered too
+    rays = g["rays"].to(DEV).requires_grad_(True)
+    depths = g["depths"].to(DEV)
+    ogm = g["sampler"] == "OGM"
+    rands = [g["u1"], g["u2"]] if ogm else [g["u1"]]
+    with replay_random(rands, [g["noise"]]):
+        loss = opt.compute_loss(None, (rays, depths), 0)
+    res = opt._results_lidar
+    loss.backward()
+    gp = opt._model.nerf_model._model_sigma.params.grad
+    tg = gp[3072:]
+
+    # (1) oracle, same inputs end to end
+    p_ref = golden_params(g).requires_grad_(True)
+    r_ref = g["rays"].clone().requires_grad_(True)
+    cfg = dict(loss_selection=g["loss_selection"], min_js_score=g["min_js"])
+    ref = O.mapping_forward(r_ref, g["depths"], p_ref, g.get("occ"), g["u1"], g.get("u2"), g["noise"], g["scale"],
+                            g["n_samples"], log2_hashmap_size=g["log2_T"], cfg=cfg, sampler=g["sampler"])
+    ref["loss"].backward()
+    assert torch.equal(res["samples_fine"].cpu(), ref["z"]), "sample depths are not bit-exact w.r.t. the oracle"
+    assert abs(loss.item() - ref["loss"].item()) < 1e-4 * abs(ref["loss"].item())
+    for k, kk in (("weights_fine", "weights"), ("depth_fine", "depth"), ("opacity_fine", "opacity"), ("variance", "variance")):
+        assert rel_err(res[k], ref[kk]) < 1e-3, k
+    assert rel_err(gp[:3072], p_ref.grad[:3072]) < 1e-3
+    assert rel_err(tg, p_ref.grad[3072:]) < 1e-3
+    assert rel_err(rays.grad, r_ref.grad) < 1e-3
+
+    # (2) the reference's own run
+    assert abs(loss.item() - g["loss"].item()) < 1e-4 * abs(g["loss"].item())
+    dz = (res["samples_fine"].cpu() - g["z"]).abs()
+    if ogm:
+        assert (dz > 1e-6).float().mean().item() < 1e-3 and dz.max().item() < 1e-3
+    else:
+        assert dz.max().item() == 0.0
+    assert rel_err(res["weights_fine"], g["weights"]) < 1e-3
+    assert rel_err(res["depth_fine"], g["depth"]) < 1e-3
+    assert rel_err(res["opacity_fine"], g["opacity"]) < 1e-3
+    assert rel_err(res["variance"], g["variance"]) < 1e-3
+    assert abs(opt._depth_eps - g["depth_eps"]) < 1e-4 * g["depth_eps"]
+    assert rel_err(gp[:3072], g["mlp_grad"]) < (3e-3 if ogm else 1e-3)
+    assert rel_err(tg[g["table_grad_idx"].to(DEV)], g["table_grad_val"]) < (5e-3 if ogm else 1e-3)
+    assert abs(tg.double().norm().item() - g["table_grad_norm"]) < 1e-3 * g["table_grad_norm"]
+    # d(loss)/d(rays) runs through the x-derivative of the finest hash levels (cells of 2e-6 cube units):
+    # it is discontinuous in z at the ulp level, so it is compared on the rays whose depths are identical
+    same = (res["samples_fine"].cpu() == g["z"]).all(1)
+    assert same.float().mean().item() > 0.3
+    assert rel_err(rays.grad.cpu()[same], g["rays_grad"][same]) < 1e-3
+    if ogm:
+        opt._step_occupancy_grid()
+        assert rel_err(opt._occupancy_grid, g["occ_after"]) < 1e-5
+        assert rel_err(opt._occupancy_grid.detach().cpu() - g["occ"], g["occ_after"] - g["occ"]) < 1e-3
+
+
+@pytest.mark.parametrize("name", ["c1_ogm_l1js", "s128_ogm_l2js", "c1_uniform_l2los"])
+def test_pose_gradient_through_device_ray_builder(name):
+    """Same step with the rays built ON THE DEVICE from the keyframe pose 6-vector (R0), so the chain
+    kernels -> d_rays -> autograd ray builder -> pose is covered.  The checker is the oracle run on the very
+    rays the device built (copied to the CPU), so depths stay bit-exact; the oracle's own ray builder and
+    pose chain are pinned against the reference in test_oracle.py::test_ray_builder_and_pose_gradient."""
+    from oracle import loner_oracle as O
+    g = load_golden(name)
+    opt, M = make_optimizer(g)
     pose = g["kf_pose"].to(DEV).requires_grad_(True)
     wc = M.WorldCube(g["scale"].to(DEV), g["shift"].to(DEV))
     rr = torch.tensor(g["ray_range"], device=DEV)
@@ -71,33 +139,25 @@ def test_compute_loss_and_backward_match_reference(name):
     rands = [g["u1"], g["u2"]] if g["sampler"] == "OGM" else [g["u1"]]
     with replay_random(rands, [g["noise"]]):
         loss = opt.compute_loss(None, (rays, depths), 0)
-    assert abs(loss.item() - g["loss"].item()) < 1e-4 * abs(g["loss"].item())
-    res = opt._results_lidar
-    if g["sampler"] == "OGM":
-        # rays come from our device-side ray builder (ulp-level differences to the CPU-built golden rays),
-        # so depths agree to rounding except the rare ill-conditioned fine sample (see test_oracle.py)
-        dz = (res["samples_fine"].cpu() - g["z"]).abs()
-        assert (dz > 1e-5).float().mean().item() < 1e-3 and dz.max().item() < 1e-2
-    else:
-        assert torch.equal(res["samples_fine"].cpu(), g["z"])
-    assert rel_err(res["weights_fine"], g["weights"]) < 1e-3
-    # 1e-3 is north_star's bar; the oracle's one ill-conditioned fine sample (test_oracle.py) moves a depth by 1.5e-4
-    assert rel_err(res["depth_fine"], g["depth"]) < 1e-3
-    assert rel_err(res["opacity_fine"], g["opacity"]) < 1e-3
-    assert rel_err(res["variance"], g["variance"]) < 1e-3
-    assert abs(opt._depth_eps - g["depth_eps"]) < 1e-4 * g["depth_eps"]
     loss.backward()
-    gp = opt._model.nerf_model._model_sigma.params.grad
-    assert rel_err(gp[:3072], g["mlp_grad"]) < 1e-3
-    tg = gp[3072:]
-    assert rel_err(tg[g["table_grad_idx"].to(DEV)], g["table_grad_val"]) < 1e-3
-    assert abs(tg.double().norm().item() - g["table_grad_norm"]) < 1e-3 * g["table_grad_norm"]
-    assert rel_err(rays.grad, g["rays_grad"]) < 1e-3
-    assert rel_err(pose.grad, g["pose_grad"]) < 1e-3
-    if g["sampler"] == "OGM":
-        opt._step_occupancy_grid()
-        assert rel_err(opt._occupancy_grid, g["occ_after"]) < 1e-5
-        assert rel_err(opt._occupancy_grid.detach().cpu() - g["occ"], g["occ_after"] - g["occ"]) < 1e-3
+    # oracle on the device-built rays; its d_rays is pushed through the device ray builder's autograd graph
+    p_ref = golden_params(g).requires_grad_(True)
+    r_ref = rays.detach().cpu().requires_grad_(True)
+    cfg = dict(loss_selection=g["loss_selection"], min_js_score=g["min_js"])
+    ref = O.mapping_forward(r_ref, g["depths"], p_ref, g.get("occ"), g["u1"], g.get("u2"), g["noise"], g["scale"],
+                            g["n_samples"], log2_hashmap_size=g["log2_T"], cfg=cfg, sampler=g["sampler"])
+    ref["loss"].backward()
+    assert torch.equal(opt._results_lidar["samples_fine"].cpu(), ref["z"])
+    assert abs(loss.item() - ref["loss"].item()) < 1e-4 * abs(ref["loss"].item())
+    assert rel_err(rays.grad, r_ref.grad) < 1e-3
+    pose2 = g["kf_pose"].to(DEV).requires_grad_(True)
+    rays_l2, _ = M.build_lidar_rays(g["kf_directions"].to(DEV), g["kf_distances"].to(DEV), pose2, wc, rr)
+    rays_l2.backward(r_ref.grad[:n_l].to(DEV))
+    assert rel_err(pose.grad, pose2.grad) < 1e-3
+    # and the reference's recorded pose gradient: same order of magnitude and direction (it is a sum of the
+    # z-chaotic ray gradients above, so only a loose bound is meaningful)
+    cos = torch.nn.functional.cosine_similarity(pose.grad.cpu().flatten(), g["pose_grad"].flatten(), dim=0).item()
+    assert cos > 0.9, cos
 
 
 def test_model_forward_dict_and_adjusted():
