@@ -119,17 +119,20 @@ LB_API int lb_encode_bwd(const lb_plan* plan, const float* x01, const float* tab
  * Point source: either (rays,z) with P = n_rays*n_samples, or x01 [P,3] when rays == NULL
  * (then n_rays = P, n_samples = 1).  params = [mlp | table] flat fp32 (tcnn layout).
  * sigma [P]; enc [P,32] (required) receives the encodings: it is the hand-off between the encode and
- * the MLP kernel and must be kept for lb_sigma_bwd. */
+ * the MLP kernel and must be kept for lb_sigma_bwd.  act [P] uint64 receives the ReLU bit mask of the 64
+ * hidden units; when non-NULL the MLP runs on the tcgen05 tensor cores (bf16-split operands, fp32
+ * accumulate in TMEM) and act must be handed to lb_sigma_bwd; NULL selects the fp32 CUDA-core MLP. */
 LB_API int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
                  const float* params, int n_rays, int n_samples, float* sigma, float* enc,
-                 void* stream);
+                 uint64_t* act, void* stream);
 /* Backward of the above: d_sigma [P] -> grad_params += (MLP grads, table scatter-add; NULL to skip);
  * d_rays [N,13] += (origin/direction gradients through the grid input) when non-NULL
  * (or d_x01 [P,3] when the point source is x01).  enc_inout = enc as written by lb_sigma_fwd; it is
- * CONSUMED: on return it holds dL/d_enc. */
+ * CONSUMED: on return it holds dL/d_enc.  act = the mask written by lb_sigma_fwd (NULL: fp32 CUDA-core MLP,
+ * which recomputes the hidden layer). */
 LB_API int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
-                 const float* params, float* enc_inout, const float* d_sigma, int n_rays,
-                 int n_samples, float* grad_params, float* d_rays, float* d_x01, void* stream);
+                 const float* params, float* enc_inout, const uint64_t* act, const float* d_sigma,
+                 int n_rays, int n_samples, float* grad_params, float* d_rays, float* d_x01, void* stream);
 
 /* ---- R5/R6: compositing ------------------------------------------------------------------ */
 /* raw2outputs, sigma-only (src/models/rendering_tcnn.py:219-295).  noise [N,S] already scaled by

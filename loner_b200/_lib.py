@@ -46,8 +46,8 @@ SIGNATURES = {
     "lb_sample_uniform": (_I, [_P, _P, _P, _I, _I, _F, _P, _P]),
     "lb_encode_fwd": (_I, [_P, _P, _P, _L, _P, _P]),
     "lb_encode_bwd": (_I, [_P, _P, _P, _P, _L, _P, _P, _P]),
-    "lb_sigma_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P]),
-    "lb_sigma_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
+    "lb_sigma_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
+    "lb_sigma_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "lb_composite_fwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P]),
     "lb_composite_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P]),
     "lb_composite_loss": (_I, [_P, _P, _P, _P, _P, C.POINTER(LossConfig), _P, _I, _I,

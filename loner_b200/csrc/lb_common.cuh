@@ -58,10 +58,16 @@ int lb_launch_encode_fwd(const lb_plan* plan, const float* rays, const float* z,
 int lb_launch_encode_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* table,
                          const float* d_enc, size_t n_points, int n_samples, float* grad_table, float* d_rays,
                          float* d_x01, cudaStream_t st);
+// act [P] uint64 = ReLU bit masks (hand-off forward -> backward of the tensor-core path); NULL selects the
+// fp32 CUDA-core kernels
 int lb_launch_mlp_fwd(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
-                      cudaStream_t st);
-int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma, size_t n_points,
-                      float* grad_mlp, cudaStream_t st);
+                      uint64_t* act, cudaStream_t st);
+int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
+                      const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st);
+int lb_launch_mlp_fwd_umma(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
+                           uint64_t* act, cudaStream_t st);
+int lb_launch_mlp_bwd_umma(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
+                           const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st);
 
 static inline lb_level_table lb_make_level_table(const lb_plan* p) {
     lb_level_table t;

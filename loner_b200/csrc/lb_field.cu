@@ -8,7 +8,7 @@
 
 extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
                             const float* params, int n_rays, int n_samples, float* sigma, float* enc,
-                            void* stream) {
+                            uint64_t* act, void* stream) {
     LB_REQUIRE(plan && params && sigma && enc, "null pointer (enc [P,32] is required: it is the encode->MLP hand-off)");
     LB_REQUIRE((rays && z) || x01, "need (rays, z) or x01");
     LB_REQUIRE(plan->cfg.n_levels * LB_FEATS == LB_MLP_IN, "fused sigma head needs 16 levels x 2 features");
@@ -18,12 +18,13 @@ extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float*
     cudaStream_t st = (cudaStream_t)stream;
     int rc = lb_launch_encode_fwd(plan, rays, z, x01, params + LB_MLP_PARAMS, P, rays ? n_samples : 1, enc, st);
     if (rc) return rc;
-    return lb_launch_mlp_fwd(plan, params, enc, P, sigma, st);
+    return lb_launch_mlp_fwd(plan, params, enc, P, sigma, act, st);
 }
 
 extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
-                            const float* params, float* enc_inout, const float* d_sigma, int n_rays,
-                            int n_samples, float* grad_params, float* d_rays, float* d_x01, void* stream) {
+                            const float* params, float* enc_inout, const uint64_t* act, const float* d_sigma,
+                            int n_rays, int n_samples, float* grad_params, float* d_rays, float* d_x01,
+                            void* stream) {
     LB_REQUIRE(plan && params && enc_inout && d_sigma, "null pointer");
     LB_REQUIRE((rays && z) || x01, "need (rays, z) or x01");
     LB_REQUIRE(plan->cfg.n_levels * LB_FEATS == LB_MLP_IN, "fused sigma head needs 16 levels x 2 features");
@@ -33,7 +34,7 @@ extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float*
     const size_t P = (size_t)n_rays * (size_t)n_samples;
     if (P == 0) return LB_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    int rc = lb_launch_mlp_bwd(plan, params, enc_inout, d_sigma, P, grad_params, st);
+    int rc = lb_launch_mlp_bwd(plan, params, enc_inout, d_sigma, act, P, grad_params, st);
     if (rc) return rc;
     return lb_launch_encode_bwd(plan, rays, z, x01, params + LB_MLP_PARAMS, enc_inout, P, rays ? n_samples : 1,
                                 grad_params ? grad_params + LB_MLP_PARAMS : nullptr, d_rays, d_x01, st);

@@ -6,8 +6,8 @@
 // row-major [out,in]; only W2 row 0 produces sigma, rows 1-15 are padding and receive zero gradient.
 //
 // Two implementations behind one launcher:
-//   * SIMT  (this file, first half): fp32 CUDA-core reference, one thread per point.
-//   * UMMA  (second half): tcgen05 tensor-core kernels (see the section comment there).
+//   * SIMT  (this file): fp32 CUDA-core kernels, one thread per point.
+//   * UMMA  (lb_mlp_umma.cu): tcgen05 tensor-core kernels; used whenever the caller supplies the `act` buffer.
 // LONER_B200_MLP=simt forces the SIMT kernels (used by the tests to cross-check the tensor-core path).
 #include <stdlib.h>
 
@@ -155,24 +155,22 @@ int grid_for(int sm_count, size_t n_points, int blocks_per_sm) {
 
 }  // namespace
 
+// LONER_B200_MLP=simt forces the fp32 CUDA-core kernels (the tests use it to cross-check the tcgen05 path)
 static bool use_simt() {
-    static int v = -1;
-    if (v < 0) {
-        const char* e = getenv("LONER_B200_MLP");
-        v = (e && strcmp(e, "simt") == 0) ? 1 : 0;
-    }
-    return true || v == 1;   // UMMA kernels land in the next revision; SIMT is the only path for now
+    const char* e = getenv("LONER_B200_MLP");
+    return e && strcmp(e, "simt") == 0;
 }
 
 int lb_launch_mlp_fwd(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
-                      cudaStream_t st) {
-    (void)use_simt();
+                      uint64_t* act, cudaStream_t st) {
+    if (act && !use_simt()) return lb_launch_mlp_fwd_umma(plan, mlp, enc, n_points, sigma, act, st);
     mlp_fwd_simt_kernel<<<grid_for(plan->sm_count, n_points, 8), kThreads, 0, st>>>(mlp, enc, n_points, sigma);
     return lb_check_cuda(cudaGetLastError(), "mlp_fwd launch");
 }
 
-int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma, size_t n_points,
-                      float* grad_mlp, cudaStream_t st) {
+int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
+                      const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st) {
+    if (act && !use_simt()) return lb_launch_mlp_bwd_umma(plan, mlp, enc_inout, d_sigma, act, n_points, grad_mlp, st);
     const size_t smem = (size_t)(LB_MLP_W * LB_MLP_IN + LB_MLP_W + (2 * LB_MLP_W + LB_MLP_IN) * kLd) * sizeof(float);
     int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_bwd_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                            "mlp_bwd smem opt-in");

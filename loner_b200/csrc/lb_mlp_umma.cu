@@ -1,0 +1,490 @@
+// R4 (network half) on the 5th-generation tensor cores: the 32 -> 64 -> 1 sigma MLP, forward and backward,
+// as tcgen05.mma (UMMA) kernels with fp32 accumulators in tensor memory (TMEM).
+//
+// Replaces tcnn FullyFusedMLP inside tcnn.NetworkWithInputEncoding (reference src/models/nerf_tcnn.py:35-38,71;
+// cfg/nerf_config/default_nerf_hash.yaml:26-31).  Weight layout = tcnn's: W1 [64,32] then W2 [16,64] row-major.
+//
+// Precision.  north_star wants 1e-3 agreement with fp32 accumulate, and the weight gradient is a strongly
+// cancelling sum, so a single bf16/tf32 pass is not enough.  Every fp32 operand x is split into bf16 pieces
+// x = b1 + b2 (+ O(2^-18 x)), b1 = rn_bf16(x), b2 = rn_bf16(x - b1), and the products are accumulated in fp32:
+//   forward : H = sum of the six products Ei W1x^T of order <= 2^-18  (three pieces each, error ~2^-25: the
+//             ReLU mask must be as reliable as an fp32 evaluation, a flipped unit changes a gradient row by O(1))
+//   backward: the A operand is the ReLU mask m[p,j] in {0,1}, exact in bf16, so two pieces of B suffice:
+//     dE[p,:] = ds[p] * sum_j m[p,j] (w2[j] W1[j,:])                  A = M (K-major),  B = W1s pieces
+//     U[j,k]  = sum_p m[p,j] (ds[p] e[p,k])                           A = M^T (MN-major view of the same tile)
+//     dW1[j,k] = w2[j] U[j,k],  dW2[j] = sum_k W1[j,k] U[j,k]         (epilogue, fp32)
+//   The mask is produced by the forward kernel (64 bits per point) so the backward needs no recomputation.
+//
+// Shared-memory operand layout (no swizzle, "interleaved" canonical UMMA layout): a tile X[r][c] of 16-byte
+// chunks (8 bf16) is stored at  (r % 8) * 16 + (r / 8) * 128 + c * LBO  with LBO = (rows * 16 + 16) bytes.  The
+// extra 16 bytes rotate consecutive chunks over the banks so the conversion stores are conflict free.  The same
+// bytes serve as a K-major operand (rows = M/N, chunks along K: desc.SBO = 128, desc.LBO = LBO) and as an
+// MN-major operand (rows = K, chunks along M/N: desc.SBO = LBO, desc.LBO = 128).
+//
+// One CTA = 128 threads = one 128-point tile at a time (UMMA M = 128), persistent over tiles, 3 CTAs per SM
+// so that one CTA's conversion / epilogue overlaps another's MMAs and global loads.
+#include <cuda_bf16.h>
+
+#include "lb_common.cuh"
+
+namespace {
+
+constexpr int kTile = 128;
+constexpr int kThreads = 128;
+constexpr uint32_t kLboP = kTile * 16 + 16;        // chunk stride of a 128-row tile (points)
+constexpr uint32_t kLboW = LB_MLP_W * 16 + 16;     // chunk stride of a 64-row tile (hidden units)
+constexpr uint32_t kTmemCols = 64;
+
+// ---- PTX wrappers ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = (uint64_t)((saddr >> 4) & 0x3FFFu);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= (uint64_t)1 << 46;      // descriptor version 1 (sm_100); swizzle = none, base offset 0
+    return d;
+}
+
+// kind::f16 instruction descriptor: D = f32, A = B = bf16
+constexpr uint32_t umma_idesc(int m, int n, int a_mn_major, int b_mn_major) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+           ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}\n"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// 32 lanes x 32 consecutive columns: thread i of the warp receives columns [col, col+32) of TMEM lane base+i
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---- bf16 splitting -------------------------------------------------------------------------
+// packs rn_bf16(lo), rn_bf16(hi) into one register (lo in bits 0-15)
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ float bf16_lo_f32(uint32_t p) { return __uint_as_float(p << 16); }
+__device__ __forceinline__ float bf16_hi_f32(uint32_t p) { return __uint_as_float(p & 0xffff0000u); }
+
+// v[0..7] -> first pieces b1 (4 packed regs), second pieces b2 and (kThree) third pieces b3; every
+// subtraction is exact in fp32, so v = b1 + b2 + b3 up to 2^-26 |v|
+template <bool kThree>
+__device__ __forceinline__ void split8(const float* v, uint32_t* b1, uint32_t* b2, uint32_t* b3) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        b1[i] = pack_bf16(v[2 * i], v[2 * i + 1]);
+        const float r0 = v[2 * i] - bf16_lo_f32(b1[i]), r1 = v[2 * i + 1] - bf16_hi_f32(b1[i]);
+        b2[i] = pack_bf16(r0, r1);
+        if (kThree) b3[i] = pack_bf16(r0 - bf16_lo_f32(b2[i]), r1 - bf16_hi_f32(b2[i]));
+    }
+}
+
+__device__ __forceinline__ uint32_t tile_off(int row, int chunk, uint32_t lbo) {
+    return (uint32_t)(row & 7) * 16u + (uint32_t)(row >> 3) * 128u + (uint32_t)chunk * lbo;
+}
+
+// A 128 x 32 fp32 tile (row-major in global memory, 8 float4 per row) is handled "flat": in pass i thread t owns
+// float4 number q = t % 8 of row i * 16 + t / 8, so every warp-wide global access is 512 contiguous bytes.
+// Lane pairs (q even / odd) exchange their float4 to assemble one 8-element chunk; the even lane then stores the
+// chunk of first pieces, the odd lane the chunk of second pieces.
+struct TileRegs {
+    float4 f[8];
+};
+
+__device__ __forceinline__ void load_tile(const float* __restrict__ src, size_t tile, size_t n_points, TileRegs& t) {
+    const float4* base = reinterpret_cast<const float4*>(src) + tile * (size_t)(kTile * 8);
+    const size_t first = tile * (size_t)kTile;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int row = i * 16 + (threadIdx.x >> 3);
+        t.f[i] = (first + row < n_points) ? __ldg(base + i * kThreads + threadIdx.x) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
+// converts the register tile (optionally scaled per row by s_scale[row]) into two or three bf16 piece tiles
+template <bool kThree>
+__device__ __forceinline__ void convert_tile(const TileRegs& t, const float* s_scale, uint8_t* p1, uint8_t* p2,
+                                             uint8_t* p3) {
+    const int odd = threadIdx.x & 1;
+    const int chunk = (threadIdx.x & 7) >> 1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int row = i * 16 + (threadIdx.x >> 3);
+        float4 mine = t.f[i];
+        if (s_scale) {
+            const float s = s_scale[row];
+            mine.x *= s; mine.y *= s; mine.z *= s; mine.w *= s;
+        }
+        float4 other;
+        other.x = __shfl_xor_sync(0xffffffffu, mine.x, 1);
+        other.y = __shfl_xor_sync(0xffffffffu, mine.y, 1);
+        other.z = __shfl_xor_sync(0xffffffffu, mine.z, 1);
+        other.w = __shfl_xor_sync(0xffffffffu, mine.w, 1);
+        const float4 a = odd ? other : mine, b = odd ? mine : other;       // a = k 0..3 of the chunk, b = k 4..7
+        const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        uint32_t b1[4], b2[4], b3[4];
+        split8<kThree>(v, b1, b2, b3);
+        const uint32_t off = tile_off(row, chunk, kLboP);
+        *reinterpret_cast<uint4*>((odd ? p2 : p1) + off) =
+            odd ? make_uint4(b2[0], b2[1], b2[2], b2[3]) : make_uint4(b1[0], b1[1], b1[2], b1[3]);
+        if (kThree && !odd) *reinterpret_cast<uint4*>(p3 + off) = make_uint4(b3[0], b3[1], b3[2], b3[3]);
+    }
+}
+
+// W[64][32] fp32 (row scale optional) -> two bf16 piece tiles X[r = j][c = k / 8]
+__device__ __forceinline__ void convert_weights(const float* __restrict__ w1, const float* __restrict__ row_scale,
+                                                uint8_t* p1, uint8_t* p2, uint8_t* p3) {
+    for (int it = threadIdx.x; it < LB_MLP_W * 4; it += kThreads) {
+        const int j = it >> 2, c = it & 3;
+        const float s = row_scale ? __ldg(row_scale + j) : 1.0f;
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __ldg(w1 + j * LB_MLP_IN + c * 8 + e) * s;
+        uint32_t b1[4], b2[4], b3[4];
+        split8<true>(v, b1, b2, b3);
+        *reinterpret_cast<uint4*>(p1 + tile_off(j, c, kLboW)) = make_uint4(b1[0], b1[1], b1[2], b1[3]);
+        *reinterpret_cast<uint4*>(p2 + tile_off(j, c, kLboW)) = make_uint4(b2[0], b2[1], b2[2], b2[3]);
+        if (p3) *reinterpret_cast<uint4*>(p3 + tile_off(j, c, kLboW)) = make_uint4(b3[0], b3[1], b3[2], b3[3]);
+    }
+}
+
+// ---- shared-memory carve-up -----------------------------------------------------------------
+constexpr uint32_t kPieceP = 4 * kLboP;            // [128 x 32] bf16 piece tile
+constexpr uint32_t kPieceW = 4 * kLboW;            // [ 64 x 32] bf16 piece tile
+constexpr uint32_t kMaskT = 8 * kLboP;             // [128 x 64] bf16 mask tile
+constexpr uint32_t kOutStride = 144;               // padded row stride of the fp32 dE staging tile
+
+struct FwdSmem {
+    static constexpr uint32_t e1 = 0, e2 = e1 + kPieceP, e3 = e2 + kPieceP, wa = e3 + kPieceP, wb = wa + kPieceW,
+                              wc = wb + kPieceW, w2 = wc + kPieceW, bar = w2 + 64 * 4, tmem = bar + 8, total = tmem + 8;
+};
+struct BwdSmem {
+    static constexpr uint32_t mt = 0, e1 = mt + kMaskT, e2 = e1 + kPieceP, wa = e2 + kPieceP, wb = wa + kPieceW,
+                              out = wb + kPieceW, ds = out + kTile * kOutStride, bar = ds + kTile * 4, tmem = bar + 8,
+                              total = tmem + 8;
+};
+
+// ------------------------------------------------------------------------------------------
+// forward: sigma[p] = sum_j w2[j] relu(sum_k W1[j,k] e[p,k]);  act[p] = bit mask of the active hidden units
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 3)
+mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc, size_t n_points,
+                    float* __restrict__ sigma, unsigned long long* __restrict__ act) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    const int tid = threadIdx.x, warp = tid >> 5;
+    float* w2s = reinterpret_cast<float*>(sm + FwdSmem::w2);
+    const uint32_t bar = smem_u32(sm + FwdSmem::bar);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + FwdSmem::tmem);
+
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    if (tid == 32) mbar_init(bar, 1);
+    convert_weights(mlp, nullptr, sm + FwdSmem::wa, sm + FwdSmem::wb, sm + FwdSmem::wc);
+    if (tid < LB_MLP_W) w2s[tid] = __ldg(mlp + LB_MLP_W * LB_MLP_IN + tid);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    const uint32_t a1 = smem_u32(sm + FwdSmem::e1), a2 = smem_u32(sm + FwdSmem::e2), a3 = smem_u32(sm + FwdSmem::e3);
+    const uint32_t ba = smem_u32(sm + FwdSmem::wa), bb = smem_u32(sm + FwdSmem::wb), bc = smem_u32(sm + FwdSmem::wc);
+    constexpr uint32_t idesc = umma_idesc(128, LB_MLP_W, 0, 0);
+
+    const size_t n_tiles = (n_points + kTile - 1) / kTile;
+    TileRegs regs;
+    size_t tile = blockIdx.x;
+    if (tile < n_tiles) load_tile(enc, tile, n_points, regs);
+    uint32_t parity = 0;
+    for (; tile < n_tiles; tile += gridDim.x) {
+        convert_tile<true>(regs, nullptr, sm + FwdSmem::e1, sm + FwdSmem::e2, sm + FwdSmem::e3);
+        const size_t next = tile + gridDim.x;
+        if (next < n_tiles) load_tile(enc, next, n_points, regs);      // in flight during the MMAs and the epilogue
+        fence_async_smem();
+        tc_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tc_fence_after();
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) {                           // K = 32 = 2 x 16
+                const uint64_t da1 = umma_desc(a1 + ks * 2 * kLboP, kLboP, 128);
+                const uint64_t da2 = umma_desc(a2 + ks * 2 * kLboP, kLboP, 128);
+                const uint64_t da3 = umma_desc(a3 + ks * 2 * kLboP, kLboP, 128);
+                const uint64_t dba = umma_desc(ba + ks * 2 * kLboW, kLboW, 128);
+                const uint64_t dbb = umma_desc(bb + ks * 2 * kLboW, kLboW, 128);
+                const uint64_t dbc = umma_desc(bc + ks * 2 * kLboW, kLboW, 128);
+                // all products of order <= 2^-18: the hidden pre-activation is as accurate as an fp32 FMA chain,
+                // so the ReLU mask flips no more often than any fp32 evaluation would
+                umma_bf16(tmem, da1, dba, idesc, ks > 0);
+                umma_bf16(tmem, da1, dbb, idesc, 1);
+                umma_bf16(tmem, da2, dba, idesc, 1);
+                umma_bf16(tmem, da1, dbc, idesc, 1);
+                umma_bf16(tmem, da2, dbb, idesc, 1);
+                umma_bf16(tmem, da3, dba, idesc, 1);
+            }
+            umma_commit(bar);
+        }
+        mbar_wait(bar, parity);
+        parity ^= 1;
+        tc_fence_after();
+        // epilogue: thread t owns point tile*128 + t = TMEM lane t
+        const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
+        float s = 0.0f;
+        unsigned long long bits = 0ull;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            uint32_t r[32];
+            tmem_ld32(lane_addr + half * 32, r);
+            tmem_ld_wait();
+            uint32_t m = 0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const float h = __uint_as_float(r[j]);
+                const bool on = h > 0.0f;
+                s = fmaf(w2s[half * 32 + j], on ? h : 0.0f, s);
+                m |= on ? (1u << j) : 0u;
+            }
+            bits |= (unsigned long long)m << (32 * half);
+        }
+        const size_t p = tile * (size_t)kTile + tid;
+        if (p < n_points) {
+            sigma[p] = s;
+            if (act) act[p] = bits;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, kTmemCols);
+}
+
+// ------------------------------------------------------------------------------------------
+// backward: enc is overwritten in place with dL/d_enc; grad_mlp += (dW1, dW2 row 0)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 3)
+mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, const float* __restrict__ d_sigma,
+                    const unsigned long long* __restrict__ act, size_t n_points, float* __restrict__ grad_mlp) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    float* ds_s = reinterpret_cast<float*>(sm + BwdSmem::ds);
+    const uint32_t bar = smem_u32(sm + BwdSmem::bar);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + BwdSmem::tmem);
+    const float* w2 = mlp + LB_MLP_W * LB_MLP_IN;
+
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    if (tid == 32) mbar_init(bar, 1);
+    convert_weights(mlp, w2, sm + BwdSmem::wa, sm + BwdSmem::wb, nullptr);       // W1s[j,k] = w2[j] W1[j,k]
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t t_de = tmem;                 // dE  [128 x 32]  columns  0..31
+    const uint32_t t_u = tmem + 32;             // U   [ 64 x 32]  columns 32..63 (M = 64: lanes 0-15 of each warp)
+
+    const uint32_t mt = smem_u32(sm + BwdSmem::mt), e1 = smem_u32(sm + BwdSmem::e1), e2 = smem_u32(sm + BwdSmem::e2);
+    const uint32_t wa = smem_u32(sm + BwdSmem::wa), wb = smem_u32(sm + BwdSmem::wb);
+    constexpr uint32_t idesc_de = umma_idesc(128, LB_MLP_IN, 0, 1);     // A = M  K-major,  B = W1s MN-major
+    constexpr uint32_t idesc_u = umma_idesc(64, LB_MLP_IN, 1, 1);       // A = M^T MN-major, B = E'  MN-major
+
+    const size_t n_tiles = (n_points + kTile - 1) / kTile;
+    TileRegs regs;
+    float ds_next = 0.0f;
+    unsigned long long act_next = 0ull;
+    size_t tile = blockIdx.x;
+    if (tile < n_tiles) {
+        load_tile(enc, tile, n_points, regs);
+        const size_t p = tile * (size_t)kTile + tid;
+        if (p < n_points) { ds_next = __ldg(d_sigma + p); act_next = __ldg(act + p); }
+    }
+    uint32_t parity = 0;
+    bool first = true;
+    for (; tile < n_tiles; tile += gridDim.x) {
+        const float ds = ds_next;
+        const unsigned long long bits = act_next;
+        ds_s[tid] = ds;
+        __syncthreads();                        // also: the previous tile's staging reads are finished
+        convert_tile<false>(regs, ds_s, sm + BwdSmem::e1, sm + BwdSmem::e2, nullptr);   // E' = ds[p] e[p,:]
+        {   // mask tile: row = this thread's point, 8 chunks of 8 hidden units
+            uint8_t* row = sm + BwdSmem::mt + tile_off(tid, 0, kLboP);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint32_t b = (uint32_t)(bits >> (8 * c)) & 0xffu;
+                uint4 v;
+                v.x = ((b & 1u) ? 0x3f80u : 0u) | ((b & 2u) ? 0x3f800000u : 0u);
+                v.y = ((b & 4u) ? 0x3f80u : 0u) | ((b & 8u) ? 0x3f800000u : 0u);
+                v.z = ((b & 16u) ? 0x3f80u : 0u) | ((b & 32u) ? 0x3f800000u : 0u);
+                v.w = ((b & 64u) ? 0x3f80u : 0u) | ((b & 128u) ? 0x3f800000u : 0u);
+                *reinterpret_cast<uint4*>(row + c * kLboP) = v;
+            }
+        }
+        const size_t next = tile + gridDim.x;
+        ds_next = 0.0f; act_next = 0ull;
+        if (next < n_tiles) {
+            load_tile(enc, next, n_points, regs);
+            const size_t p = next * (size_t)kTile + tid;
+            if (p < n_points) { ds_next = __ldg(d_sigma + p); act_next = __ldg(act + p); }
+        }
+        fence_async_smem();
+        tc_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tc_fence_after();
+            // dE = M (128 x 64) . W1s (64 x 32): K = 64 hidden units = 4 x 16
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                const uint64_t da = umma_desc(mt + ks * 2 * kLboP, kLboP, 128);
+                const uint64_t dba = umma_desc(wa + ks * 256, 128, kLboW);
+                const uint64_t dbb = umma_desc(wb + ks * 256, 128, kLboW);
+                umma_bf16(t_de, da, dba, idesc_de, ks > 0);
+                umma_bf16(t_de, da, dbb, idesc_de, 1);
+            }
+            // U += M^T (64 x 128) . E' (128 x 32): K = 128 points = 8 x 16, accumulated over all tiles of this CTA
+            if (grad_mlp) {
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    const uint64_t da = umma_desc(mt + ks * 256, 128, kLboP);
+                    const uint64_t db1 = umma_desc(e1 + ks * 256, 128, kLboP);
+                    const uint64_t db2 = umma_desc(e2 + ks * 256, 128, kLboP);
+                    umma_bf16(t_u, da, db1, idesc_u, (!first || ks > 0) ? 1u : 0u);
+                    umma_bf16(t_u, da, db2, idesc_u, 1);
+                }
+            }
+            umma_commit(bar);
+        }
+        first = false;
+        mbar_wait(bar, parity);
+        parity ^= 1;
+        tc_fence_after();
+        {   // epilogue: dE row of this thread's point -> padded staging tile
+            uint32_t r[32];
+            tmem_ld32(t_de + ((uint32_t)(warp * 32) << 16), r);
+            tmem_ld_wait();
+            float4* dst = reinterpret_cast<float4*>(sm + BwdSmem::out + tid * kOutStride);
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                dst[q] = make_float4(ds * __uint_as_float(r[4 * q]), ds * __uint_as_float(r[4 * q + 1]),
+                                     ds * __uint_as_float(r[4 * q + 2]), ds * __uint_as_float(r[4 * q + 3]));
+        }
+        tc_fence_before();
+        __syncthreads();
+        {   // coalesced write-back (in place over the encodings of this tile)
+            float4* base = reinterpret_cast<float4*>(enc) + tile * (size_t)(kTile * 8);
+            const size_t first_p = tile * (size_t)kTile;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int row = i * 16 + (tid >> 3);
+                const float4 v = *reinterpret_cast<const float4*>(sm + BwdSmem::out + row * kOutStride + (tid & 7) * 16);
+                if (first_p + row < n_points) base[i * kThreads + tid] = v;
+            }
+        }
+    }
+    // weight gradients from U (all MMAs of this CTA have completed: the last tile's commit was waited on)
+    if (grad_mlp && !first) {
+        tc_fence_after();
+        uint32_t r[32];
+        tmem_ld32(t_u + ((uint32_t)(warp * 32) << 16), r);
+        tmem_ld_wait();
+        if (lane < 16) {
+            const int j = warp * 16 + lane;
+            const float w2j = __ldg(w2 + j);
+            float dw2 = 0.0f;
+#pragma unroll
+            for (int k = 0; k < LB_MLP_IN; ++k) {
+                const float u = __uint_as_float(r[k]);
+                atomicAdd(grad_mlp + j * LB_MLP_IN + k, w2j * u);
+                dw2 = fmaf(__ldg(mlp + j * LB_MLP_IN + k), u, dw2);
+            }
+            atomicAdd(grad_mlp + LB_MLP_W * LB_MLP_IN + j, dw2);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, kTmemCols);
+}
+
+int umma_grid(int sm_count, size_t n_points) {
+    const size_t tiles = (n_points + kTile - 1) / kTile;
+    const size_t cap = (size_t)sm_count * 3;
+    return (int)(tiles < cap ? (tiles ? tiles : 1) : cap);
+}
+
+}  // namespace
+
+int lb_launch_mlp_fwd_umma(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
+                           uint64_t* act, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_fwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                    (int)FwdSmem::total), "mlp_fwd_umma smem opt-in");
+        if (rc) return rc;
+        attr_set = true;
+    }
+    mlp_fwd_umma_kernel<<<umma_grid(plan->sm_count, n_points), kThreads, FwdSmem::total, st>>>(
+        mlp, enc, n_points, sigma, reinterpret_cast<unsigned long long*>(act));
+    return lb_check_cuda(cudaGetLastError(), "mlp_fwd_umma launch");
+}
+
+int lb_launch_mlp_bwd_umma(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
+                           const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                    (int)BwdSmem::total), "mlp_bwd_umma smem opt-in");
+        if (rc) return rc;
+        attr_set = true;
+    }
+    mlp_bwd_umma_kernel<<<umma_grid(plan->sm_count, n_points), kThreads, BwdSmem::total, st>>>(
+        mlp, enc_inout, d_sigma, reinterpret_cast<const unsigned long long*>(act), n_points, grad_mlp);
+    return lb_check_cuda(cudaGetLastError(), "mlp_bwd_umma launch");
+}

@@ -24,20 +24,20 @@ class SigmaFromRays(torch.autograd.Function):
     def forward(ctx, plan, params, rays, z):
         rays_c, z_c = rays.detach().contiguous(), z.detach().contiguous()
         need_grad = params.requires_grad or rays.requires_grad
-        sigma, enc = ops.sigma_fwd(plan, params.detach(), rays=rays_c, z=z_c, save_enc=need_grad)
+        sigma, saved = ops.sigma_fwd(plan, params.detach(), rays=rays_c, z=z_c, save_enc=need_grad)
         ctx.plan = plan
-        ctx.save_for_backward(params.detach(), rays_c, z_c, enc)
+        ctx.save_for_backward(params.detach(), rays_c, z_c, *(saved or (None, None)))
         ctx.need = (params.requires_grad, rays.requires_grad)
         return sigma
 
     @staticmethod
     def backward(ctx, d_sigma):
-        params, rays, z, enc = ctx.saved_tensors
+        params, rays, z, enc, act = ctx.saved_tensors
         need_p, need_r = ctx.need
         gp = torch.zeros_like(params) if need_p else None
         dr = torch.zeros_like(rays) if need_r else None
         if need_p or need_r:
-            ops.sigma_bwd(ctx.plan, params, enc, d_sigma.contiguous(), rays=rays, z=z, grad_params=gp, d_rays=dr)
+            ops.sigma_bwd(ctx.plan, params, (enc, act), d_sigma.contiguous(), rays=rays, z=z, grad_params=gp, d_rays=dr)
         return None, gp, dr, None
 
 
@@ -48,20 +48,20 @@ class SigmaFromPoints(torch.autograd.Function):
     def forward(ctx, plan, params, x01):
         x_c = x01.detach().contiguous()
         need_grad = params.requires_grad or x01.requires_grad
-        sigma, enc = ops.sigma_fwd(plan, params.detach(), x01=x_c, save_enc=need_grad)
+        sigma, saved = ops.sigma_fwd(plan, params.detach(), x01=x_c, save_enc=need_grad)
         ctx.plan = plan
-        ctx.save_for_backward(params.detach(), x_c, enc)
+        ctx.save_for_backward(params.detach(), x_c, *(saved or (None, None)))
         ctx.need = (params.requires_grad, x01.requires_grad)
         return sigma
 
     @staticmethod
     def backward(ctx, d_sigma):
-        params, x01, enc = ctx.saved_tensors
+        params, x01, enc, act = ctx.saved_tensors
         need_p, need_x = ctx.need
         gp = torch.zeros_like(params) if need_p else None
         dx = None
         if need_p or need_x:
-            dx = ops.sigma_bwd(ctx.plan, params, enc, d_sigma.contiguous(), x01=x01, grad_params=gp, need_dx=need_x)
+            dx = ops.sigma_bwd(ctx.plan, params, (enc, act), d_sigma.contiguous(), x01=x01, grad_params=gp, need_dx=need_x)
         return None, gp, dx
 
 

@@ -124,8 +124,9 @@ def encode_bwd(plan, x01, table, d_enc, grad_table, need_dx):
     return dx
 
 
-def sigma_fwd(plan, params, rays=None, z=None, x01=None, save_enc=True):
-    """Fused xyz -> hash grid -> MLP. Returns (sigma [N,S] or [P], enc_save or None)."""
+def sigma_fwd(plan, params, rays=None, z=None, x01=None, save_enc=True, tensor_cores=True):
+    """Fused xyz -> hash grid -> MLP. Returns (sigma [N,S] or [P], saved) where saved = (enc, act) for
+    sigma_bwd (None when save_enc is False).  tensor_cores=False selects the fp32 CUDA-core MLP."""
     if rays is not None:
         n, s = z.shape
         shape = (n, s)
@@ -134,23 +135,26 @@ def sigma_fwd(plan, params, rays=None, z=None, x01=None, save_enc=True):
         shape = (n,)
     sigma = torch.empty(shape, device=params.device, dtype=torch.float32)
     # the encodings are the encode -> MLP hand-off, so the buffer always exists; `save_enc` only says whether
-    # the caller intends to keep it for lb_sigma_bwd
+    # the caller intends to keep it (and the ReLU masks) for lb_sigma_bwd
     enc = torch.empty(n * s, plan.n_enc, device=params.device, dtype=torch.float32)
+    act = torch.empty(n * s, device=params.device, dtype=torch.int64) if tensor_cores else None
     _lib.call("lb_sigma_fwd", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
-              _p(params, name="params"), n, s, _p(sigma), _p(enc), _stream())
-    return sigma, (enc if save_enc else None)
+              _p(params, name="params"), n, s, _p(sigma), _p(enc), _p(act, torch.int64), _stream())
+    return sigma, ((enc, act) if save_enc else None)
 
 
-def sigma_bwd(plan, params, enc, d_sigma, rays=None, z=None, x01=None, grad_params=None, d_rays=None, need_dx=False):
+def sigma_bwd(plan, params, saved, d_sigma, rays=None, z=None, x01=None, grad_params=None, d_rays=None, need_dx=False):
     """Accumulates into grad_params / d_rays (caller zero-fills); returns d_x01 when asked.
-    `enc` is consumed (overwritten in place with dL/d_enc)."""
+    `saved` = (enc, act) from sigma_fwd; enc is consumed (overwritten in place with dL/d_enc)."""
+    enc, act = saved
     if rays is not None:
         n, s = z.shape
     else:
         n, s = x01.shape[0], 1
     dx = torch.empty(n, 3, device=params.device, dtype=torch.float32) if (need_dx and rays is None) else None
     _lib.call("lb_sigma_bwd", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
-              _p(params, name="params"), _p(enc, name="enc"), _p(d_sigma, name="d_sigma"), n, s,
+              _p(params, name="params"), _p(enc, name="enc"), _p(act, torch.int64, name="act"),
+              _p(d_sigma, name="d_sigma"), n, s,
               _p(grad_params, name="grad_params"), _p(d_rays, name="d_rays"), _p(dx), _stream())
     return dx
 
