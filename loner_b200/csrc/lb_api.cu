@@ -57,6 +57,7 @@ extern "C" int lb_plan_create(const lb_grid_config* cfg, lb_plan** out) {
         for (int d = 0; d < 3 && stride <= params; ++d) stride *= res;
         p->levels[l].scale = scale;
         p->levels[l].res = res;
+        p->levels[l].res2 = res * res;
         p->levels[l].offset = (uint32_t)offset;
         p->levels[l].size = params;
         p->levels[l].dense = (params < stride) ? 0u : 1u;

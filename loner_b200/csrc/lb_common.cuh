@@ -16,6 +16,7 @@
 struct lb_level {
     float    scale;      // 2^(l*log2(pls)) * base - 1
     uint32_t res;        // ceil(scale) + 1
+    uint32_t res2;       // res * res (z stride of a dense level)
     uint32_t offset;     // in entries (float2)
     uint32_t size;       // entries in this level
     uint32_t dense;      // 1: x + y*res + z*res^2 ; 0: coherent prime hash

@@ -29,8 +29,8 @@ __device__ __forceinline__ Point load_point(const float* __restrict__ rays, cons
                                             const float* __restrict__ x01, size_t p, int n_samples, float* z_out) {
     Point q;
     if (kFromRays) {
-        const size_t r = p / (size_t)n_samples;
-        const float* ray = rays + r * LB_RAY_STRIDE;
+        const uint32_t r = (uint32_t)p / (uint32_t)n_samples;     // P < 2^32 (checked by the launchers)
+        const float* ray = rays + (size_t)r * LB_RAY_STRIDE;
         const float z = __ldg(zv + p);
         // same roundings as the reference's torch ops (o + d*z, then (xyz+1)/2): at the finest level one
         // ulp of x01 is 3 % of a cell, so the sample position must match bit for bit
@@ -46,12 +46,18 @@ __device__ __forceinline__ Point load_point(const float* __restrict__ rays, cons
     return q;
 }
 
-// One lane's view of a level: its x-side index term, the two y / z index terms and the weights.
+// slow path (out-of-cube points on dense levels, non-power-of-two hashed levels): kept out of line so that the
+// sixteen unrolled level bodies stay small enough for the instruction cache
+__device__ __noinline__ uint4 wrap_indices(uint4 i, uint32_t size) {
+    return make_uint4(i.x % size, i.y % size, i.z % size, i.w % size);
+}
+
+// One lane's view of a level: cell, fractional position, its x-side weight and the entry indices of its four
+// (y,z) corners (k = by + 2*bz), level offset included.
 struct Side {
-    uint32_t ix, iy[2], iz[2];   // additive (dense) or xor (hash) index terms
+    uint32_t idx[4];
     float wx, wy[2], wz[2];
     uint32_t cx, cy, cz;         // cell (for run detection)
-    float fx, fy, fz;
 };
 
 __device__ __forceinline__ Side locate_side(const lb_level& L, const Point& q, int half) {
@@ -59,26 +65,35 @@ __device__ __forceinline__ Side locate_side(const lb_level& L, const Point& q, i
     const float px = fmaf(L.scale, q.x, 0.5f), py = fmaf(L.scale, q.y, 0.5f), pz = fmaf(L.scale, q.z, 0.5f);
     const float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
     s.cx = (uint32_t)(int)flx; s.cy = (uint32_t)(int)fly; s.cz = (uint32_t)(int)flz;
-    s.fx = px - flx; s.fy = py - fly; s.fz = pz - flz;
-    s.wx = half ? s.fx : 1.0f - s.fx;
-    s.wy[0] = 1.0f - s.fy; s.wy[1] = s.fy;
-    s.wz[0] = 1.0f - s.fz; s.wz[1] = s.fz;
+    const float fx = px - flx, fy = py - fly, fz = pz - flz;
+    s.wx = half ? fx : 1.0f - fx;
+    s.wy[0] = 1.0f - fy; s.wy[1] = fy;
+    s.wz[0] = 1.0f - fz; s.wz[1] = fz;
     const uint32_t x = s.cx + (uint32_t)half;
+    bool wrap;
     if (L.dense) {
-        s.ix = x;
-        s.iy[0] = s.cy * L.res; s.iy[1] = s.iy[0] + L.res;
-        s.iz[0] = s.cz * L.res * L.res; s.iz[1] = s.iz[0] + L.res * L.res;
+        // x + y*res + z*res^2; tcnn wraps with "% size", which in-cube points never need
+        const uint32_t a0 = x + s.cy * L.res, a1 = a0 + L.res;
+        const uint32_t z0 = s.cz * L.res2, z1 = z0 + L.res2;
+        s.idx[0] = a0 + z0; s.idx[1] = a1 + z0; s.idx[2] = a0 + z1; s.idx[3] = a1 + z1;
+        wrap = s.idx[3] >= L.size || s.idx[0] >= L.size;
     } else {
-        s.ix = x;
-        s.iy[0] = s.cy * 2654435761u; s.iy[1] = (s.cy + 1u) * 2654435761u;
-        s.iz[0] = s.cz * 805459861u; s.iz[1] = (s.cz + 1u) * 805459861u;
+        const uint32_t y0 = s.cy * 2654435761u, y1 = y0 + 2654435761u;
+        const uint32_t z0 = s.cz * 805459861u, z1 = z0 + 805459861u;
+        s.idx[0] = x ^ y0 ^ z0; s.idx[1] = x ^ y1 ^ z0; s.idx[2] = x ^ y0 ^ z1; s.idx[3] = x ^ y1 ^ z1;
+        wrap = L.mask == 0u;
+        if (!wrap) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s.idx[k] &= L.mask;
+        }
     }
+    if (wrap) {
+        const uint4 w = wrap_indices(make_uint4(s.idx[0], s.idx[1], s.idx[2], s.idx[3]), L.size);
+        s.idx[0] = w.x; s.idx[1] = w.y; s.idx[2] = w.z; s.idx[3] = w.w;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s.idx[k] += L.offset;
     return s;
-}
-
-__device__ __forceinline__ uint32_t side_index(const lb_level& L, const Side& s, int by, int bz) {
-    const uint32_t raw = L.dense ? (s.ix + s.iy[by] + s.iz[bz]) : (s.ix ^ s.iy[by] ^ s.iz[bz]);
-    return L.offset + (L.mask ? (raw & L.mask) : (raw % L.size));
 }
 
 // ------------------------------------------------------------------------------------------
@@ -106,13 +121,15 @@ encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
                 const Side s = locate_side(L, q, half);
                 float2 v[4];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) v[k] = __ldg(table + side_index(L, s, k & 1, k >> 1));
+                for (int k = 0; k < 4; ++k) v[k] = __ldg(table + s.idx[k]);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const float w = s.wx * s.wy[k & 1] * s.wz[k >> 1];
+                    const float w = s.wy[k & 1] * s.wz[k >> 1];
                     a = fmaf(w, v[k].x, a);
                     b = fmaf(w, v[k].y, b);
                 }
+                a *= s.wx;
+                b *= s.wx;
             }
             part[2 * l] = a;
             part[2 * l + 1] = b;
@@ -186,9 +203,7 @@ encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
             const lb_level& L = T.lv[l];
             const Side s = locate_side(L, q, half);
             const float d0 = de[2 * l], d1 = de[2 * l + 1];
-            uint32_t idx[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) idx[k] = side_index(L, s, k & 1, k >> 1);
+            const uint32_t* idx = s.idx;
             if (kInputGrad) {
                 float val[4], oth[4];
 #pragma unroll
@@ -261,7 +276,7 @@ encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
 #pragma unroll
                     for (int i = 0; i < 6; ++i) v[i] = 0.0f;
                 }
-                const unsigned long long ray = valid ? (unsigned long long)(p / (size_t)n_samples) : ~0ull;
+                const unsigned long long ray = valid ? (unsigned long long)((uint32_t)p / (uint32_t)n_samples) : ~0ull;
                 const unsigned long long r0 = __shfl_sync(kFull, ray, 0);
                 const bool uniform = __all_sync(kFull, !valid || ray == r0) && (r0 != ~0ull);
                 if (uniform) {
@@ -321,7 +336,7 @@ int lb_launch_encode_bwd(const lb_plan* plan, const float* rays, const float* z,
 extern "C" int lb_encode_fwd(const lb_plan* plan, const float* x01, const float* table, int64_t n_points,
                              float* enc, void* stream) {
     LB_REQUIRE(plan && x01 && table && enc, "null pointer");
-    LB_REQUIRE(n_points >= 0, "negative size");
+    LB_REQUIRE(n_points >= 0 && n_points < (int64_t)1 << 32, "n_points must be in [0, 2^32)");
     if (n_points == 0) return LB_OK;
     return lb_launch_encode_fwd(plan, nullptr, nullptr, x01, table, (size_t)n_points, 1, enc, (cudaStream_t)stream);
 }
@@ -330,7 +345,7 @@ extern "C" int lb_encode_bwd(const lb_plan* plan, const float* x01, const float*
                              int64_t n_points, float* grad_table, float* d_x01, void* stream) {
     LB_REQUIRE(plan && x01 && table && d_enc, "null pointer");
     LB_REQUIRE(grad_table || d_x01, "nothing to compute");
-    LB_REQUIRE(n_points >= 0, "negative size");
+    LB_REQUIRE(n_points >= 0 && n_points < (int64_t)1 << 32, "n_points must be in [0, 2^32)");
     if (n_points == 0) return LB_OK;
     return lb_launch_encode_bwd(plan, nullptr, nullptr, x01, table, d_enc, (size_t)n_points, 1, grad_table, nullptr,
                                 d_x01, (cudaStream_t)stream);

@@ -14,6 +14,7 @@ extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float*
     LB_REQUIRE(plan->cfg.n_levels * LB_FEATS == LB_MLP_IN, "fused sigma head needs 16 levels x 2 features");
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1, "bad sizes");
     const size_t P = (size_t)n_rays * (size_t)n_samples;
+    LB_REQUIRE(P < (size_t)1 << 32, "n_rays * n_samples must be below 2^32");
     if (P == 0) return LB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     int rc = lb_launch_encode_fwd(plan, rays, z, x01, params + LB_MLP_PARAMS, P, rays ? n_samples : 1, enc, st);
@@ -32,6 +33,7 @@ extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float*
     LB_REQUIRE(grad_params || d_rays || d_x01, "nothing to compute");
     LB_REQUIRE(!(rays && d_x01) && !(!rays && d_rays), "d_rays goes with (rays, z), d_x01 with x01");
     const size_t P = (size_t)n_rays * (size_t)n_samples;
+    LB_REQUIRE(P < (size_t)1 << 32, "n_rays * n_samples must be below 2^32");
     if (P == 0) return LB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     int rc = lb_launch_mlp_bwd(plan, params, enc_inout, d_sigma, act, P, grad_params, st);
