@@ -93,6 +93,23 @@ LB_API int  lb_plan_param_counts(const lb_plan* plan, int64_t* n_mlp, int64_t* n
 LB_API int  lb_plan_level(const lb_plan* plan, int level, float* scale, uint32_t* resolution,
                    uint32_t* offset, uint32_t* size, int32_t* is_dense);
 
+/* ---- R0: ray construction ---------------------------------------------------------------- */
+/* LidarRayDirections.build_lidar_rays (src/common/ray_utils.py:269-322) incl. get_far_val (ray_utils.py:31-60)
+ * and the index selection of src/mapping/optimizer.py:389-400, as called by KeyFrame.build_lidar_rays
+ * (src/mapping/keyframe.py:75-105).  directions [3,n]; distances [n] in metres (NULL: every depth is
+ * const_depth, the sky-ray case of keyframe.py:96-98); indices [m] int64 (NULL: identity, m <= n);
+ * rot [9] = row-major R of the lidar pose, origin [3] = (t + shift) / scale (device pointers, computed by the
+ * host from the pose 6-vector); near = r0/scale, far_max = r1/scale, inv_scale = 1/scale.
+ * Outputs rays [m,13] = [o, d, -d, 0, 0, near, min(far_max, cube exit)], depths [m] in cube units. */
+LB_API int lb_build_lidar_rays(const float* directions, const float* distances, const int64_t* indices, int n,
+                        int m, const float* rot, const float* origin, float near, float far_max,
+                        float inv_scale, float const_depth, float* rays, float* depths, void* stream);
+/* its backward: d_rays [m,13] -> d_rot [9] += , d_origin [3] +=  (the pose chain rule R(axis-angle), o(t)
+ * of src/common/pose_utils.py:354-368 stays with the host's autograd). */
+LB_API int lb_build_lidar_rays_bwd(const float* directions, const int64_t* indices, int n, int m,
+                            const float* rot, const float* origin, float far_max, const float* d_rays,
+                            float* d_rot, float* d_origin, void* stream);
+
 /* ---- R2: sampling ------------------------------------------------------------------------ */
 /* OccGridRaySampler.get_samples (src/models/ray_sampling.py:53-92) incl. OccupancyGridModel.interpolate
  * (src/models/model_tcnn.py:126-134) and sample_pdf (src/models/rendering_tcnn.py:19-68).

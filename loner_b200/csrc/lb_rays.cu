@@ -1,0 +1,171 @@
+// R0: LiDAR ray construction on the device, forward and backward.
+//
+// Replaces LidarRayDirections.build_lidar_rays (reference src/common/ray_utils.py:269-322) with get_far_val
+// (ray_utils.py:31-60) as called by KeyFrame.build_lidar_rays (src/mapping/keyframe.py:75-105), fused with the
+// index selection directions[:, idx] / distances[idx] (src/mapping/optimizer.py:389-400).  The pose enters as
+// the rotation matrix R [3,3] and the ray origin o = (t + shift) / scale [3], both tiny device tensors that the
+// host computes from the pose 6-vector with autograd (pose_utils.py:354-368), so the chain rule to the pose
+// stays in PyTorch while the per-ray work (and its reduction to dL/dR, dL/do) runs here.
+//
+//   u = R dir;  d = u / |u|;  near = r0 / s;  far = min(r1 / s, exit(o, d))
+//   exit(o, d) = min_axis max(clamp((-1 - o_a) / (d_a + 1e-15), 0), clamp((1 - o_a) / (d_a + 1e-15), 0))
+//   rays[i] = [o, d, -d, 0, 0, near, far];  depths[i] = distance / s
+#include "lb_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+struct Pose {
+    float r[9], o[3];
+};
+
+__device__ __forceinline__ Pose load_pose(const float* __restrict__ rot, const float* __restrict__ origin) {
+    Pose p;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) p.r[i] = __ldg(rot + i);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) p.o[i] = __ldg(origin + i);
+    return p;
+}
+
+struct RayGeom {
+    float u[3], inv_norm, d[3];
+    float exit_t;      // cube exit distance
+    int exit_axis;     // axis whose slab gives the exit, -1 when the clamp at 0 is active
+    float exit_den;    // d_a + 1e-15 of that axis
+};
+
+__device__ __forceinline__ RayGeom ray_geometry(const Pose& p, float dx, float dy, float dz) {
+    RayGeom g;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) g.u[a] = p.r[3 * a] * dx + p.r[3 * a + 1] * dy + p.r[3 * a + 2] * dz;
+    const float n = sqrtf(g.u[0] * g.u[0] + g.u[1] * g.u[1] + g.u[2] * g.u[2]);
+    g.inv_norm = 1.0f / n;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) g.d[a] = g.u[a] / n;
+    g.exit_t = 3.402823466e38f;
+    g.exit_axis = -1;
+    g.exit_den = 1.0f;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float den = g.d[a] + 1e-15f;
+        const float t0 = (-1.0f - p.o[a]) / den, t1 = (1.0f - p.o[a]) / den;
+        const float m = fmaxf(fmaxf(t0, 0.0f), fmaxf(t1, 0.0f));
+        if (m < g.exit_t) {
+            g.exit_t = m;
+            g.exit_axis = (m > 0.0f) ? a : -1;
+            g.exit_den = den;
+        }
+    }
+    return g;
+}
+
+__global__ void __launch_bounds__(kThreads)
+build_rays_kernel(const float* __restrict__ directions, const float* __restrict__ distances,
+                  const long long* __restrict__ indices, int n, int m, const float* __restrict__ rot,
+                  const float* __restrict__ origin, float near, float far_max, float inv_scale, float const_depth,
+                  float* __restrict__ rays, float* __restrict__ depths) {
+    const int i = blockIdx.x * kThreads + threadIdx.x;
+    if (i >= m) return;
+    const Pose p = load_pose(rot, origin);
+    long long j = indices ? indices[i] : (long long)i;
+    if (j < 0) j += n;                                   // torch-style negative index
+    const float dx = __ldg(directions + j), dy = __ldg(directions + (size_t)n + j), dz = __ldg(directions + 2 * (size_t)n + j);
+    const RayGeom g = ray_geometry(p, dx, dy, dz);
+    float* r = rays + (size_t)i * LB_RAY_STRIDE;
+    r[0] = p.o[0]; r[1] = p.o[1]; r[2] = p.o[2];
+    r[3] = g.d[0]; r[4] = g.d[1]; r[5] = g.d[2];
+    r[6] = -g.d[0]; r[7] = -g.d[1]; r[8] = -g.d[2];
+    r[9] = 0.0f; r[10] = 0.0f;
+    r[11] = near;
+    r[12] = fminf(far_max, g.exit_t);
+    depths[i] = distances ? __ldg(distances + j) * inv_scale : const_depth;
+}
+
+// d_rot [9] += sum_i g_u (x) dir_i,  d_origin [3] += sum_i (g_o + far term)
+__global__ void __launch_bounds__(kThreads)
+build_rays_bwd_kernel(const float* __restrict__ directions, const long long* __restrict__ indices, int n, int m,
+                      const float* __restrict__ rot, const float* __restrict__ origin, float far_max,
+                      const float* __restrict__ d_rays, float* __restrict__ d_rot, float* __restrict__ d_origin) {
+    __shared__ float red[kThreads / 32][12];
+    const Pose p = load_pose(rot, origin);
+    float acc[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) acc[k] = 0.0f;
+    for (int i = blockIdx.x * kThreads + threadIdx.x; i < m; i += gridDim.x * kThreads) {
+        long long j = indices ? indices[i] : (long long)i;
+        if (j < 0) j += n;
+        const float dir[3] = {__ldg(directions + j), __ldg(directions + (size_t)n + j), __ldg(directions + 2 * (size_t)n + j)};
+        const RayGeom g = ray_geometry(p, dir[0], dir[1], dir[2]);
+        const float* gr = d_rays + (size_t)i * LB_RAY_STRIDE;
+        float go[3], gd[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            go[a] = __ldg(gr + a);
+            gd[a] = __ldg(gr + 3 + a) - __ldg(gr + 6 + a);       // view direction = -d
+        }
+        const float gfar = __ldg(gr + 12);
+        if (g.exit_t < far_max && g.exit_axis >= 0) {            // far = exit(o, d): (+-1 - o_a) / (d_a + eps)
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                if (a == g.exit_axis) {
+                    go[a] -= gfar / g.exit_den;
+                    gd[a] -= gfar * g.exit_t / g.exit_den;
+                }
+            }
+        }
+        const float dot = g.d[0] * gd[0] + g.d[1] * gd[1] + g.d[2] * gd[2];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float gu = (gd[a] - g.d[a] * dot) * g.inv_norm;
+            acc[3 * a] = fmaf(gu, dir[0], acc[3 * a]);
+            acc[3 * a + 1] = fmaf(gu, dir[1], acc[3 * a + 1]);
+            acc[3 * a + 2] = fmaf(gu, dir[2], acc[3 * a + 2]);
+            acc[9 + a] += go[a];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) acc[k] = warp_sum(acc[k]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) red[warp][k] = acc[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        float t = 0.0f;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) t += red[w][threadIdx.x];
+        atomicAdd(threadIdx.x < 9 ? d_rot + threadIdx.x : d_origin + (threadIdx.x - 9), t);
+    }
+}
+
+}  // namespace
+
+extern "C" int lb_build_lidar_rays(const float* directions, const float* distances, const int64_t* indices, int n,
+                                   int m, const float* rot, const float* origin, float near, float far_max,
+                                   float inv_scale, float const_depth, float* rays, float* depths, void* stream) {
+    LB_REQUIRE(directions && rot && origin && rays && depths, "null pointer");
+    LB_REQUIRE(n > 0 && m >= 0, "bad sizes");
+    if (m == 0) return LB_OK;
+    build_rays_kernel<<<(m + kThreads - 1) / kThreads, kThreads, 0, (cudaStream_t)stream>>>(
+        directions, distances, reinterpret_cast<const long long*>(indices), n, m, rot, origin, near, far_max, inv_scale,
+        const_depth, rays, depths);
+    LB_LAUNCH_CHECK("lb_build_lidar_rays");
+    return LB_OK;
+}
+
+extern "C" int lb_build_lidar_rays_bwd(const float* directions, const int64_t* indices, int n, int m,
+                                       const float* rot, const float* origin, float far_max, const float* d_rays,
+                                       float* d_rot, float* d_origin, void* stream) {
+    LB_REQUIRE(directions && rot && origin && d_rays && d_rot && d_origin, "null pointer");
+    LB_REQUIRE(n > 0 && m >= 0, "bad sizes");
+    if (m == 0) return LB_OK;
+    int blocks = (m + kThreads - 1) / kThreads;
+    if (blocks > 148) blocks = 148;
+    build_rays_bwd_kernel<<<blocks, kThreads, 0, (cudaStream_t)stream>>>(
+        directions, reinterpret_cast<const long long*>(indices), n, m, rot, origin, far_max, d_rays, d_rot, d_origin);
+    LB_LAUNCH_CHECK("lb_build_lidar_rays_bwd");
+    return LB_OK;
+}

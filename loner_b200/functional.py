@@ -17,6 +17,29 @@ def _zeros_like_flat(t):
     return torch.zeros(t.numel(), device=t.device, dtype=torch.float32)
 
 
+class BuildLidarRays(torch.autograd.Function):
+    """R0 (reference ray_utils.py:269-322): rays from the pose's rotation matrix and origin; differentiable
+    w.r.t. rot [3,3] and origin [3] so that autograd carries the gradient on to the pose 6-vector."""
+
+    @staticmethod
+    def forward(ctx, rot, origin, directions, distances, indices, near, far_max, inv_scale, const_depth):
+        rot_c, org_c = rot.detach().contiguous(), origin.detach().contiguous()
+        rays, depths = ops.build_lidar_rays(directions, distances, indices, rot_c, org_c, near, far_max, inv_scale,
+                                            const_depth)
+        ctx.save_for_backward(rot_c, org_c, directions, indices)
+        ctx.far_max = far_max
+        ctx.mark_non_differentiable(depths)
+        return rays, depths
+
+    @staticmethod
+    def backward(ctx, d_rays, _d_depths):
+        rot, origin, directions, indices = ctx.saved_tensors
+        d_rot = torch.zeros(3, 3, device=rot.device, dtype=torch.float32)
+        d_org = torch.zeros(3, device=rot.device, dtype=torch.float32)
+        ops.build_lidar_rays_bwd(directions, indices, rot, origin, ctx.far_max, d_rays.contiguous(), d_rot, d_org)
+        return d_rot, d_org, None, None, None, None, None, None, None
+
+
 class SigmaFromRays(torch.autograd.Function):
     """Fused xyz=o+d*z -> hash grid -> 32-64-1 MLP (reference rendering_tcnn.py:390-392, nerf_tcnn.py:63-72)."""
 

@@ -18,7 +18,7 @@ import torch
 
 from . import ops
 from ._lib import LonerB200Error
-from .functional import RenderLoss
+from .functional import BuildLidarRays, RenderLoss
 from .models import Model, OccupancyGridModel, OccGridRaySampler, UniformRaySampler
 from .optim import FusedAdam
 
@@ -77,7 +77,16 @@ class WorldCube:
     shift: torch.Tensor
 
     def to(self, device):
-        return WorldCube(torch.as_tensor(self.scale_factor).to(device), torch.as_tensor(self.shift).to(device))
+        wc = WorldCube(torch.as_tensor(self.scale_factor).to(device), torch.as_tensor(self.shift).to(device))
+        wc._scale_host = self.scale_host
+        return wc
+
+    @property
+    def scale_host(self):
+        """scale_factor as a Python float, read back from the device once (kernel launch parameters)."""
+        if getattr(self, "_scale_host", None) is None:
+            self._scale_host = float(torch.as_tensor(self.scale_factor).reshape(-1)[0])
+        return self._scale_host
 
 
 @dataclass
@@ -118,21 +127,39 @@ def get_far_val(pts_o, pts_d):
     return t.clamp(min=0).max(dim=0)[0].min(dim=1)[0].unsqueeze(1)
 
 
-def build_lidar_rays(directions, distances, pose6, world_cube, ray_range, ignore_world_cube=False):
-    """reference ray_utils.py:269-322.  directions [3,n] (already index-selected), pose6 = [t, axis-angle].
-    Returns (rays [m,13], depths [m]) in cube units; differentiable w.r.t. pose6."""
-    scale, shift = world_cube.scale_factor, world_cube.shift
-    R = axis_angle_to_matrix(pose6[3:].unsqueeze(0))[0]
-    o = ((pose6[:3] + shift) / scale).tile(directions.shape[1], 1)
-    d = (R @ directions.to(R.dtype)).T
-    d = d / torch.norm(d, dim=1, keepdim=True)
-    near = ray_range[0] / scale * torch.ones_like(o[:, :1])
-    far = torch.minimum(ray_range[1] / scale * torch.ones_like(o[:, :1]), get_far_val(o, d))
-    rays = torch.cat([o, d, -d, torch.zeros_like(o[:, :2]), near, far], 1)
-    depths = distances / scale
+def _range_host(ray_range):
+    if torch.is_tensor(ray_range):
+        ray_range = ray_range.tolist()
+    return float(ray_range[0]), float(ray_range[1])
+
+
+def pose_to_rot_origin(pose6, world_cube):
+    """pose 6-vectors [..., 6] = [t, axis-angle] -> (R [..., 3, 3], ray origin (t + shift) / scale [..., 3]);
+    reference pose_utils.py:354-368 + ray_utils.py:293-296.  Differentiable; batched over keyframes."""
+    R = axis_angle_to_matrix(pose6[..., 3:])
+    o = (pose6[..., :3] + world_cube.shift) / world_cube.scale_factor
+    return R.float(), o.float()
+
+
+def build_lidar_rays(directions, distances, pose6, world_cube, ray_range, ignore_world_cube=False, indices=None,
+                     const_depth=None, rot_origin=None):
+    """reference ray_utils.py:269-322.  directions [3,n], distances [n] (metres), pose6 = [t, axis-angle].
+    `indices` (int64 [m]) fuses the reference's directions[:, idx] / distances[idx] selection into the kernel;
+    `const_depth` (metres) replaces the distances (sky rays, keyframe.py:96-98).
+    Returns (rays [m,13], depths [m]) in cube units; differentiable w.r.t. pose6: the rotation matrix and the
+    origin are formed here with autograd (6 numbers), the per-ray work runs in lb_build_lidar_rays."""
+    if not directions.is_cuda:
+        raise LonerB200Error("build_lidar_rays: directions must be a CUDA tensor (no CPU path)")
+    s_host = world_cube.scale_host
+    r0, r1 = _range_host(ray_range)
+    R, o = rot_origin if rot_origin is not None else pose_to_rot_origin(pose6, world_cube)
+    dist = None if const_depth is not None else distances.float().contiguous()
+    rays, depths = BuildLidarRays.apply(R, o.reshape(3), directions.float().contiguous(), dist,
+                                        indices, r0 / s_host, r1 / s_host, 1.0 / s_host,
+                                        0.0 if const_depth is None else const_depth / s_host)
     if ignore_world_cube:
         return rays, depths
-    valid = (far > (near + 1. / scale))[..., 0]
+    valid = rays[:, 12] > (r0 / s_host + 1. / s_host)
     return rays[valid], depths[valid]
 
 
@@ -180,17 +207,18 @@ class KeyFrame:
         return self._time
 
     def build_lidar_rays(self, lidar_indices, ray_range, world_cube, use_gt_poses=False, ignore_world_cube=False,
-                         sky_indices=None):
+                         sky_indices=None, rot_origin=None):
         """reference keyframe.py:75-105: lidar rays from the (differentiable) pose, sky rays with depth
         ray_range[1]+1 from the detached pose."""
         pose = (self._gt_pose if use_gt_poses else self._pose).get_pose_tensor()
         s = self._scan
-        rays, depths = build_lidar_rays(s.ray_directions[:, lidar_indices], s.distances[lidar_indices], pose,
-                                        world_cube, ray_range, ignore_world_cube)
+        rays, depths = build_lidar_rays(s.ray_directions, s.distances, pose, world_cube, ray_range, ignore_world_cube,
+                                        indices=lidar_indices, rot_origin=rot_origin)
         if sky_indices is not None:
-            sd = s.sky_rays[:, sky_indices]
-            sky_dist = torch.full((sd.shape[1],), float(ray_range[1]) + 1.0, device=sd.device)
-            srays, sdepths = build_lidar_rays(sd, sky_dist, pose.detach(), world_cube, ray_range, ignore_world_cube)
+            sky_ro = None if rot_origin is None else (rot_origin[0].detach(), rot_origin[1].detach())
+            srays, sdepths = build_lidar_rays(s.sky_rays, None, pose.detach(), world_cube, ray_range,
+                                              ignore_world_cube, indices=sky_indices,
+                                              const_depth=_range_host(ray_range)[1] + 1.0, rot_origin=sky_ro)
             rays, depths = torch.cat((rays, srays)), torch.cat((depths, sdepths))
         return rays, depths
 
@@ -240,7 +268,8 @@ class Optimizer:
         self._world_cube = world_cube.to(self._device)
         self._scale_factor = self._world_cube.scale_factor
         self._scale_float = float(world_cube.scale_factor)
-        self._ray_range = torch.tensor(list(self._model_config.model.ray_range), dtype=torch.float32, device=self._device)
+        # host tuple: launch parameters of the ray builder (a device tensor would cost a sync per keyframe)
+        self._ray_range = tuple(float(v) for v in self._model_config.model.ray_range)
         self._model = Model(self._model_config.model).to(self._device)
         self._dp = data_parallel or RayDataParallel()
         strategy = settings.samples_selection.strategy
@@ -379,10 +408,14 @@ class Optimizer:
     def build_batch(self, keyframes, ignore_world_cube=False):
         """One iteration's ray batch: per keyframe index draw + ray construction (optimizer.py:363-424)."""
         rays, depths = [], []
-        for kf in keyframes:
+        # one batched pose -> (R, origin) evaluation for the whole window (autograd reaches every pose leaf)
+        poses = torch.stack([(kf._gt_pose if self._use_gt_poses else kf._pose).get_pose_tensor() for kf in keyframes])
+        R, o = pose_to_rot_origin(poses, self._world_cube)
+        for k, kf in enumerate(keyframes):
             idx, sky_idx = self._select_rays(kf)
             r, d = kf.build_lidar_rays(idx, self._ray_range, self._world_cube, self._use_gt_poses,
-                                       ignore_world_cube=ignore_world_cube, sky_indices=sky_idx)
+                                       ignore_world_cube=ignore_world_cube, sky_indices=sky_idx,
+                                       rot_origin=(R[k], o[k]))
             rays.append(r)
             depths.append(d)
         return torch.vstack(rays), torch.cat(depths)

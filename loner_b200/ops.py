@@ -78,6 +78,30 @@ class Plan:
 _T_STEPS = {}
 
 
+def build_lidar_rays(directions, distances, indices, rot, origin, near, far_max, inv_scale, const_depth=0.0,
+                     out_rays=None, out_depths=None):
+    """R0 forward.  directions [3,n]; distances [n] or None (constant depth); indices [m] int64 or None.
+    Writes into out_rays [m,13] / out_depths [m] when given (slices of a batch buffer)."""
+    n = directions.shape[1]
+    m = n if indices is None else indices.shape[0]
+    dev = directions.device
+    rays = out_rays if out_rays is not None else torch.empty(m, 13, device=dev, dtype=torch.float32)
+    depths = out_depths if out_depths is not None else torch.empty(m, device=dev, dtype=torch.float32)
+    _lib.call("lb_build_lidar_rays", _p(directions, name="directions"), _p(distances, name="distances"),
+              _p(indices, torch.int64, name="indices"), n, m, _p(rot, name="rot"), _p(origin, name="origin"),
+              float(near), float(far_max), float(inv_scale), float(const_depth), _p(rays), _p(depths), _stream())
+    return rays, depths
+
+
+def build_lidar_rays_bwd(directions, indices, rot, origin, far_max, d_rays, d_rot, d_origin):
+    """R0 backward: accumulates into d_rot [9] and d_origin [3]."""
+    n = directions.shape[1]
+    m = d_rays.shape[0]
+    _lib.call("lb_build_lidar_rays_bwd", _p(directions, name="directions"), _p(indices, torch.int64, name="indices"),
+              n, m, _p(rot, name="rot"), _p(origin, name="origin"), float(far_max), _p(d_rays, name="d_rays"),
+              _p(d_rot), _p(d_origin), _stream())
+
+
 def t_steps(n, device):
     """linspace(0,1,n) computed on the CPU (so every device consumes identical bits), cached."""
     key = (n, str(device))

@@ -119,28 +119,24 @@ def test_sigma_fwd_bwd_golden(name, tc, dev, ops, O):
     # backward against oracle autograd for a random upstream gradient
     gen = torch.Generator().manual_seed(1)
     ds = torch.randn(z.shape, generator=gen)
-    # The checker evaluates the oracle's hash encoding in fp32 and its MLP in fp64: with a random upstream
-    # gradient ONE ReLU unit whose pre-activation is an fp32 rounding tie (|h| < 1e-7 |W1||e|) moves the MLP
-    # gradient by 1e-3 of its max, and which side of the tie an fp32 evaluation lands on depends on its
-    # summation order (tcnn itself evaluates in fp16).  The plain fp32 oracle is checked below with that slack.
+    # A hidden unit whose pre-activation is a rounding tie (|h| < 1e-6 sum|W1||e|) has no well-defined ReLU
+    # derivative in floating point: which side an evaluation lands on depends on its summation order (tcnn
+    # itself evaluates in fp16).  The upstream gradient is zeroed at such points (one in 2 M units here) so
+    # that every other contribution can be compared tightly.
     pr, rr = p.clone().requires_grad_(True), g["rays"].clone().requires_grad_(True)
     xyz = rr[:, None, 0:3] + rr[:, None, 3:6] * g["z"][..., None]
-    e_ref = O.hash_encode((xyz.reshape(-1, 3) + 1) / 2, pr[3072:], g["log2_T"])
-    O.sigma_mlp(e_ref.double(), pr[:3072].double()).view(z.shape).backward(ds.double())
-    p32, r32 = p.clone().requires_grad_(True), g["rays"].clone().requires_grad_(True)
-    xyz32 = r32[:, None, 0:3] + r32[:, None, 3:6] * g["z"][..., None]
-    O.sigma_field(xyz32.reshape(-1, 3), p32, g["log2_T"]).view(z.shape).backward(ds)
+    with torch.no_grad():
+        e0 = O.hash_encode((xyz.reshape(-1, 3) + 1) / 2, p[3072:], g["log2_T"]).double()
+        w1 = p[:2048].view(64, 32).double()
+        tie = ((e0 @ w1.t()).abs() < 1e-6 * (e0.abs() @ w1.abs().t())).any(1)
+        ds.view(-1)[tie] = 0
+    O.sigma_field(xyz.reshape(-1, 3), pr, g["log2_T"]).view(z.shape).backward(ds)
     gp = torch.zeros_like(p, device=dev)
     dr = torch.zeros(rays.shape, device=dev)
     ops.sigma_bwd(plan, p.to(dev), enc, ds.to(dev), rays=rays, z=z, grad_params=gp, d_rays=dr)
-    def either(a, sl, tol=1e-4):      # within tol of the fp64-MLP or of the fp32-MLP evaluation of the oracle
-        return min(rel_err(a[sl], pr.grad[sl]), rel_err(a[sl], p32.grad[sl])) < tol
-    # (the encodings feeding the tie differ in the last bit between implementations as well, so neither reference
-    # is guaranteed to side with the kernel: the MLP block is bounded by the one-tie slack, the tables tightly)
-    assert either(gp, slice(3072, None), 3e-4)
-    assert rel_err(gp[:3072], p32.grad[:3072]) < 3e-3 and rel_err(gp[3072:], p32.grad[3072:]) < 3e-3
-    assert rel_err(gp[:3072], pr.grad[:3072]) < 3e-3 and rel_err(gp[3072:], pr.grad[3072:]) < 3e-3
-    assert min(rel_err(dr[:, :6], rr.grad[:, :6]), rel_err(dr[:, :6], r32.grad[:, :6])) < 1e-3
+    assert rel_err(gp[:3072], pr.grad[:3072]) < 1e-4
+    assert rel_err(gp[3072:], pr.grad[3072:]) < 1e-4
+    assert rel_err(dr[:, :6], rr.grad[:, :6]) < 1e-3
     assert (dr[:, 6:] == 0).all()
     # x01 point source (tcnn module path) gives the same numbers
     x01 = ((xyz.detach().reshape(-1, 3) + 1) / 2).to(dev).contiguous()
@@ -148,7 +144,7 @@ def test_sigma_fwd_bwd_golden(name, tc, dev, ops, O):
     assert rel_err(s2.view(z.shape), g["sigma"]) < 1e-4
     gp2 = torch.zeros_like(gp)
     dx = ops.sigma_bwd(plan, p.to(dev), enc2, ds.to(dev).reshape(-1), x01=x01, grad_params=gp2, need_dx=True)
-    assert either(gp2, slice(0, 3072), 3e-3) and either(gp2, slice(3072, None), 3e-4)
+    assert rel_err(gp2, pr.grad) < 1e-4
     assert dx.shape == (x01.shape[0], 3)
     # frozen sigma head (tracking phase): ray gradients only
     dr3 = torch.zeros(rays.shape, device=dev)
@@ -167,6 +163,10 @@ def test_mlp_tensor_cores_match_fp32(P, dev, ops, O):
     p = torch.cat([(torch.rand(3072, generator=gen) - 0.5) * 1.5, (torch.rand(plan.n_table_params, generator=gen) - 0.5) * 4.0])
     x = torch.rand(P, 3, generator=gen)
     ds = torch.randn(P, generator=gen)
+    with torch.no_grad():     # no upstream gradient at ReLU rounding ties (see test_sigma_fwd_bwd_golden)
+        e0 = O.hash_encode(x, p[3072:], log2T).double()
+        w1 = p[:2048].view(64, 32).double()
+        ds[((e0 @ w1.t()).abs() < 1e-6 * (e0.abs() @ w1.abs().t())).any(1)] = 0
     pr, xr = p.clone().requires_grad_(True), x.clone().requires_grad_(True)
     ref = O.sigma_mlp(O.hash_encode(xr, pr[3072:], log2T), pr[:3072])
     ref.backward(ds)
@@ -281,3 +281,38 @@ def test_occ_update_golden(name, dev, ops, O):
     ops.sgd_step(occ.view(-1), grad.view(-1), 1e-4)
     assert rel_err(occ - g["occ"].to(dev), g["occ_after"] - g["occ"]) < 1e-4
     assert rel_err(occ, g["occ_after"]) < 1e-6
+
+
+# ------------------------------------------------------------------------------------------ ray construction
+@pytest.mark.parametrize("far_clip", [False, True])
+def test_build_lidar_rays_matches_oracle(far_clip, dev, O):
+    """lb_build_lidar_rays (+ backward to the pose 6-vector) against the oracle's restatement of
+    ray_utils.py:269-322; far_clip places the sensor near a cube face so that far = cube exit for most rays."""
+    from loner_b200 import mapping as M
+    gen = torch.Generator().manual_seed(7)
+    n = 3000
+    dirs = torch.randn(3, n, generator=gen)
+    dirs = dirs / dirs.norm(dim=0, keepdim=True)
+    dist = torch.rand(n, generator=gen) * 40 + 1
+    idx = torch.randint(n, (777,), generator=gen)
+    pose = torch.tensor([20.0 if far_clip else 1.0, -2.0, 0.5, 0.3, -0.2, 0.9])
+    scale, shift = torch.tensor(60.0 if not far_clip else 25.0), torch.tensor([0.5, 1.0, -0.25])
+    rr = torch.tensor([1.0, 50.0])
+    pr = pose.clone().requires_grad_(True)
+    rays_ref, depths_ref = O.build_lidar_rays(dirs[:, idx], dist[idx], pr, shift, scale, rr)
+    g = torch.randn(rays_ref.shape, generator=gen)
+    rays_ref.backward(g)
+    pd = pose.to(dev).requires_grad_(True)
+    wc = M.WorldCube(scale.to(dev), shift.to(dev))
+    rays, depths = M.build_lidar_rays(dirs.to(dev), dist.to(dev), pd, wc, (1.0, 50.0), ignore_world_cube=False,
+                                      indices=idx.to(dev))
+    assert rays.shape == rays_ref.shape
+    if far_clip:
+        assert (rays_ref[:, 12] < 50.0 / 25.0 - 1e-6).float().mean() > 0.3
+    assert rel_err(rays, rays_ref) < 1e-6 and rel_err(depths, depths_ref) < 1e-6
+    rays.backward(g.to(dev))
+    assert rel_err(pd.grad, pr.grad) < 1e-4
+    # sky rays: constant depth, detached pose
+    srays, sdepths = M.build_lidar_rays(dirs.to(dev), None, pd.detach(), wc, (1.0, 50.0), False, indices=idx.to(dev),
+                                        const_depth=51.0)
+    assert torch.equal(srays, rays.detach()) and torch.allclose(sdepths, torch.full_like(sdepths, 51.0 / float(scale)))
