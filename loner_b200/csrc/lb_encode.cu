@@ -60,7 +60,8 @@ struct Side {
     uint32_t cx, cy, cz;         // cell (for run detection)
 };
 
-__device__ __forceinline__ Side locate_side(const lb_level& L, const Point& q, int half) {
+template <bool kDense>
+__device__ __forceinline__ Side locate_side_t(const lb_level& L, const Point& q, int half) {
     Side s;
     const float px = fmaf(L.scale, q.x, 0.5f), py = fmaf(L.scale, q.y, 0.5f), pz = fmaf(L.scale, q.z, 0.5f);
     const float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
@@ -70,36 +71,40 @@ __device__ __forceinline__ Side locate_side(const lb_level& L, const Point& q, i
     s.wy[0] = 1.0f - fy; s.wy[1] = fy;
     s.wz[0] = 1.0f - fz; s.wz[1] = fz;
     const uint32_t x = s.cx + (uint32_t)half;
-    bool wrap;
-    if (L.dense) {
+    if (kDense) {
         // x + y*res + z*res^2; tcnn wraps with "% size", which in-cube points never need
         const uint32_t a0 = x + s.cy * L.res, a1 = a0 + L.res;
         const uint32_t z0 = s.cz * L.res2, z1 = z0 + L.res2;
         s.idx[0] = a0 + z0; s.idx[1] = a1 + z0; s.idx[2] = a0 + z1; s.idx[3] = a1 + z1;
-        wrap = s.idx[3] >= L.size || s.idx[0] >= L.size;
+        if (s.idx[3] >= L.size || s.idx[0] >= L.size) {
+            const uint4 w = wrap_indices(make_uint4(s.idx[0], s.idx[1], s.idx[2], s.idx[3]), L.size);
+            s.idx[0] = w.x; s.idx[1] = w.y; s.idx[2] = w.z; s.idx[3] = w.w;
+        }
     } else {
+        // coherent prime hash; a hashed level always has size = 2^log2_hashmap_size (lb_plan_create), so the
+        // "% size" of tcnn is a mask
         const uint32_t y0 = s.cy * 2654435761u, y1 = y0 + 2654435761u;
         const uint32_t z0 = s.cz * 805459861u, z1 = z0 + 805459861u;
-        s.idx[0] = x ^ y0 ^ z0; s.idx[1] = x ^ y1 ^ z0; s.idx[2] = x ^ y0 ^ z1; s.idx[3] = x ^ y1 ^ z1;
-        wrap = L.mask == 0u;
-        if (!wrap) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) s.idx[k] &= L.mask;
-        }
-    }
-    if (wrap) {
-        const uint4 w = wrap_indices(make_uint4(s.idx[0], s.idx[1], s.idx[2], s.idx[3]), L.size);
-        s.idx[0] = w.x; s.idx[1] = w.y; s.idx[2] = w.z; s.idx[3] = w.w;
+        s.idx[0] = (x ^ y0 ^ z0) & L.mask; s.idx[1] = (x ^ y1 ^ z0) & L.mask;
+        s.idx[2] = (x ^ y0 ^ z1) & L.mask; s.idx[3] = (x ^ y1 ^ z1) & L.mask;
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) s.idx[k] += L.offset;
     return s;
 }
 
+// kNDense >= 0: levels [0, kNDense) are dense and the rest hashed, resolved at compile time once the level loop
+// is unrolled (one index formula per level body instead of two); kNDense < 0: decided per level at run time
+template <int kNDense>
+__device__ __forceinline__ Side locate_side(const lb_level& L, const Point& q, int half, int l) {
+    if (kNDense >= 0) return (l < kNDense) ? locate_side_t<true>(L, q, half) : locate_side_t<false>(L, q, half);
+    return L.dense ? locate_side_t<true>(L, q, half) : locate_side_t<false>(L, q, half);
+}
+
 // ------------------------------------------------------------------------------------------
 // forward: enc[p][2l+f] = sum over 8 corners of w_c * table[idx_c][f]
 // ------------------------------------------------------------------------------------------
-template <bool kFromRays>
+template <bool kFromRays, int kNDense>
 __global__ void __launch_bounds__(kThreads, 8)
 encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
                   const float* __restrict__ x01, const float2* __restrict__ table, size_t n_points, int n_samples,
@@ -118,7 +123,7 @@ encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
             float a = 0.0f, b = 0.0f;
             if (l < T.n_levels) {
                 const lb_level& L = T.lv[l];
-                const Side s = locate_side(L, q, half);
+                const Side s = locate_side<kNDense>(L, q, half, l);
                 float2 v[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) v[k] = __ldg(table + s.idx[k]);
@@ -160,8 +165,21 @@ encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
 // backward: table scatter-add (warp-aggregated) and optional dL/dx01
 // ------------------------------------------------------------------------------------------
 constexpr int kAggMaxRuns = 12;   // aggregate when the warp's 16 points fall into <= 12 distinct cells
+constexpr int kAggLevels = 8;     // only the coarse levels carry the run-merging code (instruction-cache budget);
+                                  // finer levels always scatter every corner, which is equally correct
 
-template <bool kFromRays, bool kInputGrad>
+// segmented suffix sum over the warp's 16 points (2 lanes each): a run head collects its whole run.  Out of
+// line: one copy instead of 8 values x 8 levels, called convergently by all 32 lanes.
+__device__ __noinline__ float seg_suffix_sum(float v, int dist) {
+#pragma unroll
+    for (int off = 1; off < 16; off <<= 1) {
+        const float t = __shfl_down_sync(kFull, v, 2 * off);
+        if (off < dist) v += t;
+    }
+    return v;
+}
+
+template <bool kFromRays, bool kInputGrad, int kNDense>
 __global__ void __launch_bounds__(kThreads, 6)
 encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
                   const float* __restrict__ x01, const float2* __restrict__ table, const float* __restrict__ d_enc,
@@ -195,13 +213,24 @@ encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
 #pragma unroll
             for (int i = 0; i < LB_MLP_IN; ++i) de[i] = 0.0f;
         }
+        // A sample whose upstream gradient row is exactly zero (ReLU-inactive density: dL/dsigma = 0, roughly
+        // every second sample while the field is young) scatters nothing: the L2 atomics are what bounds this
+        // kernel, so such points issue none.
+        uint32_t nz_bits = 0u;
+#pragma unroll
+        for (int i = 0; i < LB_MLP_IN; ++i) nz_bits |= __float_as_uint(de[i]);
+        const bool nonzero = (nz_bits << 1) != 0u;
+        if (__all_sync(kFull, !nonzero)) {                             // warp-uniform: nothing to scatter for these 16 points
+            if (kInputGrad && !kFromRays && valid && !half) { d_x01[3 * p + 0] = 0.0f; d_x01[3 * p + 1] = 0.0f; d_x01[3 * p + 2] = 0.0f; }
+            continue;
+        }
         float gx = 0.0f, gy = 0.0f, gz = 0.0f;
         bool all_distinct = false;     // once a level has 16 distinct cells, finer levels do too
 #pragma unroll
         for (int l = 0; l < 16; ++l) {
             if (l >= T.n_levels) continue;
             const lb_level& L = T.lv[l];
-            const Side s = locate_side(L, q, half);
+            const Side s = locate_side<kNDense>(L, q, half, l);
             const float d0 = de[2 * l], d1 = de[2 * l + 1];
             const uint32_t* idx = s.idx;
             if (kInputGrad) {
@@ -231,8 +260,8 @@ encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
                     a[k] = w * d0;
                     b[k] = w * d1;
                 }
-                bool issue = valid;
-                if (!all_distinct) {
+                bool issue = valid && nonzero;
+                if (l < kAggLevels && !all_distinct) {
                     // run detection over the warp's 16 points (previous point = lane - 2)
                     const uint32_t pcx = __shfl_up_sync(kFull, s.cx, 2), pcy = __shfl_up_sync(kFull, s.cy, 2),
                                    pcz = __shfl_up_sync(kFull, s.cz, 2);
@@ -247,15 +276,11 @@ encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
                         const unsigned rest = (pair < 15) ? (heads >> (2 * pair + 2)) : 0u;
                         const int dist = rest ? 1 + ((__ffs(rest) - 1) >> 1) : 16 - pair;   // points until the next head
 #pragma unroll
-                        for (int off = 1; off < 16; off <<= 1) {
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                const float ta = __shfl_down_sync(kFull, a[k], 2 * off);
-                                const float tb = __shfl_down_sync(kFull, b[k], 2 * off);
-                                if (off < dist) { a[k] += ta; b[k] += tb; }
-                            }
+                        for (int k = 0; k < 4; ++k) {
+                            a[k] = seg_suffix_sum(a[k], dist);
+                            b[k] = seg_suffix_sum(b[k], dist);
                         }
-                        issue = valid && !same;
+                        issue = valid && !same;      // a run head carries the run's sum (zero rows add zeros)
                     }
                 }
                 if (issue) {
@@ -303,6 +328,36 @@ int grid_for(int sm_count, size_t n_points, int blocks_per_sm) {
     return (int)(tiles < cap ? (tiles ? tiles : 1) : cap);
 }
 
+// number of leading dense levels if the plan is "dense prefix, hashed (power-of-two) rest", else -1
+int dense_prefix(const lb_plan* plan) {
+    int nd = 0;
+    while (nd < plan->cfg.n_levels && plan->levels[nd].dense) ++nd;
+    for (int l = nd; l < plan->cfg.n_levels; ++l)
+        if (plan->levels[l].dense || plan->levels[l].mask == 0u) return -1;
+    return (nd >= 1 && nd <= 4) ? nd : -1;
+}
+
+template <int kNDense>
+void launch_fwd(const lb_level_table& T, int grid, const float* rays, const float* z, const float* x01, const float2* tb,
+                size_t n_points, int n_samples, float* enc, cudaStream_t st) {
+    if (rays) encode_fwd_kernel<true, kNDense><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, n_points, n_samples, enc);
+    else encode_fwd_kernel<false, kNDense><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, n_points, 1, enc);
+}
+
+template <int kNDense>
+void launch_bwd(const lb_level_table& T, int grid, const float* rays, const float* z, const float* x01, const float2* tb,
+                const float* d_enc, size_t n_points, int n_samples, float* grad_table, float* d_rays, float* d_x01,
+                cudaStream_t st) {
+    const bool in_grad = (d_rays != nullptr) || (d_x01 != nullptr);
+    if (rays) {
+        if (in_grad) encode_bwd_kernel<true, true, kNDense><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, d_rays, nullptr);
+        else encode_bwd_kernel<true, false, kNDense><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, nullptr, nullptr);
+    } else {
+        if (in_grad) encode_bwd_kernel<false, true, kNDense><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, d_x01);
+        else encode_bwd_kernel<false, false, kNDense><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, nullptr);
+    }
+}
+
 }  // namespace
 
 // internal launchers shared with lb_field.cu
@@ -311,8 +366,13 @@ int lb_launch_encode_fwd(const lb_plan* plan, const float* rays, const float* z,
     const lb_level_table T = lb_make_level_table(plan);
     const int grid = grid_for(plan->sm_count, n_points, 8);
     const float2* tb = reinterpret_cast<const float2*>(table);
-    if (rays) encode_fwd_kernel<true><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, n_points, n_samples, enc);
-    else encode_fwd_kernel<false><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, n_points, 1, enc);
+    switch (dense_prefix(plan)) {
+        case 1: launch_fwd<1>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
+        case 2: launch_fwd<2>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
+        case 3: launch_fwd<3>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
+        case 4: launch_fwd<4>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
+        default: launch_fwd<-1>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
+    }
     return lb_check_cuda(cudaGetLastError(), "encode_fwd launch");
 }
 
@@ -322,13 +382,12 @@ int lb_launch_encode_bwd(const lb_plan* plan, const float* rays, const float* z,
     const lb_level_table T = lb_make_level_table(plan);
     const int grid = grid_for(plan->sm_count, n_points, 6);
     const float2* tb = reinterpret_cast<const float2*>(table);
-    const bool in_grad = (d_rays != nullptr) || (d_x01 != nullptr);
-    if (rays) {
-        if (in_grad) encode_bwd_kernel<true, true><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, d_rays, nullptr);
-        else encode_bwd_kernel<true, false><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, nullptr, nullptr);
-    } else {
-        if (in_grad) encode_bwd_kernel<false, true><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, d_x01);
-        else encode_bwd_kernel<false, false><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, nullptr);
+    switch (dense_prefix(plan)) {
+        case 1: launch_bwd<1>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
+        case 2: launch_bwd<2>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
+        case 3: launch_bwd<3>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
+        case 4: launch_bwd<4>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
+        default: launch_bwd<-1>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
     }
     return lb_check_cuda(cudaGetLastError(), "encode_bwd launch");
 }

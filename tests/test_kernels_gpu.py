@@ -105,6 +105,30 @@ def test_encode_fwd_bwd(log2T, dev, ops, O):
     assert rel_err(dx[8:], xr.grad[8:]) < 1e-4
 
 
+def test_encode_bwd_skips_zero_rows(dev, ops, O):
+    """Rows of dL/d_enc that are exactly zero (ReLU-inactive samples) issue no atomics; whole zero warps are
+    skipped, and dL/dx of such points is written as zero."""
+    gen = torch.Generator().manual_seed(5)
+    plan = ops.Plan(log2_hashmap_size=15)
+    P = 4099
+    x = torch.rand(P, 3, generator=gen)
+    table = (torch.rand(plan.n_table_params, generator=gen) * 2 - 1) * 0.3
+    de = torch.randn(P, 32, generator=gen)
+    de[torch.rand(P, generator=gen) < 0.5] = 0          # scattered zero rows
+    de[1024:2048] = 0                                   # whole warps / tiles of zero rows
+    de[7] = -0.0
+    xr, tr = x.clone().requires_grad_(True), table.clone().requires_grad_(True)
+    O.hash_encode(xr, tr, 15).backward(de)
+    gt = torch.zeros_like(table, device=dev)
+    dx = ops.encode_bwd(plan, x.to(dev), table.to(dev), de.to(dev), gt, need_dx=True)
+    assert rel_err(gt, tr.grad) < 1e-4
+    assert rel_err(dx, xr.grad) < 1e-4
+    assert (dx[1024:2048] == 0).all()
+    gt2 = torch.zeros_like(gt)
+    ops.encode_bwd(plan, x.to(dev), table.to(dev), de.to(dev), gt2, need_dx=False)
+    assert rel_err(gt2, tr.grad) < 1e-4
+
+
 @pytest.mark.parametrize("tc", [True, False], ids=["tcgen05", "simt"])
 @pytest.mark.parametrize("name", ALL_CASES)
 def test_sigma_fwd_bwd_golden(name, tc, dev, ops, O):
