@@ -7,8 +7,9 @@
 // Precision.  north_star wants 1e-3 agreement with fp32 accumulate, and the weight gradient is a strongly
 // cancelling sum, so a single bf16/tf32 pass is not enough.  Every fp32 operand x is split into bf16 pieces
 // x = b1 + b2 (+ O(2^-18 x)), b1 = rn_bf16(x), b2 = rn_bf16(x - b1), and the products are accumulated in fp32:
-//   forward : H = sum of the six products Ei W1x^T of order <= 2^-18  (three pieces each, error ~2^-25: the
-//             ReLU mask must be as reliable as an fp32 evaluation, a flipped unit changes a gradient row by O(1))
+//   forward : kind::tf32 on exact hi/lo splits of the fp32 operands, H = Ehi Whi^T + Ehi Wlo^T + Elo Whi^T
+//             (error ~2^-21: the ReLU mask must be as reliable as an fp32 evaluation, a flipped unit changes a
+//             gradient row by O(1); the split costs 2 ALU ops per element and needs no lane exchange)
 //   backward: the A operand is the ReLU mask m[p,j] in {0,1}, exact in bf16, so two pieces of B suffice:
 //     dE[p,:] = ds[p] * sum_j m[p,j] (w2[j] W1[j,:])                  A = M (K-major),  B = W1s pieces
 //     U[j,k]  = sum_p m[p,j] (ds[p] e[p,k])                           A = M^T (MN-major view of the same tile)
@@ -57,6 +58,20 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// kind::tf32 instruction descriptor: D = f32, A = B = tf32 (fp32 bit patterns in shared memory, K = 8 per MMA)
+constexpr uint32_t umma_idesc_tf32(int m, int n) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
         "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
@@ -202,15 +217,51 @@ __device__ __forceinline__ void convert_weights(const float* __restrict__ w1, co
     }
 }
 
+// ---- tf32 splitting (forward) ------------------------------------------------------------------
+// x = hi + lo exactly, hi = x with the 13 low mantissa bits cleared (a tf32 number), lo = x - hi (13 significant
+// bits, of which the tensor core keeps 11): hi*hi + hi*lo + lo*hi reproduces the fp32 product to ~2^-21.
+__device__ __forceinline__ void split_tf32(const float4& v, uint4& hi, uint4& lo) {
+    hi.x = __float_as_uint(v.x) & 0xffffe000u; hi.y = __float_as_uint(v.y) & 0xffffe000u;
+    hi.z = __float_as_uint(v.z) & 0xffffe000u; hi.w = __float_as_uint(v.w) & 0xffffe000u;
+    lo.x = __float_as_uint(v.x - __uint_as_float(hi.x)); lo.y = __float_as_uint(v.y - __uint_as_float(hi.y));
+    lo.z = __float_as_uint(v.z - __uint_as_float(hi.z)); lo.w = __float_as_uint(v.w - __uint_as_float(hi.w));
+}
+
+// register tile -> hi / lo fp32 tiles X[r = point][c = k / 4] (8 chunks of 4 tf32): every float4 of the flat
+// mapping IS one chunk, so no lane exchange is needed and the 8 lanes of a store phase hit 8 different banks
+__device__ __forceinline__ void convert_tile_tf32(const TileRegs& t, uint8_t* hi_tile, uint8_t* lo_tile) {
+    const int chunk = threadIdx.x & 7;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int row = i * 16 + (threadIdx.x >> 3);
+        uint4 hi, lo;
+        split_tf32(t.f[i], hi, lo);
+        const uint32_t off = tile_off(row, chunk, kLboP);
+        *reinterpret_cast<uint4*>(hi_tile + off) = hi;
+        *reinterpret_cast<uint4*>(lo_tile + off) = lo;
+    }
+}
+
+__device__ __forceinline__ void convert_weights_tf32(const float* __restrict__ w1, uint8_t* hi_tile, uint8_t* lo_tile) {
+    for (int it = threadIdx.x; it < LB_MLP_W * 8; it += kThreads) {
+        const int j = it >> 3, c = it & 7;
+        const float4 v = __ldg(reinterpret_cast<const float4*>(w1 + j * LB_MLP_IN + c * 4));
+        uint4 hi, lo;
+        split_tf32(v, hi, lo);
+        *reinterpret_cast<uint4*>(hi_tile + tile_off(j, c, kLboW)) = hi;
+        *reinterpret_cast<uint4*>(lo_tile + tile_off(j, c, kLboW)) = lo;
+    }
+}
+
 // ---- shared-memory carve-up -----------------------------------------------------------------
 constexpr uint32_t kPieceP = 4 * kLboP;            // [128 x 32] bf16 piece tile
 constexpr uint32_t kPieceW = 4 * kLboW;            // [ 64 x 32] bf16 piece tile
 constexpr uint32_t kMaskT = 8 * kLboP;             // [128 x 64] bf16 mask tile
 constexpr uint32_t kOutStride = 144;               // padded row stride of the fp32 dE staging tile
 
-struct FwdSmem {
-    static constexpr uint32_t e1 = 0, e2 = e1 + kPieceP, e3 = e2 + kPieceP, wa = e3 + kPieceP, wb = wa + kPieceW,
-                              wc = wb + kPieceW, w2 = wc + kPieceW, bar = w2 + 64 * 4, tmem = bar + 8, total = tmem + 8;
+struct FwdSmem {      // tf32 tiles: 8 chunks of 4 elements per row
+    static constexpr uint32_t ehi = 0, elo = ehi + 8 * kLboP, whi = elo + 8 * kLboP, wlo = whi + 8 * kLboW,
+                              w2 = wlo + 8 * kLboW, bar = w2 + 64 * 4, tmem = bar + 8, total = tmem + 8;
 };
 struct BwdSmem {
     static constexpr uint32_t mt = 0, e1 = mt + kMaskT, e2 = e1 + kPieceP, wa = e2 + kPieceP, wb = wa + kPieceW,
@@ -232,16 +283,16 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
 
     if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
     if (tid == 32) mbar_init(bar, 1);
-    convert_weights(mlp, nullptr, sm + FwdSmem::wa, sm + FwdSmem::wb, sm + FwdSmem::wc);
+    convert_weights_tf32(mlp, sm + FwdSmem::whi, sm + FwdSmem::wlo);
     if (tid < LB_MLP_W) w2s[tid] = __ldg(mlp + LB_MLP_W * LB_MLP_IN + tid);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    const uint32_t a1 = smem_u32(sm + FwdSmem::e1), a2 = smem_u32(sm + FwdSmem::e2), a3 = smem_u32(sm + FwdSmem::e3);
-    const uint32_t ba = smem_u32(sm + FwdSmem::wa), bb = smem_u32(sm + FwdSmem::wb), bc = smem_u32(sm + FwdSmem::wc);
-    constexpr uint32_t idesc = umma_idesc(128, LB_MLP_W, 0, 0);
+    const uint32_t ahi = smem_u32(sm + FwdSmem::ehi), alo = smem_u32(sm + FwdSmem::elo);
+    const uint32_t bhi = smem_u32(sm + FwdSmem::whi), blo = smem_u32(sm + FwdSmem::wlo);
+    constexpr uint32_t idesc = umma_idesc_tf32(128, LB_MLP_W);
 
     const size_t n_tiles = (n_points + kTile - 1) / kTile;
     TileRegs regs;
@@ -249,7 +300,7 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
     if (tile < n_tiles) load_tile(enc, tile, n_points, regs);
     uint32_t parity = 0;
     for (; tile < n_tiles; tile += gridDim.x) {
-        convert_tile<true>(regs, nullptr, sm + FwdSmem::e1, sm + FwdSmem::e2, sm + FwdSmem::e3);
+        convert_tile_tf32(regs, sm + FwdSmem::ehi, sm + FwdSmem::elo);
         const size_t next = tile + gridDim.x;
         if (next < n_tiles) load_tile(enc, next, n_points, regs);      // in flight during the MMAs and the epilogue
         fence_async_smem();
@@ -258,21 +309,16 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
         if (tid == 0) {
             tc_fence_after();
 #pragma unroll
-            for (int ks = 0; ks < 2; ++ks) {                           // K = 32 = 2 x 16
-                const uint64_t da1 = umma_desc(a1 + ks * 2 * kLboP, kLboP, 128);
-                const uint64_t da2 = umma_desc(a2 + ks * 2 * kLboP, kLboP, 128);
-                const uint64_t da3 = umma_desc(a3 + ks * 2 * kLboP, kLboP, 128);
-                const uint64_t dba = umma_desc(ba + ks * 2 * kLboW, kLboW, 128);
-                const uint64_t dbb = umma_desc(bb + ks * 2 * kLboW, kLboW, 128);
-                const uint64_t dbc = umma_desc(bc + ks * 2 * kLboW, kLboW, 128);
-                // all products of order <= 2^-18: the hidden pre-activation is as accurate as an fp32 FMA chain,
-                // so the ReLU mask flips no more often than any fp32 evaluation would
-                umma_bf16(tmem, da1, dba, idesc, ks > 0);
-                umma_bf16(tmem, da1, dbb, idesc, 1);
-                umma_bf16(tmem, da2, dba, idesc, 1);
-                umma_bf16(tmem, da1, dbc, idesc, 1);
-                umma_bf16(tmem, da2, dbb, idesc, 1);
-                umma_bf16(tmem, da3, dba, idesc, 1);
+            for (int ks = 0; ks < 4; ++ks) {                           // K = 32 = 4 x 8 (tf32)
+                const uint64_t dah = umma_desc(ahi + ks * 2 * kLboP, kLboP, 128);
+                const uint64_t dal = umma_desc(alo + ks * 2 * kLboP, kLboP, 128);
+                const uint64_t dbh = umma_desc(bhi + ks * 2 * kLboW, kLboW, 128);
+                const uint64_t dbl = umma_desc(blo + ks * 2 * kLboW, kLboW, 128);
+                // hi*hi + hi*lo + lo*hi: the hidden pre-activation is as accurate as an fp32 FMA chain (~2^-21), so
+                // the ReLU mask flips no more often than any fp32 evaluation would
+                umma_tf32(tmem, dah, dbh, idesc, ks > 0);
+                umma_tf32(tmem, dah, dbl, idesc, 1);
+                umma_tf32(tmem, dal, dbh, idesc, 1);
             }
             umma_commit(bar);
         }

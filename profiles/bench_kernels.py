@@ -61,6 +61,8 @@ print(f"N={N} S={S} P={P} T=2^{T}")
 timeit("sample_occ", lambda: ops.sample_occ(rays, occ, u1, u2, S, 1.0), 12300 / S)
 timeit("encode_fwd (x01)", lambda: ops.encode_fwd(plan, x01, table), 1024 + 12 + 128)
 timeit("encode_bwd table only", lambda: ops.encode_bwd(plan, x01, table, d_enc, gt, False), 2048 + 128 + 12)
+d_enc_half = d_enc * (torch.rand(P, 1, device=dev) < 0.5)
+timeit("encode_bwd table only, 50% zero rows", lambda: ops.encode_bwd(plan, x01, table, d_enc_half, gt, False), 2048 + 128 + 12)
 timeit("encode_bwd table + dx", lambda: ops.encode_bwd(plan, x01, table, d_enc, gt, True), 3072 + 128 + 24)
 timeit("sigma_fwd (rays) + save enc", lambda: ops.sigma_fwd(plan, params, rays=rays, z=z), 1024 + 4 + 128 + 4)
 timeit("sigma_fwd (rays) no save", lambda: ops.sigma_fwd(plan, params, rays=rays, z=z, save_enc=False), 1024 + 8)
