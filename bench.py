@@ -41,12 +41,21 @@ ALGO_BYTES = {"lb_sigma_fwd": 16 * 8 * 8 + 4 + 128 + 4, "lb_sigma_bwd": 16 * 8 *
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample-rays", type=int, default=512, help="rays per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
+
+
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of a C-ABI call from the committed ncu capture (profiles/r01_traffic.json)."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    try:
+        return float(json.load(open(p)).get(kernel))
+    except Exception:
+        return None
 
 
 def measured_peaks():
@@ -282,7 +291,10 @@ def run_ours(args):
     per_launch_points = P / max(1, (n_rays + W["chunk"] - 1) // W["chunk"])
     achieved = ALGO_BYTES[dom] * per_launch_points / (t_l / n_l * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_point": ALGO_BYTES[dom],
+                "traffic": ncu_traffic(dom) if abs(per_launch_points - 16384 * 512) < 1 else None,
+                "traffic_note": "DRAM bytes per launch from ncu (profiles/r01_traffic.json); below the algorithmic bytes because the "
+                                "57 MB of tables and their gradient stay L2-resident: the gathers / atomics are L2 traffic",
+                "peak_source": peak_src, "algorithmic_bytes_per_point": ALGO_BYTES[dom],
                 "points_per_launch": per_launch_points, "avg_launch_ms": t_l / n_l,
                 "kernels_ms_per_step": {k: round(v[1] / args.steps, 4) for k, v in sorted(ktimes.items())}}
     for k in ALGO_BYTES:
