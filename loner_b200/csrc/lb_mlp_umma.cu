@@ -35,6 +35,9 @@ constexpr int kThreads = 128;
 constexpr uint32_t kLboP = kTile * 16 + 16;        // chunk stride of a 128-row tile (points)
 constexpr uint32_t kLboW = LB_MLP_W * 16 + 16;     // chunk stride of a 64-row tile (hidden units)
 constexpr uint32_t kTmemCols = 64;
+// resident CTAs per SM (shared memory 49.7 KB forward / 42.5 KB backward, 64 TMEM columns each)
+constexpr int kFwdCtasPerSm = 4;
+constexpr int kBwdCtasPerSm = 3;
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -65,15 +68,6 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
 // kind::tf32 instruction descriptor: D = f32, A = B = tf32 (fp32 bit patterns in shared memory, K = 8 per MMA)
 constexpr uint32_t umma_idesc_tf32(int m, int n) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
-}
-
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                          uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
-        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
 }
 
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
@@ -124,6 +118,35 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// A operand in tensor memory: D[tmem] (+)= A[tmem] * B[smem]
+__device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+        "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// 32 lanes x 16 consecutive columns: thread i of the warp writes columns [col, col+16) of TMEM lane base+i
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// 16-byte asynchronous global -> shared copy; src_bytes = 0 zero-fills the destination
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory"); }
 
 // ---- bf16 splitting -------------------------------------------------------------------------
 // packs rn_bf16(lo), rn_bf16(hi) into one register (lo in bits 0-15)
@@ -227,21 +250,6 @@ __device__ __forceinline__ void split_tf32(const float4& v, uint4& hi, uint4& lo
     lo.z = __float_as_uint(v.z - __uint_as_float(hi.z)); lo.w = __float_as_uint(v.w - __uint_as_float(hi.w));
 }
 
-// register tile -> hi / lo fp32 tiles X[r = point][c = k / 4] (8 chunks of 4 tf32): every float4 of the flat
-// mapping IS one chunk, so no lane exchange is needed and the 8 lanes of a store phase hit 8 different banks
-__device__ __forceinline__ void convert_tile_tf32(const TileRegs& t, uint8_t* hi_tile, uint8_t* lo_tile) {
-    const int chunk = threadIdx.x & 7;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int row = i * 16 + (threadIdx.x >> 3);
-        uint4 hi, lo;
-        split_tf32(t.f[i], hi, lo);
-        const uint32_t off = tile_off(row, chunk, kLboP);
-        *reinterpret_cast<uint4*>(hi_tile + off) = hi;
-        *reinterpret_cast<uint4*>(lo_tile + off) = lo;
-    }
-}
-
 __device__ __forceinline__ void convert_weights_tf32(const float* __restrict__ w1, uint8_t* hi_tile, uint8_t* lo_tile) {
     for (int it = threadIdx.x; it < LB_MLP_W * 8; it += kThreads) {
         const int j = it >> 3, c = it & 7;
@@ -259,20 +267,41 @@ constexpr uint32_t kPieceW = 4 * kLboW;            // [ 64 x 32] bf16 piece tile
 constexpr uint32_t kMaskT = 8 * kLboP;             // [128 x 64] bf16 mask tile
 constexpr uint32_t kOutStride = 144;               // padded row stride of the fp32 dE staging tile
 
-struct FwdSmem {      // tf32 tiles: 8 chunks of 4 elements per row
-    static constexpr uint32_t ehi = 0, elo = ehi + 8 * kLboP, whi = elo + 8 * kLboP, wlo = whi + 8 * kLboW,
-                              w2 = wlo + 8 * kLboW, bar = w2 + 64 * 4, tmem = bar + 8, total = tmem + 8;
+constexpr uint32_t kRowStride = 144;               // padded row stride of a raw fp32 staging tile (128 B of data)
+constexpr uint32_t kStage = kTile * kRowStride;
+constexpr uint32_t kFwdTmemCols = 128;             // H accumulator 64 + E hi 32 + E lo 32
+
+struct FwdSmem {      // two raw staging tiles (cp.async ring), tf32 hi / lo weight tiles (8 chunks of 4 elements per row)
+    static constexpr uint32_t stage = 0, whi = stage + 2 * kStage, wlo = whi + 8 * kLboW, w2 = wlo + 8 * kLboW,
+                              bar = w2 + 64 * 4, tmem = bar + 8, total = tmem + 8;
 };
-struct BwdSmem {
+struct BwdSmem {      // the fp32 dE staging tile reuses the mask / E' operand tiles, dead once the MMAs have completed
     static constexpr uint32_t mt = 0, e1 = mt + kMaskT, e2 = e1 + kPieceP, wa = e2 + kPieceP, wb = wa + kPieceW,
-                              out = wb + kPieceW, ds = out + kTile * kOutStride, bar = ds + kTile * 4, tmem = bar + 8,
-                              total = tmem + 8;
+                              out = 0, ds = wb + kPieceW, bar = ds + kTile * 4, tmem = bar + 8, total = tmem + 8;
+    static_assert(kTile * kOutStride <= wa, "dE staging must fit in the operand tiles it aliases");
 };
 
 // ------------------------------------------------------------------------------------------
 // forward: sigma[p] = sum_j w2[j] relu(sum_k W1[j,k] e[p,k]);  act[p] = bit mask of the active hidden units
+//
+// The shared-memory data pipe (LSU stores + tensor-core operand reads) was the busiest unit of the first version
+// (ncu: 38 % + 44 %), so the A operand (the encodings) now lives in tensor memory: cp.async stages the raw fp32
+// tile (coalesced, padded rows), thread t reads row t conflict-free, splits it into tf32 hi / lo and writes both
+// to TMEM lane t with tcgen05.st; only the 2 x 8 KB weight tiles are read from shared memory by the MMAs.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 3)
+__device__ __forceinline__ void stage_tile(const float* __restrict__ enc, size_t tile, size_t n_points, uint32_t dst) {
+    const float4* base = reinterpret_cast<const float4*>(enc) + tile * (size_t)(kTile * 8);
+    const size_t first = tile * (size_t)kTile;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int row = i * 16 + (threadIdx.x >> 3);
+        const bool ok = first + row < n_points;
+        cp_async16(dst + row * kRowStride + (threadIdx.x & 7) * 16, ok ? (const void*)(base + i * kThreads + threadIdx.x) : (const void*)enc,
+                   ok ? 16u : 0u);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, kFwdCtasPerSm)
 mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc, size_t n_points,
                     float* __restrict__ sigma, unsigned long long* __restrict__ act) {
     extern __shared__ __align__(128) uint8_t sm[];
@@ -280,45 +309,67 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
     float* w2s = reinterpret_cast<float*>(sm + FwdSmem::w2);
     const uint32_t bar = smem_u32(sm + FwdSmem::bar);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + FwdSmem::tmem);
+    const uint32_t stage0 = smem_u32(sm + FwdSmem::stage);
 
-    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    const size_t n_tiles = (n_points + kTile - 1) / kTile;
+    size_t tile = blockIdx.x;
+    if (tile < n_tiles) stage_tile(enc, tile, n_points, stage0);
+    cp_async_commit();
+
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kFwdTmemCols);
     if (tid == 32) mbar_init(bar, 1);
     convert_weights_tf32(mlp, sm + FwdSmem::whi, sm + FwdSmem::wlo);
     if (tid < LB_MLP_W) w2s[tid] = __ldg(mlp + LB_MLP_W * LB_MLP_IN + tid);
+    fence_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    const uint32_t t_h = tmem, t_ahi = tmem + 64, t_alo = tmem + 96;
+    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
 
-    const uint32_t ahi = smem_u32(sm + FwdSmem::ehi), alo = smem_u32(sm + FwdSmem::elo);
     const uint32_t bhi = smem_u32(sm + FwdSmem::whi), blo = smem_u32(sm + FwdSmem::wlo);
     constexpr uint32_t idesc = umma_idesc_tf32(128, LB_MLP_W);
 
-    const size_t n_tiles = (n_points + kTile - 1) / kTile;
-    TileRegs regs;
-    size_t tile = blockIdx.x;
-    if (tile < n_tiles) load_tile(enc, tile, n_points, regs);
-    uint32_t parity = 0;
-    for (; tile < n_tiles; tile += gridDim.x) {
-        convert_tile_tf32(regs, sm + FwdSmem::ehi, sm + FwdSmem::elo);
+    uint32_t parity = 0, buf = 0;
+    for (; tile < n_tiles; tile += gridDim.x, buf ^= 1u) {
+        // the other staging tile was read (by its row owners) before the second barrier of the previous iteration
         const size_t next = tile + gridDim.x;
-        if (next < n_tiles) load_tile(enc, next, n_points, regs);      // in flight during the MMAs and the epilogue
-        fence_async_smem();
+        if (next < n_tiles) stage_tile(enc, next, n_points, stage0 + (buf ^ 1u) * kStage);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncthreads();                                               // every thread's copies of this tile have landed
+        {   // row tid -> tf32 hi / lo -> TMEM lane tid (the previous tile's MMAs were waited on: A is free)
+            const uint8_t* row = sm + FwdSmem::stage + buf * kStage + tid * kRowStride;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                uint32_t hi[16], lo[16];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 v = *reinterpret_cast<const float4*>(row + (h * 4 + q) * 16);
+                    uint4 a, b;
+                    split_tf32(v, a, b);
+                    hi[4 * q] = a.x; hi[4 * q + 1] = a.y; hi[4 * q + 2] = a.z; hi[4 * q + 3] = a.w;
+                    lo[4 * q] = b.x; lo[4 * q + 1] = b.y; lo[4 * q + 2] = b.z; lo[4 * q + 3] = b.w;
+                }
+                tmem_st16(t_ahi + lane_off + h * 16, hi);
+                tmem_st16(t_alo + lane_off + h * 16, lo);
+            }
+            tmem_st_wait();
+        }
         tc_fence_before();
         __syncthreads();
         if (tid == 0) {
             tc_fence_after();
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {                           // K = 32 = 4 x 8 (tf32)
-                const uint64_t dah = umma_desc(ahi + ks * 2 * kLboP, kLboP, 128);
-                const uint64_t dal = umma_desc(alo + ks * 2 * kLboP, kLboP, 128);
                 const uint64_t dbh = umma_desc(bhi + ks * 2 * kLboW, kLboW, 128);
                 const uint64_t dbl = umma_desc(blo + ks * 2 * kLboW, kLboW, 128);
                 // hi*hi + hi*lo + lo*hi: the hidden pre-activation is as accurate as an fp32 FMA chain (~2^-21), so
                 // the ReLU mask flips no more often than any fp32 evaluation would
-                umma_tf32(tmem, dah, dbh, idesc, ks > 0);
-                umma_tf32(tmem, dah, dbl, idesc, 1);
-                umma_tf32(tmem, dal, dbh, idesc, 1);
+                umma_tf32_ts(t_h, t_ahi + ks * 8, dbh, idesc, ks > 0);
+                umma_tf32_ts(t_h, t_ahi + ks * 8, dbl, idesc, 1);
+                umma_tf32_ts(t_h, t_alo + ks * 8, dbh, idesc, 1);
             }
             umma_commit(bar);
         }
@@ -326,13 +377,12 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
         parity ^= 1;
         tc_fence_after();
         // epilogue: thread t owns point tile*128 + t = TMEM lane t
-        const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
         float s = 0.0f;
         unsigned long long bits = 0ull;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
             uint32_t r[32];
-            tmem_ld32(lane_addr + half * 32, r);
+            tmem_ld32(t_h + lane_off + half * 32, r);
             tmem_ld_wait();
             uint32_t m = 0;
 #pragma unroll
@@ -350,15 +400,16 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
             if (act) act[p] = bits;
         }
     }
+    cp_async_wait<0>();
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, kTmemCols);
+    if (warp == 0) tmem_dealloc(tmem, kFwdTmemCols);
 }
 
 // ------------------------------------------------------------------------------------------
 // backward: enc is overwritten in place with dL/d_enc; grad_mlp += (dW1, dW2 row 0)
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, kBwdCtasPerSm)
 mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, const float* __restrict__ d_sigma,
                     const unsigned long long* __restrict__ act, size_t n_points, float* __restrict__ grad_mlp) {
     extern __shared__ __align__(128) uint8_t sm[];
@@ -384,23 +435,32 @@ mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, cons
     constexpr uint32_t idesc_u = umma_idesc(64, LB_MLP_IN, 1, 1);       // A = M^T MN-major, B = E'  MN-major
 
     const size_t n_tiles = (n_points + kTile - 1) / kTile;
-    TileRegs regs;
-    float ds_next = 0.0f;
-    unsigned long long act_next = 0ull;
+    // two sets of staging registers, prefetch distance 2 (see the forward kernel)
+    struct Staged {
+        TileRegs regs;
+        float ds;
+        unsigned long long bits;
+    } st_a, st_b;
+    auto fetch = [&](Staged& st, size_t t) {
+        st.ds = 0.0f;
+        st.bits = 0ull;
+        if (t < n_tiles) {
+            load_tile(enc, t, n_points, st.regs);
+            const size_t p = t * (size_t)kTile + tid;
+            if (p < n_points) { st.ds = __ldg(d_sigma + p); st.bits = __ldg(act + p); }
+        }
+    };
     size_t tile = blockIdx.x;
-    if (tile < n_tiles) {
-        load_tile(enc, tile, n_points, regs);
-        const size_t p = tile * (size_t)kTile + tid;
-        if (p < n_points) { ds_next = __ldg(d_sigma + p); act_next = __ldg(act + p); }
-    }
+    fetch(st_a, tile);
+    fetch(st_b, tile + gridDim.x);
     uint32_t parity = 0;
     bool first = true;
-    for (; tile < n_tiles; tile += gridDim.x) {
-        const float ds = ds_next;
-        const unsigned long long bits = act_next;
+    auto process = [&](Staged& st) {
+        const float ds = st.ds;
+        const unsigned long long bits = st.bits;
         ds_s[tid] = ds;
         __syncthreads();                        // also: the previous tile's staging reads are finished
-        convert_tile<false>(regs, ds_s, sm + BwdSmem::e1, sm + BwdSmem::e2, nullptr);   // E' = ds[p] e[p,:]
+        convert_tile<false>(st.regs, ds_s, sm + BwdSmem::e1, sm + BwdSmem::e2, nullptr);   // E' = ds[p] e[p,:]
         {   // mask tile: row = this thread's point, 8 chunks of 8 hidden units
             uint8_t* row = sm + BwdSmem::mt + tile_off(tid, 0, kLboP);
 #pragma unroll
@@ -414,13 +474,7 @@ mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, cons
                 *reinterpret_cast<uint4*>(row + c * kLboP) = v;
             }
         }
-        const size_t next = tile + gridDim.x;
-        ds_next = 0.0f; act_next = 0ull;
-        if (next < n_tiles) {
-            load_tile(enc, next, n_points, regs);
-            const size_t p = next * (size_t)kTile + tid;
-            if (p < n_points) { ds_next = __ldg(d_sigma + p); act_next = __ldg(act + p); }
-        }
+        fetch(st, tile + 2 * (size_t)gridDim.x);
         fence_async_smem();
         tc_fence_before();
         __syncthreads();
@@ -474,6 +528,12 @@ mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, cons
                 if (first_p + row < n_points) base[i * kThreads + tid] = v;
             }
         }
+        tile += gridDim.x;
+    };
+    while (tile < n_tiles) {
+        process(st_a);
+        if (tile >= n_tiles) break;
+        process(st_b);
     }
     // weight gradients from U (all MMAs of this CTA have completed: the last tile's commit was waited on)
     if (grad_mlp && !first) {
@@ -499,9 +559,9 @@ mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, cons
     if (warp == 0) tmem_dealloc(tmem, kTmemCols);
 }
 
-int umma_grid(int sm_count, size_t n_points) {
+int umma_grid(int sm_count, size_t n_points, int ctas_per_sm) {
     const size_t tiles = (n_points + kTile - 1) / kTile;
-    const size_t cap = (size_t)sm_count * 3;
+    const size_t cap = (size_t)sm_count * ctas_per_sm;
     return (int)(tiles < cap ? (tiles ? tiles : 1) : cap);
 }
 
@@ -516,7 +576,7 @@ int lb_launch_mlp_fwd_umma(const lb_plan* plan, const float* mlp, const float* e
         if (rc) return rc;
         attr_set = true;
     }
-    mlp_fwd_umma_kernel<<<umma_grid(plan->sm_count, n_points), kThreads, FwdSmem::total, st>>>(
+    mlp_fwd_umma_kernel<<<umma_grid(plan->sm_count, n_points, kFwdCtasPerSm), kThreads, FwdSmem::total, st>>>(
         mlp, enc, n_points, sigma, reinterpret_cast<unsigned long long*>(act));
     return lb_check_cuda(cudaGetLastError(), "mlp_fwd_umma launch");
 }
@@ -530,7 +590,7 @@ int lb_launch_mlp_bwd_umma(const lb_plan* plan, const float* mlp, float* enc_ino
         if (rc) return rc;
         attr_set = true;
     }
-    mlp_bwd_umma_kernel<<<umma_grid(plan->sm_count, n_points), kThreads, BwdSmem::total, st>>>(
+    mlp_bwd_umma_kernel<<<umma_grid(plan->sm_count, n_points, kBwdCtasPerSm), kThreads, BwdSmem::total, st>>>(
         mlp, enc_inout, d_sigma, reinterpret_cast<const unsigned long long*>(act), n_points, grad_mlp);
     return lb_check_cuda(cudaGetLastError(), "mlp_bwd_umma launch");
 }
