@@ -273,7 +273,7 @@ constexpr uint32_t kFwdTmemCols = 128;             // H accumulator 64 + E hi 32
 
 struct FwdSmem {      // two raw staging tiles (cp.async ring), tf32 hi / lo weight tiles (8 chunks of 4 elements per row)
     static constexpr uint32_t stage = 0, whi = stage + 2 * kStage, wlo = whi + 8 * kLboW, w2 = wlo + 8 * kLboW,
-                              bar = w2 + 64 * 4, tmem = bar + 8, total = tmem + 8;
+                              v = w2 + 64 * 4, bar = v + 32 * 4, tmem = bar + 8, total = tmem + 8;
 };
 struct BwdSmem {      // the fp32 dE staging tile reuses the mask / E' operand tiles, dead once the MMAs have completed
     static constexpr uint32_t mt = 0, e1 = mt + kMaskT, e2 = e1 + kPieceP, wa = e2 + kPieceP, wb = wa + kPieceW,
@@ -307,6 +307,7 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
     extern __shared__ __align__(128) uint8_t sm[];
     const int tid = threadIdx.x, warp = tid >> 5;
     float* w2s = reinterpret_cast<float*>(sm + FwdSmem::w2);
+    float* vs = reinterpret_cast<float*>(sm + FwdSmem::v);
     const uint32_t bar = smem_u32(sm + FwdSmem::bar);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + FwdSmem::tmem);
     const uint32_t stage0 = smem_u32(sm + FwdSmem::stage);
@@ -319,7 +320,16 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
     if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kFwdTmemCols);
     if (tid == 32) mbar_init(bar, 1);
     convert_weights_tf32(mlp, sm + FwdSmem::whi, sm + FwdSmem::wlo);
-    if (tid < LB_MLP_W) w2s[tid] = __ldg(mlp + LB_MLP_W * LB_MLP_IN + tid);
+    // relu(h) = (h + |h|) / 2, so  sigma = e . v + sum_j (w2[j] / 2) |h_j|  with  v = W1^T w2 / 2: the linear half is a
+    // 32-term fp32 dot product on the staged row, the other half one FFMA per hidden unit (|h| is an operand modifier)
+    if (tid < LB_MLP_W) w2s[tid] = 0.5f * __ldg(mlp + LB_MLP_W * LB_MLP_IN + tid);
+    if (tid >= 64 && tid < 64 + LB_MLP_IN) {
+        const int k = tid - 64;
+        float a = 0.0f;
+        for (int j = 0; j < LB_MLP_W; ++j)
+            a = fmaf(0.5f * __ldg(mlp + LB_MLP_W * LB_MLP_IN + j), __ldg(mlp + j * LB_MLP_IN + k), a);
+        vs[k] = a;
+    }
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -332,6 +342,7 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
     constexpr uint32_t idesc = umma_idesc_tf32(128, LB_MLP_W);
 
     uint32_t parity = 0, buf = 0;
+    float lin = 0.0f;
     for (; tile < n_tiles; tile += gridDim.x, buf ^= 1u) {
         // the other staging tile was read (by its row owners) before the second barrier of the previous iteration
         const size_t next = tile + gridDim.x;
@@ -341,12 +352,16 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
         __syncthreads();                                               // every thread's copies of this tile have landed
         {   // row tid -> tf32 hi / lo -> TMEM lane tid (the previous tile's MMAs were waited on: A is free)
             const uint8_t* row = sm + FwdSmem::stage + buf * kStage + tid * kRowStride;
+            lin = 0.0f;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 uint32_t hi[16], lo[16];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const float4 v = *reinterpret_cast<const float4*>(row + (h * 4 + q) * 16);
+                    const float4 c = *reinterpret_cast<const float4*>(vs + (h * 4 + q) * 4);
+                    lin = fmaf(v.x, c.x, lin); lin = fmaf(v.y, c.y, lin);
+                    lin = fmaf(v.z, c.z, lin); lin = fmaf(v.w, c.w, lin);
                     uint4 a, b;
                     split_tf32(v, a, b);
                     hi[4 * q] = a.x; hi[4 * q + 1] = a.y; hi[4 * q + 2] = a.z; hi[4 * q + 3] = a.w;
@@ -376,23 +391,27 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
         mbar_wait(bar, parity);
         parity ^= 1;
         tc_fence_after();
-        // epilogue: thread t owns point tile*128 + t = TMEM lane t
-        float s = 0.0f;
+        // epilogue: thread t owns point tile*128 + t = TMEM lane t.  Everything per hidden unit runs on the FMA pipe:
+        // s += (w2/2) |h|;  on = sat(h * 2^126) in {0, 1} (h > 0, normal);  the mask is summed as a float, 16 bits at a time
+        float s = lin;
         unsigned long long bits = 0ull;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
             uint32_t r[32];
             tmem_ld32(t_h + lane_off + half * 32, r);
             tmem_ld_wait();
-            uint32_t m = 0;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const float h = __uint_as_float(r[j]);
-                const bool on = h > 0.0f;
-                s = fmaf(w2s[half * 32 + j], on ? h : 0.0f, s);
-                m |= on ? (1u << j) : 0u;
+            for (int g = 0; g < 2; ++g) {
+                float mf = 0.0f;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float h = __uint_as_float(r[g * 16 + j]);
+                    s = fmaf(w2s[half * 32 + g * 16 + j], fabsf(h), s);
+                    mf = fmaf(__saturatef(h * 8.507059173e37f), (float)(1u << j), mf);
+                }
+                const uint32_t m16 = __float_as_uint(mf + 8388608.0f) & 0xffffu;
+                bits |= (unsigned long long)m16 << (32 * half + 16 * g);
             }
-            bits |= (unsigned long long)m << (32 * half);
         }
         const size_t p = tile * (size_t)kTile + tid;
         if (p < n_points) {
