@@ -194,6 +194,34 @@ LB_API int lb_occ_grad(const float* rays, const float* z, const float* depth_gt,
                 int n_rays, int n_samples, int occ_dim, float* occ_grad, void* stream);
 LB_API int lb_sgd_step(float* p, float* g, int64_t n, float lr, int zero_grad, void* stream);
 
+/* ---- R4/R5 colour branch (decoupled RGB head) ------------------------------ */
+/* tcnn.Encoding(3, {otype: SphericalHarmonics, degree: 4}) (src/models/nerf_tcnn.py:43,86;
+ * cfg/nerf_config/default_nerf_hash.yaml:4-6): d01 [P,3] in [0,1] -> 16 real SH coefficients of 2*d01-1. */
+LB_API int lb_sh4_fwd(const float* d01, int64_t n_points, float* out, void* stream);
+/* input gradient of the above: d_d01 [P,3] = J^T d_out [P,16] */
+LB_API int lb_sh4_bwd(const float* d01, const float* d_out, int64_t n_points, float* d_d01, void* stream);
+/* tcnn.Network(n_in, n_out, {FullyFusedMLP, ReLU, n_neurons 64, n_hidden_layers}) forward
+ * (src/models/nerf_tcnn.py:50-52,89-91; default_nerf_hash.yaml:8-13), one fused tcgen05 kernel.
+ * x [P,n_in] with n_in in {16,32,48,64}; params in tcnn's layout: W0 [64,n_in], W1.. [64,64], W_out [16,64]
+ * (rows >= n_out unused), row-major, no bias.  out [P,n_out]; out_act 0 = none, 1 = sigmoid (the torch.sigmoid
+ * of nerf_tcnn.py:93 fused).  acts [n_hidden,P,64] receives the post-ReLU activations for lb_net_bwd; NULL
+ * for inference. */
+LB_API int lb_net_fwd(const float* x, int64_t n_points, int n_in, int n_hidden, int n_out, int out_act,
+               const float* params, float* out, float* acts, void* stream);
+/* backward of lb_net_fwd for upstream d_out [P,n_out] (`out` = forward output, needed when out_act = 1):
+ * grad_params += dL/dparams (NULL: skip), d_x [P,n_in] = dL/dx (NULL: skip). */
+LB_API int lb_net_bwd(const float* x, int64_t n_points, int n_in, int n_hidden, int n_out, int out_act,
+               const float* params, const float* acts, const float* out, const float* d_out,
+               float* grad_params, float* d_x, void* stream);
+/* colour lines of raw2outputs (src/models/rendering_tcnn.py:284-289): rgb [N,C] = sum_s weights[N,S] colors[N,S,C]
+ * (+ 1 - sum_s weights when white_bkgd); C <= 4. */
+LB_API int lb_composite_rgb_fwd(const float* weights, const float* colors, int n_rays, int n_samples, int n_colors,
+                         int white_bkgd, float* rgb, void* stream);
+/* its backward for upstream g_rgb [N,C]: d_weights [N,S] and d_colors [N,S,C] (either may be NULL) */
+LB_API int lb_composite_rgb_bwd(const float* weights, const float* colors, const float* g_rgb, int n_rays,
+                         int n_samples, int n_colors, int white_bkgd, float* d_weights, float* d_colors,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

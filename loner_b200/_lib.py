@@ -58,6 +58,12 @@ SIGNATURES = {
     "lb_adam_step": (_I, [_P, _P, _P, _P, _L, C.c_double, C.c_double, C.c_double, C.c_double, _I, _F, _I, _P]),
     "lb_occ_grad": (_I, [_P, _P, _P, _F, _I, _I, _I, _P, _P]),
     "lb_sgd_step": (_I, [_P, _P, _L, _F, _I, _P]),
+    "lb_sh4_fwd": (_I, [_P, _L, _P, _P]),
+    "lb_sh4_bwd": (_I, [_P, _P, _L, _P, _P]),
+    "lb_net_fwd": (_I, [_P, _L, _I, _I, _I, _I, _P, _P, _P, _P]),
+    "lb_net_bwd": (_I, [_P, _L, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
+    "lb_composite_rgb_fwd": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
+    "lb_composite_rgb_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
 }
 
 

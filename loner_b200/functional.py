@@ -157,3 +157,63 @@ class RenderLoss(torch.autograd.Function):
         ds = d_sigma * g_loss if d_sigma is not None else None
         dr = d_rays * g_loss if (ctx.need_rays and d_rays is not None) else None
         return ds, None, dr, None, None, None, None, None
+
+
+# ---- colour branch ----------------------------------------------------------------
+class SH4(torch.autograd.Function):
+    """tcnn SphericalHarmonics degree 4 (reference nerf_tcnn.py:43,86): d01 [P,3] -> [P,16]; grad: d01."""
+
+    @staticmethod
+    def forward(ctx, d01):
+        d = d01.detach().contiguous()
+        ctx.save_for_backward(d)
+        return ops.sh4_fwd(d)
+
+    @staticmethod
+    def backward(ctx, d_out):
+        (d,) = ctx.saved_tensors
+        return ops.sh4_bwd(d, d_out.contiguous()) if ctx.needs_input_grad[0] else None
+
+
+class FusedNetwork(torch.autograd.Function):
+    """tcnn.Network FullyFusedMLP (reference nerf_tcnn.py:50-52,89-91) with optional fused sigmoid (:93).
+    Forward on the tensor cores (lb_net_fwd); grads: params, x."""
+
+    @staticmethod
+    def forward(ctx, x, params, n_hidden, n_out, out_act):
+        x_c, p_c = x.detach().contiguous(), params.detach().contiguous()
+        need = x.requires_grad or params.requires_grad
+        out, acts = ops.net_fwd(x_c, p_c, n_hidden, n_out, out_act, save_acts=need)
+        ctx.cfg = (n_hidden, n_out, out_act)
+        ctx.need = (x.requires_grad, params.requires_grad)
+        if need:
+            ctx.save_for_backward(x_c, p_c, acts, out)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        x, params, acts, out = ctx.saved_tensors
+        n_hidden, n_out, out_act = ctx.cfg
+        need_x, need_p = ctx.need
+        gp = torch.zeros_like(params) if need_p else None
+        dx = ops.net_bwd(x, params, acts, out, d_out.contiguous(), n_hidden, n_out, out_act, grad_params=gp,
+                         need_dx=need_x)
+        return dx, gp, None, None, None
+
+
+class CompositeRGB(torch.autograd.Function):
+    """Colour lines of raw2outputs (reference rendering_tcnn.py:284-289); grads: weights, colors."""
+
+    @staticmethod
+    def forward(ctx, weights, colors, white_bkgd):
+        w, c = weights.detach().contiguous(), colors.detach().contiguous()
+        ctx.save_for_backward(w, c)
+        ctx.white = white_bkgd
+        return ops.composite_rgb_fwd(w, c, white_bkgd)
+
+    @staticmethod
+    def backward(ctx, g_rgb):
+        w, c = ctx.saved_tensors
+        dw, dc = ops.composite_rgb_bwd(w, c, g_rgb.contiguous(), ctx.white, ctx.needs_input_grad[0],
+                                       ctx.needs_input_grad[1])
+        return dw, dc, None

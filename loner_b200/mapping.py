@@ -15,6 +15,7 @@ from dataclasses import dataclass
 from typing import List, Optional
 
 import torch
+import torch.nn as nn
 
 from . import ops
 from ._lib import LonerB200Error
@@ -254,8 +255,6 @@ class Optimizer:
 
     def __init__(self, settings, calibration, world_cube, device, use_gt_poses=False, lidar_only=True,
                  enable_sky_segmentation=True, data_parallel: Optional[RayDataParallel] = None):
-        if not lidar_only:
-            raise LonerB200Error("Optimizer: the camera/RGB path is not built yet (SURVEY 8f row f2)")
         self._settings = settings
         self._calibration = calibration
         self._device = torch.device(device if not isinstance(device, int) else f"cuda:{device}")
@@ -358,6 +357,17 @@ class Optimizer:
         self._js_score, self._eps_dev = cat(5), cat(6)
         self._lidar_depths_gt_cube = depths
         return loss
+
+    def compute_loss_camera(self, camera_samples, lidar_samples, iteration_idx, override_enables=False, tracking=False):
+        """reference optimizer.py:861-894: L1 photometric loss of the colour branch on camera rays
+        (rays [N,13], intensities [N,num_colors]); sigma is evaluated under no_grad (detach_sigma)."""
+        camera_rays, camera_intensities = camera_samples[0], camera_samples[1]
+        camera_rays = camera_rays.reshape(-1, camera_rays.shape[-1])
+        self._results_camera = self._model(camera_rays, self._ray_sampler, self._scale_factor, camera=True,
+                                           return_variance=True)
+        self._camera_color_samples_fine = self._results_camera['rgb_fine'].reshape(-1, 1)
+        self._camera_intensities_gt = camera_intensities.reshape(-1, 1).to(self._camera_color_samples_fine)
+        return nn.functional.l1_loss(self._camera_color_samples_fine, self._camera_intensities_gt)
 
     @property
     def _lidar_depth_samples_fine(self):

@@ -17,7 +17,7 @@ import torch.nn as nn
 
 from . import ops, tcnn
 from ._lib import LonerB200Error
-from .functional import Composite, SigmaFromRays
+from .functional import Composite, CompositeRGB, SigmaFromRays
 
 
 class DecoupledNeRF(nn.Module):
@@ -61,7 +61,13 @@ class DecoupledNeRF(nn.Module):
         sigma = sigma.nan_to_num(posinf=self._max_float, neginf=self._min_float)
         if sigma_only:
             return sigma
-        raise LonerB200Error("intensity (RGB) branch is not built yet (SURVEY 8f row f2)")
+        # intensity head (nerf_tcnn.py:64,83-95): 2nd hash grid (+ SH-4 of the view direction) -> fused MLP; the
+        # torch.sigmoid of :93 runs in the network kernel's output epilogue
+        h = self._pos_encoding(pos)
+        if self._enable_view_dependence:
+            h = torch.cat([h, self._dir_encoding((dir + 1) / 2)], dim=-1)
+        color = self._model_intensity(h, out_act=ops.OUT_ACT["Sigmoid"])
+        return torch.cat([color, sigma], dim=-1)
 
 
 class OccupancyGridModel(nn.Module):
@@ -140,11 +146,9 @@ def raw2outputs(raw, z_vals, rays_d, raw_noise_std=0, white_bkgd=False, sigma_on
                 softplus=False, far=None, ret_var=False, rays=None):
     """src/models/rendering_tcnn.py:219-295 for sigma-only raw.  `rays` [N,13] may be passed instead of
     (rays_d, far) to avoid re-packing; gradients flow to sigma, rays_d (|d|) and far."""
-    if not sigma_only:
-        raise LonerB200Error("raw2outputs: colour compositing belongs to the RGB branch (not built yet)")
     if softplus:
         raise LonerB200Error("raw2outputs: softplus=True is never used by the reference path")
-    sigma = raw[..., 0]
+    sigma = raw[..., 0] if sigma_only else raw[..., num_colors]
     if rays is None:
         n = z_vals.shape[0]
         pad = torch.zeros(n, 3, device=z_vals.device, dtype=torch.float32)
@@ -154,7 +158,8 @@ def raw2outputs(raw, z_vals, rays_d, raw_noise_std=0, white_bkgd=False, sigma_on
     w, depth, opac, var = Composite.apply(sigma, z_vals, rays, noise)
     if far is None and rays_d is not None:
         depth = torch.sum(w * z_vals, -1)
-    return torch.tensor([-1.]), depth, w, opac, (var if ret_var else None)
+    rgb = torch.tensor([-1.]) if sigma_only else CompositeRGB.apply(w, raw[..., :num_colors], bool(white_bkgd))
+    return rgb, depth, w, opac, (var if ret_var else None)
 
 
 def raw2outputs_adjusted(raw, z_vals, rays_o, rays_d, raw_noise_std=0, white_bkgd=False, sigma_only=False,
@@ -162,9 +167,7 @@ def raw2outputs_adjusted(raw, z_vals, rays_o, rays_d, raw_noise_std=0, white_bkg
     """src/models/rendering_tcnn.py:70-214, effective semantics: noise forced to 0 (:104), depth = z at
     the sample where transmittance crosses 0.5 (:130-132) else 0; the peak/prominence write-backs
     (:196-199) hit a temporary copy in the reference and change nothing.  Inference only."""
-    if not sigma_only:
-        raise LonerB200Error("raw2outputs_adjusted: colour compositing belongs to the RGB branch (not built yet)")
-    sigma = raw[..., 0].detach().contiguous()
+    sigma = (raw[..., 0] if sigma_only else raw[..., num_colors]).detach().contiguous()
     if rays is None:
         n = z_vals.shape[0]
         pad = torch.zeros(n, 3, device=z_vals.device, dtype=torch.float32)
@@ -173,7 +176,8 @@ def raw2outputs_adjusted(raw, z_vals, rays_o, rays_d, raw_noise_std=0, white_bkg
         torch.randn(sigma.shape, device=sigma.device)
     w, depth, opac, var = ops.composite_fwd(sigma, z_vals.detach().contiguous(), rays.detach().contiguous(), None,
                                             "adjusted", True)
-    return torch.tensor([-1.]), depth, w, opac, (var if ret_var else None)
+    rgb = torch.tensor([-1.]) if sigma_only else CompositeRGB.apply(w, raw[..., :num_colors], bool(white_bkgd))
+    return rgb, depth, w, opac, (var if ret_var else None)
 
 
 def inference(model, xyz_, dir_, sigma_only=False, netchunk=32768, detach_sigma=True, meshing=False):
@@ -195,20 +199,24 @@ def render_rays(rays, ray_sampler, nerf_model, ray_range, scale_factor, N_sample
     The reference's NaN/inf prints (:419-424, eight host syncs per chunk) are dropped."""
     if render_strategy not in ('default', 'adjusted'):
         raise ValueError(f"Unknown render strategy: {render_strategy}")
-    if not sigma_only:
-        raise LonerB200Error("render_rays: the RGB branch (camera=True) is not built yet (SURVEY 8f row f2)")
     if netchunk != 0:
         raise LonerB200Error("render_rays: only netchunk == 0 is supported (reference bug at rendering_tcnn.py:327-330)")
     rays = rays.float()
     z_vals = ray_sampler.get_samples(rays, N_samples, perturb)
-    sigma = nerf_model.sigma_from_rays(rays, z_vals)
-    raw = sigma.unsqueeze(-1)
+    if sigma_only:
+        raw = nerf_model.sigma_from_rays(rays, z_vals).unsqueeze(-1)
+    else:
+        # camera rays (rendering_tcnn.py:387-392): colour + sigma per sample point through DecoupledNeRF.forward
+        xyz = rays[:, None, 0:3] + rays[:, None, 3:6] * z_vals.unsqueeze(2)
+        raw = inference(nerf_model, xyz, rays[:, 6:9], sigma_only=False, netchunk=0, detach_sigma=detach_sigma)
     if render_strategy == 'default':
         rgb, depth, weights, opacity, variance = raw2outputs(
-            raw, z_vals, None, raw_noise_std, white_bkgd, sigma_only=True, ret_var=return_variance, rays=rays)
+            raw, z_vals, None, raw_noise_std, white_bkgd, sigma_only=sigma_only, num_colors=num_colors,
+            ret_var=return_variance, rays=rays)
     else:
         rgb, depth, weights, opacity, variance = raw2outputs_adjusted(
-            raw, z_vals, None, None, raw_noise_std, white_bkgd, sigma_only=True, ret_var=return_variance, rays=rays)
+            raw, z_vals, None, None, raw_noise_std, white_bkgd, sigma_only=sigma_only, num_colors=num_colors,
+            ret_var=return_variance, rays=rays)
     result = {'rgb_fine': rgb, 'depth_fine': depth, 'weights_fine': weights, 'opacity_fine': opacity}
     if return_variance:
         result["variance"] = variance

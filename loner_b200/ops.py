@@ -249,3 +249,56 @@ def occ_grad(rays, z, depth_gt, scale_factor, occ_dim, out=None):
     _lib.call("lb_occ_grad", _p(rays, name="rays"), _p(z, name="z"), _p(depth_gt, name="depth_gt"), float(scale_factor),
               n, s, occ_dim, _p(out, name="occ_grad"), _stream())
     return out
+
+
+# ---- colour branch ----------------------------------------------------------------
+def sh4_fwd(d01):
+    P = d01.shape[0]
+    out = torch.empty(P, 16, device=d01.device, dtype=torch.float32)
+    _lib.call("lb_sh4_fwd", _p(d01, name="d01"), P, _p(out), _stream())
+    return out
+
+
+def sh4_bwd(d01, d_out):
+    P = d01.shape[0]
+    dx = torch.empty(P, 3, device=d01.device, dtype=torch.float32)
+    _lib.call("lb_sh4_bwd", _p(d01, name="d01"), _p(d_out, name="d_out"), P, _p(dx), _stream())
+    return dx
+
+
+OUT_ACT = {"None": 0, "none": 0, None: 0, "Sigmoid": 1, "sigmoid": 1}
+
+
+def net_fwd(x, params, n_hidden, n_out, out_act=0, save_acts=False):
+    """tcnn.Network forward: x [P, n_in] (n_in multiple of 16) -> out [P, n_out] (+ activations for the backward)."""
+    P, n_in = x.shape
+    out = torch.empty(P, n_out, device=x.device, dtype=torch.float32)
+    acts = torch.empty(n_hidden, P, 64, device=x.device, dtype=torch.float32) if save_acts else None
+    _lib.call("lb_net_fwd", _p(x, name="x"), P, n_in, n_hidden, n_out, out_act, _p(params, name="params"), _p(out),
+              _p(acts), _stream())
+    return out, acts
+
+
+def net_bwd(x, params, acts, out, d_out, n_hidden, n_out, out_act=0, grad_params=None, need_dx=False):
+    P, n_in = x.shape
+    dx = torch.empty(P, n_in, device=x.device, dtype=torch.float32) if need_dx else None
+    _lib.call("lb_net_bwd", _p(x, name="x"), P, n_in, n_hidden, n_out, out_act, _p(params, name="params"),
+              _p(acts, name="acts"), _p(out, name="out"), _p(d_out, name="d_out"), _p(grad_params), _p(dx), _stream())
+    return dx
+
+
+def composite_rgb_fwd(weights, colors, white_bkgd):
+    N, S, Cn = colors.shape
+    rgb = torch.empty(N, Cn, device=colors.device, dtype=torch.float32)
+    _lib.call("lb_composite_rgb_fwd", _p(weights, name="weights"), _p(colors, name="colors"), N, S, Cn,
+              1 if white_bkgd else 0, _p(rgb), _stream())
+    return rgb
+
+
+def composite_rgb_bwd(weights, colors, g_rgb, white_bkgd, need_dw=True, need_dc=True):
+    N, S, Cn = colors.shape
+    dw = torch.empty(N, S, device=colors.device, dtype=torch.float32) if need_dw else None
+    dc = torch.empty(N, S, Cn, device=colors.device, dtype=torch.float32) if need_dc else None
+    _lib.call("lb_composite_rgb_bwd", _p(weights, name="weights"), _p(colors, name="colors"), _p(g_rgb, name="g_rgb"),
+              N, S, Cn, 1 if white_bkgd else 0, _p(dw), _p(dc), _stream())
+    return dw, dc

@@ -19,7 +19,7 @@ import torch.nn as nn
 
 from . import ops
 from ._lib import LonerB200Error
-from .functional import HashEncode, SigmaFromPoints
+from .functional import FusedNetwork, HashEncode, SH4, SigmaFromPoints
 
 
 def _init_tables(n, gen):
@@ -90,23 +90,38 @@ class Encoding(nn.Module):
     def forward(self, x):
         if self.otype == "HashGrid":
             return HashEncode.apply(self.plan, self.params, x.float())
-        raise LonerB200Error("SphericalHarmonics forward belongs to the RGB branch (SURVEY 8f row f2): not built yet")
+        return SH4.apply(x.float())
 
 
 class Network(nn.Module):
-    """Fully fused MLP without input encoding (the intensity head; RGB branch)."""
+    """Fully fused MLP without input encoding (the intensity head of the RGB branch, nerf_tcnn.py:50-52):
+    n_input_dims (padded with ones to a multiple of 16, as tcnn does) -> 64 x n_hidden_layers -> n_output_dims."""
 
     def __init__(self, n_input_dims, n_output_dims, network_config, seed=1337):
         super().__init__()
+        if network_config.get("otype") != "FullyFusedMLP" or network_config.get("activation") != "ReLU" \
+                or int(network_config["n_neurons"]) != 64:
+            raise LonerB200Error(f"unsupported network config {dict(network_config)}")
+        out_act = str(network_config.get("output_activation"))
+        if out_act not in ("None", "Sigmoid"):
+            raise LonerB200Error(f"unsupported output_activation {out_act}")
         self.n_input_dims, self.n_output_dims = n_input_dims, n_output_dims
+        self.n_input_padded = _pad16(n_input_dims)
+        if self.n_input_padded > 64 or n_output_dims > 16:
+            raise LonerB200Error("Network: at most 64 inputs and 16 outputs")
+        self.out_act = ops.OUT_ACT[out_act]
         self.dtype = torch.float32
         self.seed = seed
         w = int(network_config["n_neurons"])
-        nh = int(network_config["n_hidden_layers"])
-        shapes = [(w, _pad16(n_input_dims))] + [(w, w)] * (nh - 1) + [(_pad16(n_output_dims), w)]
+        self.n_hidden = int(network_config["n_hidden_layers"])
+        shapes = [(w, self.n_input_padded)] + [(w, w)] * (self.n_hidden - 1) + [(_pad16(n_output_dims), w)]
         self.shapes = shapes
         g = torch.Generator().manual_seed(seed)
         self.params = nn.Parameter(_init_mlp(shapes, g))
 
-    def forward(self, x):
-        raise LonerB200Error("tcnn.Network forward belongs to the RGB branch (SURVEY 8f row f2): not built yet")
+    def forward(self, x, out_act=None):
+        x = x.float()
+        if x.shape[1] < self.n_input_padded:
+            x = torch.nn.functional.pad(x, (0, self.n_input_padded - x.shape[1]), value=1.0)
+        return FusedNetwork.apply(x, self.params, self.n_hidden, self.n_output_dims,
+                                  self.out_act if out_act is None else out_act)

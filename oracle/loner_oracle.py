@@ -217,6 +217,62 @@ def composite_adjusted(sigma, z, rays_d):
 
 
 # --------------------------------------------------------------------------------------------
+# R4/R5 colour branch  (src/models/nerf_tcnn.py:40-52,64,83-95; src/models/rendering_tcnn.py:284-289;
+#                       src/mapping/optimizer.py:861-894)
+# --------------------------------------------------------------------------------------------
+
+INTENSITY_MLP_CFG = dict(otype="FullyFusedMLP", activation="ReLU", output_activation="None",
+                         n_neurons=64, n_hidden_layers=4)       # default_nerf_hash.yaml:8-13
+
+
+def sh4(d01):
+    """tcnn SphericalHarmonics degree 4 on 2*d01-1 (nerf_tcnn.py:43,86)."""
+    return tcnn_shim.sh4(d01)
+
+
+def init_intensity_params(log2_hashmap_size=19, n_colors=3, seed=1337):
+    """(table_flat, mlp_flat) of the intensity head with the reference's module seeds (tcnn default 1337 each)."""
+    enc = tcnn_shim.Encoding(3, grid_cfg(log2_hashmap_size), seed=seed)
+    net = tcnn_shim.Network(48, n_colors, INTENSITY_MLP_CFG, seed=seed)
+    return enc.params.detach().clone(), net.params.detach().clone()
+
+
+def intensity_mlp(x, mlp_flat, n_in=48, n_out=3, cfg=None):
+    """tcnn.Network: n_in -> 64 x n_hidden -> n_out, ReLU, no bias, no output activation."""
+    return tcnn_shim._MLP(n_in, n_out, cfg or INTENSITY_MLP_CFG)(x, mlp_flat)
+
+
+def color_field(xyz, viewdirs, table_flat, mlp_flat, log2_hashmap_size=19, n_colors=3):
+    """Colour half of DecoupledNeRF.forward (nerf_tcnn.py:63-64,83-93): xyz [P,3] in [-1,1], viewdirs [P,3]."""
+    h_x = hash_encode((xyz + 1) / 2, table_flat, log2_hashmap_size)
+    h_d = sh4((viewdirs + 1) / 2)
+    return torch.sigmoid(intensity_mlp(torch.cat([h_x, h_d], -1), mlp_flat, 48, n_colors))
+
+
+def composite_rgb(weights, colors, white_bkgd=True):
+    """rendering_tcnn.py:284-289."""
+    rgb = torch.sum(weights.unsqueeze(-1) * colors, -2)
+    return rgb + 1 - weights.sum(-1, keepdim=True) if white_bkgd else rgb
+
+
+def camera_forward(rays, intensities, sigma_params, table_int, mlp_int, z, noise, log2_T_sigma, log2_T_int,
+                   n_colors=3, white_bkgd=True):
+    """Model.forward(camera=True, detach_sigma=True) + compute_loss_camera (model_tcnn.py:70-108,
+    rendering_tcnn.py:380-425, optimizer.py:861-894) at given sample depths z [N,S] and noise [N,S]."""
+    n, s = z.shape
+    xyz = rays[:, None, 0:3] + rays[:, None, 3:6] * z.unsqueeze(2)
+    with torch.no_grad():                                        # nerf_tcnn.py:66-69
+        sigma = sigma_field(xyz.reshape(-1, 3), sigma_params, log2_T_sigma).view(n, s)
+    dirs = torch.repeat_interleave(rays[:, 6:9], repeats=s, dim=0)
+    col = color_field(xyz.reshape(-1, 3), dirs, table_int, mlp_int, log2_T_int, n_colors).view(n, s, n_colors)
+    out = composite(sigma, z, rays[:, 3:6], rays[:, -1:], noise)
+    rgb = composite_rgb(out["weights"], col, white_bkgd)
+    loss = F.l1_loss(rgb.reshape(-1, 1), intensities.reshape(-1, 1))
+    out.update(rgb=rgb, colors=col, sigma=sigma, loss=loss)
+    return out
+
+
+# --------------------------------------------------------------------------------------------
 # L1-L4: JS dynamic-margin depth loss  (src/mapping/optimizer.py:701-859, src/models/losses.py:29-51)
 # --------------------------------------------------------------------------------------------
 

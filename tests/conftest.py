@@ -32,3 +32,14 @@ def golden_params(g):
     p[O.MLP_PARAMS:] *= g["table_scale"]
     assert abs(p.double().sum().item() - g["params_checksum"]) < 1e-6 * max(1.0, abs(g["params_checksum"]))
     return p
+
+
+def golden_rgb_params(g):
+    """(sigma params, intensity table, intensity MLP) an rgb golden fixture was generated with."""
+    from oracle import loner_oracle as O
+    p = golden_params(g)
+    table, mlp = O.init_intensity_params(g["log2_T_int"], 3, g["param_seed"])
+    table = table * g["table_scale"]
+    assert abs(table.double().sum().item() - g["table_int_checksum"]) < 1e-6 * max(1.0, abs(g["table_int_checksum"]))
+    assert abs(mlp.double().sum().item() - g["mlp_int_checksum"]) < 1e-6 * max(1.0, abs(g["mlp_int_checksum"]))
+    return p, table, mlp

@@ -340,3 +340,85 @@ def test_build_lidar_rays_matches_oracle(far_clip, dev, O):
     srays, sdepths = M.build_lidar_rays(dirs.to(dev), None, pd.detach(), wc, (1.0, 50.0), False, indices=idx.to(dev),
                                         const_depth=51.0)
     assert torch.equal(srays, rays.detach()) and torch.allclose(sdepths, torch.full_like(sdepths, 51.0 / float(scale)))
+
+
+# ---- colour branch ---------------------------------------------------------------
+def test_sh4_matches_oracle():
+    from loner_b200 import ops
+    from oracle import loner_oracle as O
+    torch.manual_seed(5)
+    d01 = torch.rand(4099, 3)
+    ref_in = d01.clone().requires_grad_(True)
+    ref = O.sh4(ref_in)
+    out = ops.sh4_fwd(d01.to("cuda:0"))
+    assert rel_err(out, ref) < 1e-6
+    g = torch.randn(4099, 16)
+    ref.backward(g)
+    dx = ops.sh4_bwd(d01.to("cuda:0"), g.to("cuda:0"))
+    assert rel_err(dx, ref_in.grad) < 1e-5
+
+
+def _mlp_ref(x, params, n_in, n_hidden, n_out, sigmoid):
+    """fp64 evaluation of tcnn.Network (layout as oracle/tinycudann._MLP).  Also returns, per point, the smallest
+    |pre-activation| relative to sum|w||h_prev| over all hidden units: points below ~1e-5 sit on a ReLU tie that
+    fp32 / tf32-split arithmetic may resolve the other way, which changes that point's gradient by O(1)."""
+    off, h = 0, x.double()
+    shapes = [(64, n_in)] + [(64, 64)] * (n_hidden - 1) + [(16, 64)]
+    margin = torch.full((x.shape[0],), float("inf"), dtype=torch.float64)
+    for li, (o, i) in enumerate(shapes):
+        W = params[off:off + o * i].view(o, i).double()
+        off += o * i
+        pre = h @ W.t()
+        if li < len(shapes) - 1:
+            scale = (h.abs() @ W.abs().t()).clamp_min(1e-30)
+            margin = torch.minimum(margin, (pre.abs() / scale).min(dim=1).values.detach())
+            h = torch.relu(pre)
+        else:
+            h = pre
+    h = h[:, :n_out]
+    return (torch.sigmoid(h) if sigmoid else h), margin
+
+
+@pytest.mark.parametrize("P,n_in,n_hidden,n_out,act", [(1, 48, 4, 3, 1), (127, 48, 4, 3, 1), (129, 32, 1, 1, 0),
+                                                       (5000, 16, 2, 16, 0), (33000, 64, 4, 4, 1), (777, 32, 6, 2, 0), (70001, 48, 4, 3, 0)])
+def test_fused_network_matches_fp64(P, n_in, n_hidden, n_out, act):
+    """tcnn.Network forward (tcgen05, tf32 hi/lo 3-pass) and backward (fp32 tiles) vs an fp64 evaluation."""
+    from loner_b200 import ops
+    torch.manual_seed(P)
+    n_params = 64 * n_in + (n_hidden - 1) * 64 * 64 + 16 * 64
+    params = (torch.rand(n_params) * 2 - 1) * 0.3
+    x = torch.randn(P, n_in) * 0.5
+    pr = params.clone().requires_grad_(True)
+    xr = x.clone().requires_grad_(True)
+    ref, margin = _mlp_ref(xr, pr, n_in, n_hidden, n_out, act == 1)
+    out, acts = ops.net_fwd(x.to("cuda:0"), params.to("cuda:0"), n_hidden, n_out, act, save_acts=True)
+    assert rel_err(out, ref) < 1e-5          # tf32 hi/lo 3-pass: ~2^-21 per layer
+    out_inf, none = ops.net_fwd(x.to("cuda:0"), params.to("cuda:0"), n_hidden, n_out, act, save_acts=False)
+    assert none is None and torch.equal(out_inf, out)
+    g = torch.randn(P, n_out) * (margin > 1e-5).float()[:, None]      # no upstream gradient at ReLU ties
+    ref.backward(g.double())
+    gp = torch.zeros(n_params, device="cuda:0")
+    dx = ops.net_bwd(x.to("cuda:0"), params.to("cuda:0"), acts, out, g.to("cuda:0"), n_hidden, n_out, act, grad_params=gp, need_dx=True)
+    assert rel_err(gp, pr.grad) < 1e-4
+    assert rel_err(dx, xr.grad) < 1e-4
+    used_out = n_out * 64
+    out_off = n_params - 16 * 64
+    assert (gp[out_off + used_out:] == 0).all()          # padded output rows get no gradient
+
+
+def test_composite_rgb_matches_oracle():
+    from loner_b200 import ops
+    from oracle import loner_oracle as O
+    torch.manual_seed(9)
+    N, S = 301, 64
+    w = (torch.rand(N, S) / S).requires_grad_(True)
+    col = torch.rand(N, S, 3).requires_grad_(True)
+    for white in (True, False):
+        ref = O.composite_rgb(w, col, white)
+        out = ops.composite_rgb_fwd(w.detach().to("cuda:0"), col.detach().to("cuda:0"), white)
+        assert rel_err(out, ref) < 1e-5
+        g = torch.randn(N, 3)
+        w.grad = col.grad = None
+        ref.backward(g)
+        dw, dc = ops.composite_rgb_bwd(w.detach().to("cuda:0"), col.detach().to("cuda:0"), g.to("cuda:0"), white)
+        assert rel_err(dw, w.grad) < 1e-5 and rel_err(dc, col.grad) < 1e-5

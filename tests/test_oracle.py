@@ -137,3 +137,26 @@ def test_level_table_matches_survey_counts():
         assert entries * 2 == n
         assert [l["res"] for l in lv[:3]] == [16, 32, 64]
         assert lv[0]["dense"] and lv[1]["dense"]
+
+
+def test_colour_branch_against_reference():
+    """Oracle colour field, colour compositing and camera L1 loss + gradients vs the reference's own
+    Model.forward(camera=True) / compute_loss_camera run (tests/golden/rgb_camera.pt)."""
+    from conftest import golden_rgb_params
+    g = load_golden("rgb_camera")
+    p, table, mlp = golden_rgb_params(g)
+    table.requires_grad_(True)
+    mlp.requires_grad_(True)
+    rays = g["rays"].clone().requires_grad_(True)
+    assert torch.equal(O.sample_uniform(g["rays"], g["u1"], g["n_samples"], 1.0), g["z"])
+    out = O.camera_forward(rays, g["intensities"], p, table, mlp, g["z"], g["noise"], g["log2_T"], g["log2_T_int"])
+    torch.testing.assert_close(out["colors"].detach(), g["raw"][..., :3], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(out["sigma"], g["raw"][..., 3], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(out["rgb"].detach(), g["rgb"], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(out["loss"].detach(), g["loss"], rtol=1e-5, atol=1e-7)
+    out["loss"].backward()
+    torch.testing.assert_close(mlp.grad, g["mlp_int_grad"], rtol=1e-4, atol=1e-8)
+    torch.testing.assert_close(table.grad[g["table_int_grad_idx"]], g["table_int_grad_val"], rtol=1e-4, atol=1e-9)
+    assert abs(table.grad.double().norm().item() - g["table_int_grad_norm"]) < 1e-4 * g["table_int_grad_norm"]
+    torch.testing.assert_close(rays.grad, g["rays_grad"], rtol=1e-4, atol=1e-7)
+    assert g["sigma_grad_is_none"]          # detach_sigma=True: the camera loss does not touch the sigma head
