@@ -204,8 +204,8 @@ LB_API int lb_sh4_bwd(const float* d01, const float* d_out, int64_t n_points, fl
  * (src/models/nerf_tcnn.py:50-52,89-91; default_nerf_hash.yaml:8-13), one fused tcgen05 kernel.
  * x [P,n_in] with n_in in {16,32,48,64}; params in tcnn's layout: W0 [64,n_in], W1.. [64,64], W_out [16,64]
  * (rows >= n_out unused), row-major, no bias.  out [P,n_out]; out_act 0 = none, 1 = sigmoid (the torch.sigmoid
- * of nerf_tcnn.py:93 fused).  acts [n_hidden,P,64] receives the post-ReLU activations for lb_net_bwd; NULL
- * for inference. */
+ * of nerf_tcnn.py:93 fused).  acts receives the post-ReLU activations for lb_net_bwd (NULL for inference):
+ * n_hidden * ceil(P/128)*128 * 64 floats in a tile-transposed layout private to the two kernels. */
 LB_API int lb_net_fwd(const float* x, int64_t n_points, int n_in, int n_hidden, int n_out, int out_act,
                const float* params, float* out, float* acts, void* stream);
 /* backward of lb_net_fwd for upstream d_out [P,n_out] (`out` = forward output, needed when out_act = 1):

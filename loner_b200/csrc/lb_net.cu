@@ -69,6 +69,18 @@ __device__ __forceinline__ size_t layer_param_off(const NetShape& s, int l) {
     return l == 0 ? 0 : (size_t)kW * s.n_in + (size_t)(l - 1) * kW * kW;
 }
 
+// activation tile written by lb_net_fwd: [16-byte chunk q of the 64-wide row][row r] float4 -> shared tile [r][q]
+__device__ __forceinline__ void load_act_tile(const float* __restrict__ acts, size_t layer, size_t n_tiles, size_t tile,
+                                              int valid_rows, float* dst) {
+    const float4* src = reinterpret_cast<const float4*>(acts) + (layer * n_tiles + tile) * (size_t)(kT * 16);
+    for (int it = threadIdx.x; it < kT * 16; it += kBwdThreads) {
+        const int q = it / kT, r = it - q * kT;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < valid_rows) v = __ldg(src + it);
+        *reinterpret_cast<float4*>(dst + r * kLd + q * 4) = v;
+    }
+}
+
 // rows x cols fp32 (row-major, leading dimension ld_src) -> shared tile (leading dimension kLd); rows beyond
 // `valid_rows` are zero
 __device__ __forceinline__ void load_tile_f4(const float* __restrict__ src, size_t ld_src, int rows, int cols,
@@ -116,7 +128,7 @@ net_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x, co
             }
             sDO[it] = g;
         }
-        load_tile_f4(acts + ((size_t)(s.n_hidden - 1) * n_points + p0) * kW, kW, kT, kW, valid, sH);
+        load_act_tile(acts, (size_t)(s.n_hidden - 1), n_tiles, tile, valid, sH);
         load_tile_f4(params + out_off, kW, kOutPad, kW, kOutPad, sW);
         __syncthreads();
         // dW_out[c, j] += sum_p dZo[p, c] H[p, j]
@@ -137,7 +149,7 @@ net_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x, co
         for (int l = s.n_hidden - 1; l >= 0; --l) {
             const int K = l == 0 ? s.n_in : kW;
             __syncthreads();                  // sDZ complete; sH / sW no longer read
-            if (l > 0) load_tile_f4(acts + ((size_t)(l - 1) * n_points + p0) * kW, kW, kT, kW, valid, sH);
+            if (l > 0) load_act_tile(acts, (size_t)(l - 1), n_tiles, tile, valid, sH);
             else load_tile_f4(x + p0 * s.n_in, s.n_in, kT, K, valid, sH);
             load_tile_f4(params + layer_param_off(s, l), K, kW, K, kW, sW);
             __syncthreads();

@@ -5,8 +5,8 @@
 // `torch.sigmoid` (reference src/models/nerf_tcnn.py:50-52,86-93; cfg/nerf_config/default_nerf_hash.yaml:8-13).
 // Weight layout = tcnn's: W0 [64, n_in], W1.. [64, 64], W_out [16, 64] (output rows padded to 16), row-major, no bias.
 //
-// Design.  One CTA per SM, two independent warpgroups of 128 threads; each warpgroup walks its own 128-point
-// tiles (UMMA M = 128) and thread t owns point (TMEM lane) t of the tile:
+// Design.  One CTA of 512 threads per SM = two independent groups of 8 warps; each group walks its own 128-point
+// tiles (UMMA M = 128); thread (t, half) owns point (TMEM lane) t and one 32-column half of its rows:
 //   * the input tile x[128, n_in] is staged with cp.async (coalesced, padded rows); thread t reads row t, splits
 //     it exactly into tf32 hi / lo and writes both to tensor memory (tcgen05.st) -- the A operand of every layer
 //     lives in TMEM, only the weights (B, hi / lo tiles resident in shared memory for all layers) are read from
@@ -16,7 +16,7 @@
 //     optionally streams the activation row to global memory for the backward pass, splits it and writes it back
 //     to TMEM as the next layer's A operand;
 //   * the output layer is one N = 16 MMA group; its epilogue applies the optional sigmoid and stores n_out values.
-// While one warpgroup runs an epilogue the other one's MMAs occupy the tensor pipe.
+// While one group runs an epilogue the other one's MMAs occupy the tensor pipe.
 #include "lb_common.cuh"
 #include "lb_umma.cuh"
 
@@ -25,8 +25,8 @@ namespace {
 using namespace lb_umma;
 
 constexpr int kTile = 128;
-constexpr int kGroupThreads = 128;
-constexpr int kThreads = 256;
+constexpr int kGroupThreads = 256;      // 8 warps: two column halves per TMEM lane
+constexpr int kThreads = 512;
 constexpr int kWidth = 64;
 constexpr int kOutPad = 16;
 constexpr uint32_t kLboW = kWidth * 16 + 16;       // chunk stride of a 64-row weight tile
@@ -91,7 +91,7 @@ __device__ __forceinline__ void stage_input(const float* __restrict__ x, size_t 
     const float4* base = reinterpret_cast<const float4*>(x) + tile * (size_t)(kTile * kChunks);
     const size_t first = tile * (size_t)kTile;
 #pragma unroll
-    for (int i = 0; i < kChunks; ++i) {
+    for (int i = 0; i < (kTile * kChunks) / kGroupThreads; ++i) {
         const int idx = i * kGroupThreads + gtid;
         const int row = idx / kChunks, q = idx - row * kChunks;
         const bool ok = first + row < n_points;
@@ -118,7 +118,10 @@ net_fwd_umma_kernel(const float* __restrict__ params, const float* __restrict__ 
     extern __shared__ __align__(128) uint8_t sm[];
     constexpr uint32_t kRow = kIn * 4 + 16;
     constexpr uint32_t kStage = kTile * kRow;
-    const int tid = threadIdx.x, group = tid >> 7, gtid = tid & 127, warp = tid >> 5;
+    // group = one 128-point tile stream; inside a group, thread (lane_t, half) owns TMEM lane lane_t and the column
+    // half `half` of every 64-wide row (warps w and w + 4 of a group reach the same 32 TMEM lanes)
+    const int tid = threadIdx.x, group = tid / kGroupThreads, gtid = tid % kGroupThreads, warp = tid >> 5;
+    const int lane_t = gtid & 127, half = gtid >> 7;
     const uint32_t piece = weight_piece_bytes(kIn, shape.n_hidden);
     // carve-up: [hi piece][lo piece][stage g0][stage g1][2 mbarriers][tmem slot]
     uint8_t* w_hi = sm;
@@ -152,9 +155,10 @@ net_fwd_umma_kernel(const float* __restrict__ params, const float* __restrict__ 
         cp_async_wait<0>();
         group_barrier(group);                                          // the staged input tile is complete
         {
-            const uint8_t* row = stage + gtid * kRow;
+            const uint8_t* row = stage + lane_t * kRow;
 #pragma unroll
             for (int c = 0; c < kIn / 16; ++c) {
+                if ((c & 1) != half) continue;                          // 16-column chunks alternate between the halves
                 float v[16];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -170,7 +174,7 @@ net_fwd_umma_kernel(const float* __restrict__ params, const float* __restrict__ 
         if (tile + stride < n_tiles) stage_input<kIn>(x, tile + stride, n_points, smem_u32(stage), gtid);
         cp_async_commit();
 
-        const size_t p = tile * (size_t)kTile + gtid;
+        const size_t p = tile * (size_t)kTile + lane_t;
         for (int l = 0; l <= shape.n_hidden; ++l) {
             const bool last = l == shape.n_hidden;
             if (gtid == 0) {
@@ -192,38 +196,41 @@ net_fwd_umma_kernel(const float* __restrict__ params, const float* __restrict__ 
             parity ^= 1;
             tc_fence_after();
             if (!last) {
-                // hidden layer epilogue: ReLU, optional activation stream-out, next A operand
-                float* act_row = acts ? acts + ((size_t)l * n_points + p) * kWidth : nullptr;
+                // hidden layer epilogue on this thread's 32 columns: ReLU, optional activation stream-out (tile-transposed
+                // layout [layer][tile][16-byte chunk][row]: a warp store covers 512 contiguous bytes), next A operand
+                uint32_t r[32];
+                tmem_ld32(t_acc + lane_off + half * 32, r);
+                tmem_ld_wait();
+                float4* act_tile = acts ? reinterpret_cast<float4*>(acts) + ((size_t)l * n_tiles + tile) * (kTile * 16) : nullptr;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t r[16];
-                    tmem_ld16(t_acc + lane_off + c * 16, r);
-                    tmem_ld_wait();
+                for (int c = 0; c < 2; ++c) {
                     float v[16];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = fmaxf(__uint_as_float(r[i]), 0.0f);
-                    if (act_row && p < n_points) {
+                    for (int i = 0; i < 16; ++i) v[i] = fmaxf(__uint_as_float(r[c * 16 + i]), 0.0f);
+                    if (act_tile) {
 #pragma unroll
                         for (int q = 0; q < 4; ++q)
-                            *reinterpret_cast<float4*>(act_row + c * 16 + q * 4) =
+                            act_tile[(half * 8 + c * 4 + q) * kTile + lane_t] =
                                 make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
                     }
-                    put_a16(v, t_ahi + lane_off + c * 16, t_alo + lane_off + c * 16);
+                    put_a16(v, t_ahi + lane_off + half * 32 + c * 16, t_alo + lane_off + half * 32 + c * 16);
                 }
                 tmem_st_wait();
                 tc_fence_before();
                 group_barrier(group);
             } else {
-                uint32_t r[16];
-                tmem_ld16(t_acc + lane_off, r);
-                tmem_ld_wait();
-                if (p < n_points) {
+                if (half == 0) {
+                    uint32_t r[16];
+                    tmem_ld16(t_acc + lane_off, r);
+                    tmem_ld_wait();
+                    if (p < n_points) {
 #pragma unroll
-                    for (int i = 0; i < kOutPad; ++i) {
-                        if (i < shape.n_out) {
-                            float o = __uint_as_float(r[i]);
-                            if (shape.out_act == 1) o = 1.0f / (1.0f + expf(-o));
-                            out[p * shape.n_out + i] = o;
+                        for (int i = 0; i < kOutPad; ++i) {
+                            if (i < shape.n_out) {
+                                float o = __uint_as_float(r[i]);
+                                if (shape.out_act == 1) o = 1.0f / (1.0f + expf(-o));
+                                out[p * shape.n_out + i] = o;
+                            }
                         }
                     }
                 }

@@ -273,7 +273,8 @@ def net_fwd(x, params, n_hidden, n_out, out_act=0, save_acts=False):
     """tcnn.Network forward: x [P, n_in] (n_in multiple of 16) -> out [P, n_out] (+ activations for the backward)."""
     P, n_in = x.shape
     out = torch.empty(P, n_out, device=x.device, dtype=torch.float32)
-    acts = torch.empty(n_hidden, P, 64, device=x.device, dtype=torch.float32) if save_acts else None
+    # activations in the kernels' tile-transposed layout [layer][tile of 128 points][16-byte chunk][row]
+    acts = torch.empty(n_hidden, (P + 127) // 128 * 128, 64, device=x.device, dtype=torch.float32) if save_acts else None
     _lib.call("lb_net_fwd", _p(x, name="x"), P, n_in, n_hidden, n_out, out_act, _p(params, name="params"), _p(out),
               _p(acts), _stream())
     return out, acts

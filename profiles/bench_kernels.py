@@ -75,3 +75,14 @@ timeit("adam_step", lambda: ops.adam_step(params, gp, m, v, 1, 0.0), None)
 timeit("occ_grad", lambda: ops.occ_grad(rays, z, depths, float(scale), 100), 76)
 timeit("torch randn [N,S]", lambda: torch.randn(N, S, device=dev))
 timeit("torch zeros_like(params)", lambda: torch.zeros_like(params))
+# colour branch: 48 -> 64 x 4 -> 3 network on the same point count
+net_params = ((torch.rand(64 * 48 + 3 * 64 * 64 + 16 * 64) * 2 - 1) * 0.2).to(dev)
+xin = torch.randn(P, 48, device=dev) * 0.3
+d01 = torch.rand(P, 3, device=dev)
+timeit("sh4_fwd", lambda: ops.sh4_fwd(d01), 12 + 64)
+timeit("net_fwd 48-64x4-3 (inference)", lambda: ops.net_fwd(xin, net_params, 4, 3, 1), 192 + 12)
+out_n, acts_n = ops.net_fwd(xin, net_params, 4, 3, 1, save_acts=True)
+timeit("net_fwd 48-64x4-3 (+ save acts)", lambda: ops.net_fwd(xin, net_params, 4, 3, 1, save_acts=True), 192 + 12 + 1024)
+g_out = torch.randn(P, 3, device=dev)
+gnp = torch.zeros_like(net_params)
+timeit("net_bwd 48-64x4-3 (params + dx)", lambda: ops.net_bwd(xin, net_params, acts_n, out_n, g_out, 4, 3, 1, grad_params=gnp, need_dx=True), 192 * 2 + 12 + 1024, reps=2)
