@@ -73,9 +73,15 @@ extern "C" int lb_plan_create(const lb_grid_config* cfg, lb_plan** out) {
     p->n_mlp_params = LB_MLP_W * (cfg->n_levels * LB_FEATS) + LB_MLP_OUT_PAD * LB_MLP_W;
     int dev = 0;
     p->sm_count = 148;
+    p->l2_bytes = 126ll << 20;
     if (cudaGetDevice(&dev) == cudaSuccess) {
-        int sm = 0;
+        int sm = 0, l2 = 0;
         if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sm > 0) p->sm_count = sm;
+        if (cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, dev) == cudaSuccess && l2 > 0) p->l2_bytes = l2;
+    }
+    if (const char* e = getenv("LONER_B200_L2_BYTES")) {   // tests force level-group passes on small tables
+        const long long v = atoll(e);
+        if (v > 0) p->l2_bytes = v;
     }
     cudaGetLastError();  // plan creation must work without a device (host-only tests)
     *out = p;

@@ -34,6 +34,7 @@ struct lb_plan {
     int64_t        n_table_entries;   // float2 entries over all levels
     int64_t        n_mlp_params;
     int            sm_count;
+    int64_t        l2_bytes;          // device L2 size (level-group passes for tables that do not fit, lb_encode.cu)
 };
 
 void lb_set_error(const char* fmt, ...);

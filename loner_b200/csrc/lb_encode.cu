@@ -31,7 +31,7 @@ __device__ __forceinline__ Point load_point(const float* __restrict__ rays, cons
     if (kFromRays) {
         const uint32_t r = (uint32_t)p / (uint32_t)n_samples;     // P < 2^32 (checked by the launchers)
         const float* ray = rays + (size_t)r * LB_RAY_STRIDE;
-        const float z = __ldg(zv + p);
+        const float z = __ldcs(zv + p);                            // use-once stream: evict-first, the tables keep the L2
         // same roundings as the reference's torch ops (o + d*z, then (xyz+1)/2): at the finest level one
         // ulp of x01 is 3 % of a cell, so the sample position must match bit for bit
         q.x = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 0), __fmul_rn(__ldg(ray + 3), z)), 1.0f), 0.5f);
@@ -39,9 +39,9 @@ __device__ __forceinline__ Point load_point(const float* __restrict__ rays, cons
         q.z = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 2), __fmul_rn(__ldg(ray + 5), z)), 1.0f), 0.5f);
         if (z_out) *z_out = z;
     } else {
-        q.x = __ldg(x01 + 3 * p + 0);
-        q.y = __ldg(x01 + 3 * p + 1);
-        q.z = __ldg(x01 + 3 * p + 2);
+        q.x = __ldcs(x01 + 3 * p + 0);
+        q.y = __ldcs(x01 + 3 * p + 1);
+        q.z = __ldcs(x01 + 3 * p + 2);
     }
     return q;
 }
@@ -108,7 +108,7 @@ template <bool kFromRays, int kNDense>
 __global__ void __launch_bounds__(kThreads, 8)
 encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
                   const float* __restrict__ x01, const float2* __restrict__ table, size_t n_points, int n_samples,
-                  float* __restrict__ enc) {
+                  float* __restrict__ enc, int l_begin, int l_end) {
     const int half = threadIdx.x & 1;
     const int width = T.n_levels * LB_FEATS;
     const size_t n_tiles = (n_points + kPointsPerBlock - 1) / kPointsPerBlock;
@@ -121,7 +121,7 @@ encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
 #pragma unroll
         for (int l = 0; l < 16; ++l) {
             float a = 0.0f, b = 0.0f;
-            if (l < T.n_levels) {
+            if (l >= l_begin && l < l_end) {                       // level-group pass (whole range when the tables fit L2)
                 const lb_level& L = T.lv[l];
                 const Side s = locate_side<kNDense>(L, q, half, l);
                 float2 v[4];
@@ -149,13 +149,19 @@ encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
         }
         if (valid) {
             if (width == LB_MLP_IN) {
+                // one float4 = two levels; a pass stores only its own columns (passes start on even levels)
                 float4* dst = reinterpret_cast<float4*>(enc + p * LB_MLP_IN + half * 16);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) dst[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
+                for (int i = 0; i < 4; ++i) {
+                    const int l0 = 2 * (half * 4 + i);
+                    if (l0 >= l_begin && l0 < l_end) __stcs(dst + i, make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]));
+                }
             } else {
 #pragma unroll
-                for (int i = 0; i < 16; ++i)
-                    if (half * 16 + i < width) enc[p * width + half * 16 + i] = out[i];
+                for (int i = 0; i < 16; ++i) {
+                    const int c = half * 16 + i;
+                    if (c < width && c >= 2 * l_begin && c < 2 * l_end) enc[p * width + c] = out[i];
+                }
             }
         }
     }
@@ -184,7 +190,7 @@ __global__ void __launch_bounds__(kThreads, 6)
 encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
                   const float* __restrict__ x01, const float2* __restrict__ table, const float* __restrict__ d_enc,
                   size_t n_points, int n_samples, float* __restrict__ grad_table, float* __restrict__ d_rays,
-                  float* __restrict__ d_x01) {
+                  float* __restrict__ d_x01, int l_begin, int l_end) {
     const int lane = threadIdx.x & 31;
     const int half = lane & 1;
     const int pair = lane >> 1;
@@ -202,12 +208,14 @@ encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
                 const float4* src = reinterpret_cast<const float4*>(d_enc + p * LB_MLP_IN);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    const float4 v = __ldg(src + i);
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (2 * i >= l_begin && 2 * i < l_end) v = __ldcs(src + i);    // only this pass's levels; use-once stream
                     de[4 * i] = v.x; de[4 * i + 1] = v.y; de[4 * i + 2] = v.z; de[4 * i + 3] = v.w;
                 }
             } else {
 #pragma unroll
-                for (int i = 0; i < LB_MLP_IN; ++i) de[i] = (i < width) ? __ldg(d_enc + p * width + i) : 0.0f;
+                for (int i = 0; i < LB_MLP_IN; ++i)
+                    de[i] = (i < width && i >= 2 * l_begin && i < 2 * l_end) ? __ldg(d_enc + p * width + i) : 0.0f;
             }
         } else {
 #pragma unroll
@@ -221,14 +229,14 @@ encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
         for (int i = 0; i < LB_MLP_IN; ++i) nz_bits |= __float_as_uint(de[i]);
         const bool nonzero = (nz_bits << 1) != 0u;
         if (__all_sync(kFull, !nonzero)) {                             // warp-uniform: nothing to scatter for these 16 points
-            if (kInputGrad && !kFromRays && valid && !half) { d_x01[3 * p + 0] = 0.0f; d_x01[3 * p + 1] = 0.0f; d_x01[3 * p + 2] = 0.0f; }
+            if (kInputGrad && !kFromRays && valid && !half && l_begin == 0) { d_x01[3 * p + 0] = 0.0f; d_x01[3 * p + 1] = 0.0f; d_x01[3 * p + 2] = 0.0f; }
             continue;
         }
         float gx = 0.0f, gy = 0.0f, gz = 0.0f;
         bool all_distinct = false;     // once a level has 16 distinct cells, finer levels do too
 #pragma unroll
         for (int l = 0; l < 16; ++l) {
-            if (l >= T.n_levels) continue;
+            if (l < l_begin || l >= l_end) continue;
             const lb_level& L = T.lv[l];
             const Side s = locate_side<kNDense>(L, q, half, l);
             const float d0 = de[2 * l], d1 = de[2 * l + 1];
@@ -316,7 +324,11 @@ encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
                     for (int i = 0; i < 6; ++i) atomicAdd(d_rays + ray * LB_RAY_STRIDE + i, v[i]);
                 }
             } else if (valid && !half) {
-                d_x01[3 * p + 0] = gx; d_x01[3 * p + 1] = gy; d_x01[3 * p + 2] = gz;
+                if (l_begin == 0) {
+                    d_x01[3 * p + 0] = gx; d_x01[3 * p + 1] = gy; d_x01[3 * p + 2] = gz;
+                } else {                                   // later level-group passes accumulate
+                    d_x01[3 * p + 0] += gx; d_x01[3 * p + 1] += gy; d_x01[3 * p + 2] += gz;
+                }
             }
         }
     }
@@ -339,23 +351,44 @@ int dense_prefix(const lb_plan* plan) {
 
 template <int kNDense>
 void launch_fwd(const lb_level_table& T, int grid, const float* rays, const float* z, const float* x01, const float2* tb,
-                size_t n_points, int n_samples, float* enc, cudaStream_t st) {
-    if (rays) encode_fwd_kernel<true, kNDense><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, n_points, n_samples, enc);
-    else encode_fwd_kernel<false, kNDense><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, n_points, 1, enc);
+                size_t n_points, int n_samples, float* enc, int l0, int l1, cudaStream_t st) {
+    if (rays) encode_fwd_kernel<true, kNDense><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, n_points, n_samples, enc, l0, l1);
+    else encode_fwd_kernel<false, kNDense><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, n_points, 1, enc, l0, l1);
 }
 
 template <int kNDense>
 void launch_bwd(const lb_level_table& T, int grid, const float* rays, const float* z, const float* x01, const float2* tb,
                 const float* d_enc, size_t n_points, int n_samples, float* grad_table, float* d_rays, float* d_x01,
-                cudaStream_t st) {
+                int l0, int l1, cudaStream_t st) {
     const bool in_grad = (d_rays != nullptr) || (d_x01 != nullptr);
     if (rays) {
-        if (in_grad) encode_bwd_kernel<true, true, kNDense><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, d_rays, nullptr);
-        else encode_bwd_kernel<true, false, kNDense><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, nullptr, nullptr);
+        if (in_grad) encode_bwd_kernel<true, true, kNDense><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, d_rays, nullptr, l0, l1);
+        else encode_bwd_kernel<true, false, kNDense><<<grid, kThreads, 0, st>>>(T, rays, z, nullptr, tb, d_enc, n_points, n_samples, grad_table, nullptr, nullptr, l0, l1);
     } else {
-        if (in_grad) encode_bwd_kernel<false, true, kNDense><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, d_x01);
-        else encode_bwd_kernel<false, false, kNDense><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, nullptr);
+        if (in_grad) encode_bwd_kernel<false, true, kNDense><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, d_x01, l0, l1);
+        else encode_bwd_kernel<false, false, kNDense><<<grid, kThreads, 0, st>>>(T, nullptr, nullptr, x01, tb, d_enc, n_points, 1, grad_table, nullptr, nullptr, l0, l1);
     }
+}
+
+// Level-group passes.  When the tables fit the L2 (T <= 2^19: 57 MB) one launch walks all levels per point.  Larger
+// tables (T = 2^22: 422 MB) would turn every gather / atomic into a random 32-byte HBM access, so the levels are
+// processed in groups whose tables stay L2-resident while ALL points of the chunk visit them: one launch per
+// group, each reading / writing only its own columns of the row-major [P, 32] encoding.  Groups start on even
+// levels (a float4 of the row = two levels).  Returns the end of the group that starts at l0.
+int next_group_end(const lb_plan* plan, int l0) {
+    const int n = plan->cfg.n_levels;
+    const uint64_t budget = (uint64_t)plan->l2_bytes * 55 / 100;
+    if ((uint64_t)plan->n_table_entries * 8 <= budget) return n;
+    uint64_t bytes = 0;
+    int l = l0;
+    while (l < n) {
+        uint64_t step = (uint64_t)plan->levels[l].size * 8;
+        if (l + 1 < n) step += (uint64_t)plan->levels[l + 1].size * 8;
+        if (l > l0 && bytes + step > budget) break;
+        bytes += step;
+        l += 2;
+    }
+    return l < n ? l : n;
 }
 
 }  // namespace
@@ -366,12 +399,17 @@ int lb_launch_encode_fwd(const lb_plan* plan, const float* rays, const float* z,
     const lb_level_table T = lb_make_level_table(plan);
     const int grid = grid_for(plan->sm_count, n_points, 8);
     const float2* tb = reinterpret_cast<const float2*>(table);
-    switch (dense_prefix(plan)) {
-        case 1: launch_fwd<1>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
-        case 2: launch_fwd<2>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
-        case 3: launch_fwd<3>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
-        case 4: launch_fwd<4>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
-        default: launch_fwd<-1>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, st); break;
+    const int nd = dense_prefix(plan);
+    for (int l0 = 0; l0 < plan->cfg.n_levels;) {
+        const int l1 = next_group_end(plan, l0);
+        switch (nd) {
+            case 1: launch_fwd<1>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, l0, l1, st); break;
+            case 2: launch_fwd<2>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, l0, l1, st); break;
+            case 3: launch_fwd<3>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, l0, l1, st); break;
+            case 4: launch_fwd<4>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, l0, l1, st); break;
+            default: launch_fwd<-1>(T, grid, rays, z, x01, tb, n_points, n_samples, enc, l0, l1, st); break;
+        }
+        l0 = l1;
     }
     return lb_check_cuda(cudaGetLastError(), "encode_fwd launch");
 }
@@ -382,12 +420,17 @@ int lb_launch_encode_bwd(const lb_plan* plan, const float* rays, const float* z,
     const lb_level_table T = lb_make_level_table(plan);
     const int grid = grid_for(plan->sm_count, n_points, 6);
     const float2* tb = reinterpret_cast<const float2*>(table);
-    switch (dense_prefix(plan)) {
-        case 1: launch_bwd<1>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
-        case 2: launch_bwd<2>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
-        case 3: launch_bwd<3>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
-        case 4: launch_bwd<4>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
-        default: launch_bwd<-1>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, st); break;
+    const int nd = dense_prefix(plan);
+    for (int l0 = 0; l0 < plan->cfg.n_levels;) {
+        const int l1 = next_group_end(plan, l0);
+        switch (nd) {
+            case 1: launch_bwd<1>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, l0, l1, st); break;
+            case 2: launch_bwd<2>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, l0, l1, st); break;
+            case 3: launch_bwd<3>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, l0, l1, st); break;
+            case 4: launch_bwd<4>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, l0, l1, st); break;
+            default: launch_bwd<-1>(T, grid, rays, z, x01, tb, d_enc, n_points, n_samples, grad_table, d_rays, d_x01, l0, l1, st); break;
+        }
+        l0 = l1;
     }
     return lb_check_cuda(cudaGetLastError(), "encode_bwd launch");
 }
