@@ -27,8 +27,18 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-WORKLOAD = dict(name="newer_college_shaped_C2", keyframes=8, rays_per_keyframe=4096, sky_per_keyframe=0,
-                n_samples=512, log2_hashmap_size=19, chunk=16384, ray_range=(1.0, 50.0), voxel_size=100)
+WORKLOADS = {
+    # BASELINE.json configs[1] -- the workload `metric` is quoted on (default)
+    "c2": dict(name="newer_college_shaped_C2", keyframes=8, rays_per_keyframe=4096, sky_per_keyframe=0, n_samples=512,
+               log2_hashmap_size=19, chunk=16384, ray_range=(1.0, 50.0), voxel_size=100, pose_grad=False),
+    # configs[2]: joint keyframe pose refinement (gradients to ray origins / directions -> pose 6-vectors)
+    "c3": dict(name="fusionportable_shaped_C3_pose_refinement", keyframes=8, rays_per_keyframe=4096, sky_per_keyframe=0,
+               n_samples=512, log2_hashmap_size=19, chunk=16384, ray_range=(1.0, 50.0), voxel_size=100, pose_grad=True),
+    # configs[3]: 2^22 hash tables, 32768 rays per GPU (262144 rays/iter at 8 GPUs)
+    "c4": dict(name="haveri_hpk_shaped_C4_T22", keyframes=8, rays_per_keyframe=4096, sky_per_keyframe=0, n_samples=512,
+               log2_hashmap_size=22, chunk=16384, ray_range=(2.5, 45.0), voxel_size=100, pose_grad=False),
+}
+WORKLOAD = WORKLOADS["c2"]
 METRIC = "mapping rays/sec (fwd+bwd)"
 UNIT = "rays/s"
 
@@ -46,6 +56,8 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample-rays", type=int, default=512, help="rays per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS),
+                    help="c2 = BASELINE configs[1] (default, the headline); c3 / c4 = configs[2] / configs[3] variants")
     return ap.parse_args()
 
 
@@ -206,12 +218,20 @@ def run_ours(args):
                                   chunk=W["chunk"], voxel_size=W["voxel_size"])
     opt = M.Optimizer(settings, None, M.WorldCube(scale, shift), dev)
     window = [M.KeyFrame(M.LidarScanData(k.directions, k.distances, k.sky_directions), k.pose, device=dev) for k in kfs]
-    for kf in window:
-        kf.is_anchored = True     # configs[1]: map optimisation with fixed poses (reference first phase, defaults.yaml:80-84)
+    for i, kf in enumerate(window):
+        # configs[1]: map optimisation with fixed poses (reference first phase, defaults.yaml:80-84);
+        # pose refinement (configs[2]): every keyframe but the anchor carries a trainable pose 6-vector
+        free = bool(W["pose_grad"]) and i > 0
+        kf.is_anchored = not free
+        kf.get_lidar_pose().set_fixed(not free)
     opt._model.freeze_sigma_head(False)
     opt._model.freeze_rgb_head(True)
     sigma_params = opt._model.get_sigma_parameters()
-    adam = M.FusedAdam([{"params": sigma_params, "lr": settings.model_config.train.lrate_sigma_mlp}])
+    groups = [{"params": sigma_params, "lr": settings.model_config.train.lrate_sigma_mlp}]
+    pose_params = [kf.get_lidar_pose().get_pose_tensor() for kf in window if not kf.is_anchored]
+    if pose_params:
+        groups.append({"params": pose_params, "lr": settings.model_config.train.lrate_pose})
+    adam = M.FusedAdam(groups)
     n_acc = settings.model_config.model.occ_model.N_iters_acc
     n_rays = W["keyframes"] * W["rays_per_keyframe"]
 
@@ -222,7 +242,7 @@ def run_ours(args):
             rays, depths = host_batch[0].to(dev, non_blocking=True), host_batch[1].to(dev, non_blocking=True)
         loss = opt.compute_loss(None, (rays, depths), i)
         loss.backward()
-        opt._dp.all_reduce_grads(sigma_params)
+        opt._dp.all_reduce_grads(sigma_params + pose_params)
         adam.step()
         adam.zero_grad(set_to_none=True)
         if i % n_acc == 0:
@@ -307,7 +327,8 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": W["name"], **{k: W[k] for k in ("keyframes", "rays_per_keyframe", "n_samples", "log2_hashmap_size", "chunk")},
                        "rays_per_step_per_gpu": n_rays, "parallelism": f"ray-dp{world}",
-                       "l2": "inputs_exceed_l2 (per-step working set ~2.4 GB of encodings + 57 MB tables vs 126 MB L2)"},
+                       "pose_refinement": bool(W["pose_grad"]),
+                       "l2": "inputs_exceed_l2 (per-step working set ~2.4 GB of encodings + hash tables vs 126 MB L2)"},
             "roofline": roofline,
             "e2e": {"value": n_rays * world * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                     "h2d_bytes_per_step": n_rays * 14 * 4, "d2h_bytes_per_step": 4, "last_loss": last},
@@ -322,6 +343,7 @@ def run_ours(args):
 
 if __name__ == "__main__":
     a = parse_args()
+    WORKLOAD = WORKLOADS[a.workload]
     if a.impl == "reference":
         run_reference(a)
     else:

@@ -43,29 +43,6 @@ constexpr int kFwdCtasPerSm = 4;
 constexpr int kBwdCtasPerSm = 3;
 
 
-// ---- bf16 splitting -------------------------------------------------------------------------
-// packs rn_bf16(lo), rn_bf16(hi) into one register (lo in bits 0-15)
-__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
-    uint32_t r;
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-    return r;
-}
-__device__ __forceinline__ float bf16_lo_f32(uint32_t p) { return __uint_as_float(p << 16); }
-__device__ __forceinline__ float bf16_hi_f32(uint32_t p) { return __uint_as_float(p & 0xffff0000u); }
-
-// v[0..7] -> first pieces b1 (4 packed regs), second pieces b2 and (kThree) third pieces b3; every
-// subtraction is exact in fp32, so v = b1 + b2 + b3 up to 2^-26 |v|
-template <bool kThree>
-__device__ __forceinline__ void split8(const float* v, uint32_t* b1, uint32_t* b2, uint32_t* b3) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        b1[i] = pack_bf16(v[2 * i], v[2 * i + 1]);
-        const float r0 = v[2 * i] - bf16_lo_f32(b1[i]), r1 = v[2 * i + 1] - bf16_hi_f32(b1[i]);
-        b2[i] = pack_bf16(r0, r1);
-        if (kThree) b3[i] = pack_bf16(r0 - bf16_lo_f32(b2[i]), r1 - bf16_hi_f32(b2[i]));
-    }
-}
-
 // A 128 x 32 fp32 tile (row-major in global memory, 8 float4 per row) is handled "flat": in pass i thread t owns
 // float4 number q = t % 8 of row i * 16 + t / 8, so every warp-wide global access is 512 contiguous bytes.
 // Lane pairs (q even / odd) exchange their float4 to assemble one 8-element chunk; the even lane then stores the

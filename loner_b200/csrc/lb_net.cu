@@ -1,11 +1,14 @@
-// RGB branch, remaining pieces: spherical-harmonics direction encoding (forward / input gradient), the backward
-// pass of the fused network (fp32 CUDA-core tile GEMMs; the tcgen05 forward is lb_net_umma.cu) and colour
-// compositing.
+// RGB branch, remaining pieces: spherical-harmonics direction encoding (forward / input gradient), colour
+// compositing, and the C entry point of the fused network's backward (the tcgen05 kernels are in lb_net_umma.cu).
 //
 // Replaces tcnn.Encoding(3, {"otype": "SphericalHarmonics", "degree": 4}) (reference src/models/nerf_tcnn.py:43,86),
 // the autograd backward of tcnn.Network (nerf_tcnn.py:50-52,89-91) and the colour lines of raw2outputs
 // (src/models/rendering_tcnn.py:284-289).
 #include "lb_common.cuh"
+
+int lb_launch_net_bwd_umma(const float* x, size_t n_points, int n_in, int n_hidden, int n_out, int out_act, const float* params,
+                           const float* acts, const float* out, const float* d_out, float* grad_params, float* d_x,
+                           cudaStream_t st);
 
 namespace {
 
@@ -50,193 +53,6 @@ sh4_bwd_kernel(const float* __restrict__ d01, const float* __restrict__ d_out, s
     d_d01[3 * p] = 2.0f * gx;
     d_d01[3 * p + 1] = 2.0f * gy;
     d_d01[3 * p + 2] = 2.0f * gz;
-}
-
-// ------------------------------------------------------------------------------------------
-// network backward: per 128-point tile, layer by layer from the output, two tile GEMMs per layer
-//   dW_l[j,k] += sum_p dZ_l[p,j] Hprev[p,k]        dHprev[p,k] = sum_j dZ_l[p,j] W_l[j,k]
-// dZ / Hprev / W_l tiles live in shared memory (row stride 68 floats); the weight-gradient accumulators of all
-// layers stay in shared memory for the CTA's lifetime (every entry has one owner thread) and are flushed with
-// one atomicAdd per entry at the end.
-// ------------------------------------------------------------------------------------------
-constexpr int kT = 128, kW = 64, kLd = 68, kOutPad = 16, kBwdThreads = 256;
-
-struct NetShape {
-    int n_in, n_hidden, n_out, out_act;
-};
-
-__device__ __forceinline__ size_t layer_param_off(const NetShape& s, int l) {
-    return l == 0 ? 0 : (size_t)kW * s.n_in + (size_t)(l - 1) * kW * kW;
-}
-
-// activation tile written by lb_net_fwd: [16-byte chunk q of the 64-wide row][row r] float4 -> shared tile [r][q]
-__device__ __forceinline__ void load_act_tile(const float* __restrict__ acts, size_t layer, size_t n_tiles, size_t tile,
-                                              int valid_rows, float* dst) {
-    const float4* src = reinterpret_cast<const float4*>(acts) + (layer * n_tiles + tile) * (size_t)(kT * 16);
-    for (int it = threadIdx.x; it < kT * 16; it += kBwdThreads) {
-        const int q = it / kT, r = it - q * kT;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < valid_rows) v = __ldg(src + it);
-        *reinterpret_cast<float4*>(dst + r * kLd + q * 4) = v;
-    }
-}
-
-// rows x cols fp32 (row-major, leading dimension ld_src) -> shared tile (leading dimension kLd); rows beyond
-// `valid_rows` are zero
-__device__ __forceinline__ void load_tile_f4(const float* __restrict__ src, size_t ld_src, int rows, int cols,
-                                             int valid_rows, float* dst) {
-    const int c4 = cols / 4;
-    for (int it = threadIdx.x; it < rows * c4; it += kBwdThreads) {
-        const int r = it / c4, c = it - r * c4;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < valid_rows) v = __ldg(reinterpret_cast<const float4*>(src + (size_t)r * ld_src + c * 4));
-        *reinterpret_cast<float4*>(dst + r * kLd + c * 4) = v;
-    }
-}
-
-__global__ void __launch_bounds__(kBwdThreads, 1)
-net_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x, const float* __restrict__ acts,
-               const float* __restrict__ out, const float* __restrict__ d_out, size_t n_points, NetShape s,
-               float* __restrict__ grad_params, float* __restrict__ d_x) {
-    extern __shared__ __align__(16) float smf[];
-    float* sDZ = smf;                         // [128][68]
-    float* sH = sDZ + kT * kLd;               // [128][68]
-    float* sW = sH + kT * kLd;                // [64][68]
-    float* sDO = sW + kW * kLd;               // [128][16]
-    float* sAcc = sDO + kT * kOutPad;         // per layer [64][64] (+ output layer [16][64])
-    const int tid = threadIdx.x;
-    const int n_acc = s.n_hidden * kW * kW + kOutPad * kW;
-    for (int i = tid; i < n_acc; i += kBwdThreads) sAcc[i] = 0.0f;
-    const size_t out_off = layer_param_off(s, s.n_hidden);
-    const int ty = tid >> 4, tx = tid & 15;   // 16 x 16 thread grid over a 64 x 64 (or 128 x 64) output tile
-
-    const size_t n_tiles = (n_points + kT - 1) / kT;
-    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const size_t p0 = tile * (size_t)kT;
-        const int valid = (int)((n_points - p0) < (size_t)kT ? (n_points - p0) : (size_t)kT);
-        __syncthreads();
-        // output layer: dZo[p,c] = d_out (* o (1 - o) for the fused sigmoid)
-        for (int it = tid; it < kT * kOutPad; it += kBwdThreads) {
-            const int r = it / kOutPad, c = it - r * kOutPad;
-            float g = 0.0f;
-            if (r < valid && c < s.n_out) {
-                g = __ldg(d_out + (p0 + r) * s.n_out + c);
-                if (s.out_act == 1) {
-                    const float o = __ldg(out + (p0 + r) * s.n_out + c);
-                    g *= o * (1.0f - o);
-                }
-            }
-            sDO[it] = g;
-        }
-        load_act_tile(acts, (size_t)(s.n_hidden - 1), n_tiles, tile, valid, sH);
-        load_tile_f4(params + out_off, kW, kOutPad, kW, kOutPad, sW);
-        __syncthreads();
-        // dW_out[c, j] += sum_p dZo[p, c] H[p, j]
-        for (int it = tid; it < s.n_out * kW; it += kBwdThreads) {
-            const int c = it / kW, j = it - c * kW;
-            float a = 0.0f;
-#pragma unroll 8
-            for (int p = 0; p < kT; ++p) a = fmaf(sDO[p * kOutPad + c], sH[p * kLd + j], a);
-            sAcc[s.n_hidden * kW * kW + c * kW + j] += a;
-        }
-        // dZ_{last hidden}[p, j] = (sum_c dZo[p, c] Wout[c, j]) * [H[p, j] > 0]
-        for (int it = tid; it < kT * kW; it += kBwdThreads) {
-            const int p = it / kW, j = it - p * kW;
-            float a = 0.0f;
-            for (int c = 0; c < s.n_out; ++c) a = fmaf(sDO[p * kOutPad + c], sW[c * kLd + j], a);
-            sDZ[p * kLd + j] = sH[p * kLd + j] > 0.0f ? a : 0.0f;
-        }
-        for (int l = s.n_hidden - 1; l >= 0; --l) {
-            const int K = l == 0 ? s.n_in : kW;
-            __syncthreads();                  // sDZ complete; sH / sW no longer read
-            if (l > 0) load_act_tile(acts, (size_t)(l - 1), n_tiles, tile, valid, sH);
-            else load_tile_f4(x + p0 * s.n_in, s.n_in, kT, K, valid, sH);
-            load_tile_f4(params + layer_param_off(s, l), K, kW, K, kW, sW);
-            __syncthreads();
-            const int k0 = tx * 4;
-            if (k0 < K) {
-                // dW_l[j0..j0+3][k0..k0+3] += sum_p dZ[p][j] Hprev[p][k]
-                const int j0 = ty * 4;
-                float acc[4][4];
-#pragma unroll
-                for (int a = 0; a < 4; ++a)
-#pragma unroll
-                    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0f;
-#pragma unroll 4
-                for (int p = 0; p < kT; ++p) {
-                    const float4 dz = *reinterpret_cast<const float4*>(sDZ + p * kLd + j0);
-                    const float4 h = *reinterpret_cast<const float4*>(sH + p * kLd + k0);
-                    const float dzv[4] = {dz.x, dz.y, dz.z, dz.w}, hv[4] = {h.x, h.y, h.z, h.w};
-#pragma unroll
-                    for (int a = 0; a < 4; ++a)
-#pragma unroll
-                        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(dzv[a], hv[b], acc[a][b]);
-                }
-                float* dst = sAcc + l * kW * kW;
-#pragma unroll
-                for (int a = 0; a < 4; ++a)
-#pragma unroll
-                    for (int b = 0; b < 4; ++b) dst[(j0 + a) * kW + k0 + b] += acc[a][b];   // owner-exclusive entry
-            }
-            const bool need_prev = l > 0 || d_x != nullptr;
-            float dprev[8][4];
-            if (need_prev && k0 < K) {
-                // dHprev[p0r..p0r+7][k0..k0+3] = sum_j dZ[p][j] W[j][k]
-                const int r0 = ty * 8;
-#pragma unroll
-                for (int a = 0; a < 8; ++a)
-#pragma unroll
-                    for (int b = 0; b < 4; ++b) dprev[a][b] = 0.0f;
-#pragma unroll 2
-                for (int j4 = 0; j4 < kW; j4 += 4) {
-                    float wv[4][4];
-#pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
-                        const float4 w = *reinterpret_cast<const float4*>(sW + (j4 + jj) * kLd + k0);
-                        wv[jj][0] = w.x; wv[jj][1] = w.y; wv[jj][2] = w.z; wv[jj][3] = w.w;
-                    }
-#pragma unroll
-                    for (int a = 0; a < 8; ++a) {
-                        const float4 dz = *reinterpret_cast<const float4*>(sDZ + (r0 + a) * kLd + j4);
-                        const float dzv[4] = {dz.x, dz.y, dz.z, dz.w};
-#pragma unroll
-                        for (int jj = 0; jj < 4; ++jj)
-#pragma unroll
-                            for (int b = 0; b < 4; ++b) dprev[a][b] = fmaf(dzv[jj], wv[jj][b], dprev[a][b]);
-                    }
-                }
-            }
-            __syncthreads();                  // every read of sDZ for this layer is done
-            if (need_prev && k0 < K) {
-                const int r0 = ty * 8;
-#pragma unroll
-                for (int a = 0; a < 8; ++a) {
-                    if (l > 0) {
-                        const float4 h = *reinterpret_cast<const float4*>(sH + (r0 + a) * kLd + k0);
-                        *reinterpret_cast<float4*>(sDZ + (r0 + a) * kLd + k0) =
-                            make_float4(h.x > 0.f ? dprev[a][0] : 0.f, h.y > 0.f ? dprev[a][1] : 0.f,
-                                        h.z > 0.f ? dprev[a][2] : 0.f, h.w > 0.f ? dprev[a][3] : 0.f);
-                    } else if (r0 + a < valid) {
-                        *reinterpret_cast<float4*>(d_x + (p0 + r0 + a) * s.n_in + k0) =
-                            make_float4(dprev[a][0], dprev[a][1], dprev[a][2], dprev[a][3]);
-                    }
-                }
-            }
-        }
-    }
-    __syncthreads();
-    if (grad_params) {
-        for (int l = 0; l < s.n_hidden; ++l) {
-            const int K = l == 0 ? s.n_in : kW;
-            const size_t off = layer_param_off(s, l);
-            for (int i = tid; i < kW * K; i += kBwdThreads) {
-                const int j = i / K, k = i - j * K;
-                atomicAdd(grad_params + off + i, sAcc[l * kW * kW + j * kW + k]);
-            }
-        }
-        for (int i = tid; i < s.n_out * kW; i += kBwdThreads)
-            atomicAdd(grad_params + out_off + i, sAcc[s.n_hidden * kW * kW + i]);
-    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -307,26 +123,16 @@ extern "C" int lb_net_bwd(const float* x, int64_t n_points, int n_in, int n_hidd
     LB_REQUIRE(n_points >= 0, "negative size");
     LB_REQUIRE(n_in >= 16 && n_in <= 64 && n_in % 16 == 0, "n_in must be 16, 32, 48 or 64");
     LB_REQUIRE(n_hidden >= 1 && n_hidden <= 6, "n_hidden_layers must be in [1, 6]");
-    LB_REQUIRE(n_out >= 1 && n_out <= kOutPad, "n_out must be in [1, 16]");
+    LB_REQUIRE(n_out >= 1 && n_out <= 16, "n_out must be in [1, 16]");
     LB_REQUIRE(out_act == 0 || (out_act == 1 && out), "out_act 1 (sigmoid) needs the forward output");
     if (n_points == 0) return LB_OK;
-    const NetShape s{n_in, n_hidden, n_out, out_act};
-    const size_t smem = sizeof(float) * ((size_t)2 * kT * kLd + kW * kLd + kT * kOutPad + (size_t)n_hidden * kW * kW + kOutPad * kW);
-    if (smem > 227 * 1024) {
-        lb_set_error("lb_net_bwd: %d hidden layers do not fit in shared memory", n_hidden);
+    const int rc = lb_launch_net_bwd_umma(x, (size_t)n_points, n_in, n_hidden, n_out, out_act, params, acts, out, d_out,
+                                          grad_params, d_x, (cudaStream_t)stream);
+    if (rc > 0) {
+        lb_set_error("lb_net_bwd: configuration does not fit in shared memory");
         return LB_ERR_UNSUPPORTED;
     }
-    int rc = lb_check_cuda(cudaFuncSetAttribute(net_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
-                           "net_bwd smem opt-in");
-    if (rc) return rc;
-    int dev = 0, sms = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const size_t tiles = ((size_t)n_points + kT - 1) / kT;
-    const int grid = (int)(tiles < (size_t)sms ? tiles : (size_t)sms);
-    net_bwd_kernel<<<grid, kBwdThreads, smem, (cudaStream_t)stream>>>(params, x, acts, out, d_out, (size_t)n_points, s,
-                                                                      grad_params, d_x);
-    LB_LAUNCH_CHECK("lb_net_bwd");
-    return LB_OK;
+    return rc;
 }
 
 extern "C" int lb_composite_rgb_fwd(const float* weights, const float* colors, int n_rays, int n_samples, int n_colors,

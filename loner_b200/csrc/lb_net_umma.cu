@@ -272,7 +272,271 @@ int launch_fwd(const float* params, const float* x, size_t n_points, NetShape sh
     return lb_check_cuda(cudaGetLastError(), "net_fwd_umma launch");
 }
 
+// ------------------------------------------------------------------------------------------
+// backward on the tensor cores.  Per 128-point tile, from the output layer down:
+//   U_l[j,k] += sum_p dZ_l[p,j] Hprev[p,k]      A = dZ_l^T (MN-major view),  B = Hprev (MN-major view)   M = 64
+//   dHprev[p,k] = sum_j dZ_l[p,j] W_l[j,k]      A = dZ_l   (K-major view),   B = W_l   (MN-major view)   M = 128
+//   dZ_{l-1} = dHprev * [Hprev > 0]
+// Operands are exact two-piece bf16 splits (x = b1 + b2 up to 2^-18), three products per K step, fp32 accumulate.
+// Thread (t, half) owns row t / 32 columns: its dZ half-row lives in registers between layers, its Hprev half-row
+// is one coalesced read of the tile-transposed activation buffer; both are written as bf16 pieces into
+// shared-memory operand tiles (canonical no-swizzle layout, row-per-thread stores are conflict free).  The weight
+// pieces of all layers stay resident in shared memory; the weight-gradient accumulators U_l stay in tensor memory
+// (64 columns per layer, M = 64 layout) for the CTA's lifetime and are flushed with one atomicAdd per entry.
+// The output layer is treated as a 64-wide layer whose rows >= n_out are zero.
+// ------------------------------------------------------------------------------------------
+constexpr uint32_t kLboP = kTile * 16 + 16;          // chunk stride of a 128-row bf16 operand tile
+constexpr uint32_t kPiece = 8 * kLboP;               // [128 x 64] bf16 piece
+constexpr int kBwdThreads = 256;
+
+__host__ __device__ inline uint32_t bwd_weight_piece_bytes(int n_in, int n_hidden) {
+    return (uint32_t)(n_in / 8) * kLboW + (uint32_t)n_hidden * (kWidth / 8) * kLboW;     // layers 0 .. n_hidden
+}
+__device__ __forceinline__ uint32_t bwd_weight_off(int n_in, int l) {
+    return l == 0 ? 0u : (uint32_t)(n_in / 8) * kLboW + (uint32_t)(l - 1) * (kWidth / 8) * kLboW;
+}
+
+// 8 fp32 -> bf16 pieces -> one 16-byte chunk of each piece tile
+__device__ __forceinline__ void put_chunk(const float* v, uint8_t* p1, uint8_t* p2, uint32_t off) {
+    uint32_t b1[4], b2[4];
+    split8<false>(v, b1, b2, nullptr);
+    *reinterpret_cast<uint4*>(p1 + off) = make_uint4(b1[0], b1[1], b1[2], b1[3]);
+    *reinterpret_cast<uint4*>(p2 + off) = make_uint4(b2[0], b2[1], b2[2], b2[3]);
+}
+
+template <int kIn>
+__global__ void __launch_bounds__(kBwdThreads, 1)
+net_bwd_umma_kernel(const float* __restrict__ params, const float* __restrict__ x, const float* __restrict__ acts,
+                    const float* __restrict__ out, const float* __restrict__ d_out, size_t n_points, NetShape shape,
+                    float* __restrict__ grad_params, float* __restrict__ d_x) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    constexpr uint32_t kRow = kIn * 4 + 16;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int t = tid & 127, half = tid >> 7;
+    const int nh = shape.n_hidden;
+    const uint32_t wpiece = bwd_weight_piece_bytes(kIn, nh);
+    uint8_t* dz1 = sm;
+    uint8_t* dz2 = dz1 + kPiece;
+    uint8_t* h1 = dz2 + kPiece;
+    uint8_t* h2 = h1 + kPiece;
+    uint8_t* w1 = h2 + kPiece;
+    uint8_t* w2 = w1 + wpiece;
+    uint8_t* xst = w2 + wpiece;
+    const uint32_t bar = smem_u32(xst + kTile * kRow);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xst + kTile * kRow + 8);
+
+    const size_t n_tiles = (n_points + kTile - 1) / kTile;
+    size_t tile = blockIdx.x;
+    {   // first x tile (256 threads)
+        constexpr int kChunks = kIn / 4;
+        const float4* base = reinterpret_cast<const float4*>(x) + tile * (size_t)(kTile * kChunks);
+        for (int idx = tid; idx < kTile * kChunks; idx += kBwdThreads) {
+            const int row = idx / kChunks, q = idx - row * kChunks;
+            const bool ok = tile < n_tiles && tile * (size_t)kTile + row < n_points;
+            cp_async16(smem_u32(xst) + row * kRow + q * 16, ok ? (const void*)(base + idx) : (const void*)x, ok ? 16u : 0u);
+        }
+        cp_async_commit();
+    }
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), 512);
+    if (tid == 32) mbar_init(bar, 1);
+    // weight pieces of all layers: X[r = out unit j][c = k / 8]; output layer rows >= 16 are zero
+    {
+        size_t src = 0;
+        for (int l = 0; l <= nh; ++l) {
+            const int K = l == 0 ? kIn : kWidth;
+            const int rows_real = l == nh ? kOutPad : kWidth;
+            const int chunks = K / 8;
+            const uint32_t off = bwd_weight_off(kIn, l);
+            for (int it = tid; it < kWidth * chunks; it += kBwdThreads) {
+                const int j = it / chunks, c = it - j * chunks;
+                float v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = j < rows_real ? __ldg(params + src + (size_t)j * K + c * 8 + e) : 0.0f;
+                put_chunk(v, w1, w2, off + tile_off(j, c, kLboW));
+            }
+            src += (size_t)rows_real * K;
+        }
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t t_dh = tmem;                                    // dHprev [128 x 64]
+    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t a1 = smem_u32(dz1), a2 = smem_u32(dz2), b1s = smem_u32(h1), b2s = smem_u32(h2);
+    const uint32_t ws1 = smem_u32(w1), ws2 = smem_u32(w2);
+    const bool need_dx = d_x != nullptr;
+
+    uint32_t parity = 0;
+    bool first = true;
+    for (; tile < n_tiles; tile += gridDim.x) {
+        const size_t p = tile * (size_t)kTile + t;
+        const bool valid = p < n_points;
+        float dz[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) dz[i] = 0.0f;
+        if (half == 0 && valid) {                                     // output layer: dZ = d_out (* o (1 - o))
+#pragma unroll
+            for (int c = 0; c < kOutPad; ++c) {
+                if (c < shape.n_out) {
+                    float g = __ldg(d_out + p * shape.n_out + c);
+                    if (shape.out_act == 1) {
+                        const float o = __ldg(out + p * shape.n_out + c);
+                        g *= o * (1.0f - o);
+                    }
+                    dz[c] = g;
+                }
+            }
+        }
+        for (int l = nh; l >= 0; --l) {
+            const int K = l == 0 ? kIn : kWidth;
+            // dZ_l half-row -> operand tiles
+#pragma unroll
+            for (int c = 0; c < 4; ++c) put_chunk(dz + 8 * c, dz1, dz2, tile_off(t, half * 4 + c, kLboP));
+            // Hprev half-row: activations of layer l-1 (tile-transposed buffer) or the staged input row
+            float hp[32];
+            if (l > 0) {
+                const float4* src = reinterpret_cast<const float4*>(acts) + ((size_t)(l - 1) * n_tiles + tile) * (kTile * 16);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const float4 v = __ldcs(src + (half * 8 + q) * kTile + t);
+                    hp[4 * q] = v.x; hp[4 * q + 1] = v.y; hp[4 * q + 2] = v.z; hp[4 * q + 3] = v.w;
+                }
+            } else {
+                cp_async_wait<0>();
+                __syncthreads();                                           // every thread's copies of the x tile landed
+                const float* row = reinterpret_cast<const float*>(xst + t * kRow);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) hp[i] = (half * 32 + i < kIn) ? row[half * 32 + i] : 0.0f;
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if (half * 32 + 8 * c < K) put_chunk(hp + 8 * c, h1, h2, tile_off(t, half * 4 + c, kLboP));
+            fence_async_smem();
+            tc_fence_before();
+            __syncthreads();
+            if (tid == 0) {
+                tc_fence_after();
+                const uint32_t t_u = tmem + 64 + 64 * l;
+                const uint32_t idesc_u = umma_idesc(64, K, 1, 1);
+                if (grad_params) {
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks) {                   // contraction over the 128 points, 16 per step
+                        const uint64_t da1 = umma_desc(a1 + ks * 256, 128, kLboP), da2 = umma_desc(a2 + ks * 256, 128, kLboP);
+                        const uint64_t db1 = umma_desc(b1s + ks * 256, 128, kLboP), db2 = umma_desc(b2s + ks * 256, 128, kLboP);
+                        umma_bf16(t_u, da1, db1, idesc_u, (!first || ks > 0) ? 1u : 0u);
+                        umma_bf16(t_u, da1, db2, idesc_u, 1);
+                        umma_bf16(t_u, da2, db1, idesc_u, 1);
+                    }
+                }
+                if (l > 0 || need_dx) {
+                    const uint32_t idesc_h = umma_idesc(128, K, 0, 1);
+                    const uint32_t woff = bwd_weight_off(kIn, l);
+                    const int ksteps = l == nh ? 1 : 4;              // contraction over the layer's outputs j (16 per step)
+                    for (int ks = 0; ks < ksteps; ++ks) {
+                        const uint64_t da1 = umma_desc(a1 + ks * 2 * kLboP, kLboP, 128), da2 = umma_desc(a2 + ks * 2 * kLboP, kLboP, 128);
+                        const uint64_t db1 = umma_desc(ws1 + woff + ks * 256, 128, kLboW), db2 = umma_desc(ws2 + woff + ks * 256, 128, kLboW);
+                        umma_bf16(t_dh, da1, db1, idesc_h, ks > 0);
+                        umma_bf16(t_dh, da1, db2, idesc_h, 1);
+                        umma_bf16(t_dh, da2, db1, idesc_h, 1);
+                    }
+                }
+                umma_commit(bar);
+            }
+            mbar_wait(bar, parity);
+            parity ^= 1;
+            tc_fence_after();
+            if (l > 0) {
+                uint32_t r[32];
+                tmem_ld32(t_dh + lane_off + half * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) dz[i] = hp[i] > 0.0f ? __uint_as_float(r[i]) : 0.0f;
+            } else {
+                if (need_dx && half * 32 < kIn) {
+                    uint32_t r[32];
+                    tmem_ld32(t_dh + lane_off + half * 32, r);
+                    tmem_ld_wait();
+                    if (valid) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q)
+                            if (half * 32 + 4 * q < kIn)
+                                *reinterpret_cast<float4*>(d_x + p * kIn + half * 32 + 4 * q) =
+                                    make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                                                __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+                    }
+                }
+                // the staged x rows have been consumed (before this layer's barrier): prefetch the next tile's
+                const size_t next = tile + gridDim.x;
+                constexpr int kChunks = kIn / 4;
+                if (next < n_tiles) {
+                    const float4* base = reinterpret_cast<const float4*>(x) + next * (size_t)(kTile * kChunks);
+                    for (int idx = tid; idx < kTile * kChunks; idx += kBwdThreads) {
+                        const int row = idx / kChunks, q = idx - row * kChunks;
+                        const bool ok = next * (size_t)kTile + row < n_points;
+                        cp_async16(smem_u32(xst) + row * kRow + q * 16, ok ? (const void*)(base + idx) : (const void*)x, ok ? 16u : 0u);
+                    }
+                }
+                cp_async_commit();
+            }
+            tc_fence_before();
+        }
+        first = false;
+    }
+    cp_async_wait<0>();
+    // flush the weight gradients: U_l row j sits in TMEM lane (j % 16) + 32 * (j / 16)
+    if (grad_params && !first) {
+        tc_fence_after();
+        size_t off = 0;
+        for (int l = 0; l <= nh; ++l) {
+            const int K = l == 0 ? kIn : kWidth;
+            const int rows_real = l == nh ? shape.n_out : kWidth;
+            uint32_t r[32];
+            tmem_ld32(tmem + 64 + 64 * l + lane_off + half * 32, r);
+            tmem_ld_wait();
+            const int j = (warp & 3) * 16 + lane;
+            if (lane < 16 && j < rows_real) {
+#pragma unroll
+                for (int k = 0; k < 32; ++k)
+                    if (half * 32 + k < K) atomicAdd(grad_params + off + (size_t)j * K + half * 32 + k, __uint_as_float(r[k]));
+            }
+            off += (size_t)(l == nh ? kOutPad : kWidth) * K;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+template <int kIn>
+int launch_bwd(const float* params, const float* x, const float* acts, const float* out, const float* d_out,
+               size_t n_points, NetShape shape, float* grad_params, float* d_x, cudaStream_t st) {
+    const uint32_t smem = 4 * kPiece + 2 * bwd_weight_piece_bytes(kIn, shape.n_hidden) + kTile * (kIn * 4 + 16) + 32;
+    if (smem > 227 * 1024) return 1;          // caller falls back to the CUDA-core kernel
+    int rc = lb_check_cuda(cudaFuncSetAttribute(net_bwd_umma_kernel<kIn>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                           "net_bwd_umma smem opt-in");
+    if (rc) return rc;
+    const size_t tiles = (n_points + kTile - 1) / kTile;
+    const int grid = (int)(tiles < (size_t)device_sm_count() ? tiles : (size_t)device_sm_count());
+    net_bwd_umma_kernel<kIn><<<grid, kBwdThreads, smem, st>>>(params, x, acts, out, d_out, n_points, shape, grad_params, d_x);
+    return lb_check_cuda(cudaGetLastError(), "net_bwd_umma launch");
+}
+
 }  // namespace
+
+// returns 0 on success, < 0 on error, 1 when the configuration does not fit (caller uses the CUDA-core kernel)
+int lb_launch_net_bwd_umma(const float* x, size_t n_points, int n_in, int n_hidden, int n_out, int out_act, const float* params,
+                           const float* acts, const float* out, const float* d_out, float* grad_params, float* d_x,
+                           cudaStream_t st) {
+    const NetShape shape{n_in, n_hidden, n_out, out_act};
+    switch (n_in) {
+        case 16: return launch_bwd<16>(params, x, acts, out, d_out, n_points, shape, grad_params, d_x, st);
+        case 32: return launch_bwd<32>(params, x, acts, out, d_out, n_points, shape, grad_params, d_x, st);
+        case 48: return launch_bwd<48>(params, x, acts, out, d_out, n_points, shape, grad_params, d_x, st);
+        default: return launch_bwd<64>(params, x, acts, out, d_out, n_points, shape, grad_params, d_x, st);
+    }
+}
 
 // tcnn.Network forward (reference src/models/nerf_tcnn.py:50-52,89-91).  x [P, n_in] (n_in already padded to a multiple
 // of 16), params = tcnn layout, out [P, n_out]; acts [n_hidden, P, 64] receives the post-ReLU activations when the

@@ -135,4 +135,27 @@ __device__ __forceinline__ void split_tf32(const float4& v, uint4& hi, uint4& lo
     lo.z = __float_as_uint(v.z - __uint_as_float(hi.z)); lo.w = __float_as_uint(v.w - __uint_as_float(hi.w));
 }
 
+// ---- bf16 splitting -------------------------------------------------------------------------
+// packs rn_bf16(lo), rn_bf16(hi) into one register (lo in bits 0-15)
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ float bf16_lo_f32(uint32_t p) { return __uint_as_float(p << 16); }
+__device__ __forceinline__ float bf16_hi_f32(uint32_t p) { return __uint_as_float(p & 0xffff0000u); }
+
+// v[0..7] -> first pieces b1 (4 packed regs), second pieces b2 and (kThree) third pieces b3; every
+// subtraction is exact in fp32, so v = b1 + b2 + b3 up to 2^-26 |v|
+template <bool kThree>
+__device__ __forceinline__ void split8(const float* v, uint32_t* b1, uint32_t* b2, uint32_t* b3) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        b1[i] = pack_bf16(v[2 * i], v[2 * i + 1]);
+        const float r0 = v[2 * i] - bf16_lo_f32(b1[i]), r1 = v[2 * i + 1] - bf16_hi_f32(b1[i]);
+        b2[i] = pack_bf16(r0, r1);
+        if (kThree) b3[i] = pack_bf16(r0 - bf16_lo_f32(b2[i]), r1 - bf16_hi_f32(b2[i]));
+    }
+}
+
 }  // namespace lb_umma
