@@ -244,3 +244,32 @@ def test_camera_loss_and_gradients_match_reference():
     a, b = rays.grad.cpu().double().flatten(), g["rays_grad"].double().flatten()
     assert torch.dot(a, b) / (a.norm() * b.norm()) > 0.99
     assert rel_err(rays.grad, g["rays_grad"]) < 2e-2
+
+
+def test_eval_drivers_and_state_dict_keys():
+    """render_frame / l1_depth_error on the golden rays: the peak metric and the error follow from
+    Model.forward's own outputs; state_dict keys are the reference's (f4: checkpoints load by name)."""
+    from loner_b200 import eval as E
+    g = load_golden("c1_ogm_l1js")
+    opt, M = make_optimizer(g)
+    rays, depths = g["rays"].to(DEV), g["depths"].to(DEV)
+    opt._model.cfg["render"]["N_samples_test"] = 128
+    torch.manual_seed(3)
+    r = E.render_frame(opt._model, opt._ray_sampler, rays, opt._scale_factor, camera=False)
+    torch.manual_seed(3)
+    opt._model.cfg["render"]["retraw"] = True
+    res = opt._model(rays, opt._ray_sampler, opt._scale_factor, testing=True, camera=False, return_variance=True)
+    assert torch.equal(r["depth"], res["depth_fine"] * opt._scale_factor)
+    peak = res["samples_fine"][torch.arange(rays.shape[0]), res["weights_fine"].argmax(dim=1)]
+    assert torch.equal(r["peak_depth_consistency"], (peak - res["depth_fine"]).abs() * opt._scale_factor)
+    torch.manual_seed(3)
+    err = E.l1_depth_error(opt._model, opt._ray_sampler, rays, depths, opt._scale_factor)
+    ok = (depths > 0) & (depths <= rays[:, -1])
+    ref = ((res["depth_fine"] - depths).abs() * opt._scale_factor)[ok].mean()
+    assert abs(err.item() - ref.item()) < 1e-5 * max(1.0, abs(ref.item()))
+    torch.manual_seed(3)
+    rc = E.render_frame(opt._model, opt._ray_sampler, rays, opt._scale_factor, camera=True, render_strategy='adjusted')
+    assert rc["rgb"].shape == (rays.shape[0], 3) and (rc["rgb"] >= 0).all() and (rc["rgb"] <= 1).all()
+    keys = set(opt._model.state_dict().keys())
+    assert keys == {"nerf_model._model_sigma.params", "nerf_model._pos_encoding.params",
+                    "nerf_model._dir_encoding.params", "nerf_model._model_intensity.params"}
