@@ -304,6 +304,17 @@ __device__ __forceinline__ void put_chunk(const float* v, uint8_t* p1, uint8_t* 
     *reinterpret_cast<uint4*>(p2 + off) = make_uint4(b2[0], b2[1], b2[2], b2[3]);
 }
 
+// this thread's 32-column half of row t of an activation tile (tile-transposed layout: coalesced across t)
+__device__ __forceinline__ void load_act_half(const float* __restrict__ acts, size_t layer, size_t n_tiles, size_t tile,
+                                              int half, int t, float* h) {
+    const float4* src = reinterpret_cast<const float4*>(acts) + (layer * n_tiles + tile) * (size_t)(kTile * 16);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const float4 v = __ldcs(src + (half * 8 + q) * kTile + t);
+        h[4 * q] = v.x; h[4 * q + 1] = v.y; h[4 * q + 2] = v.z; h[4 * q + 3] = v.w;
+    }
+}
+
 template <int kIn>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 net_bwd_umma_kernel(const float* __restrict__ params, const float* __restrict__ x, const float* __restrict__ acts,
@@ -389,20 +400,19 @@ net_bwd_umma_kernel(const float* __restrict__ params, const float* __restrict__ 
                 }
             }
         }
+        float hp_next[32];
+        load_act_half(acts, (size_t)(nh - 1), n_tiles, tile, half, t, hp_next);
         for (int l = nh; l >= 0; --l) {
             const int K = l == 0 ? kIn : kWidth;
             // dZ_l half-row -> operand tiles
 #pragma unroll
             for (int c = 0; c < 4; ++c) put_chunk(dz + 8 * c, dz1, dz2, tile_off(t, half * 4 + c, kLboP));
-            // Hprev half-row: activations of layer l-1 (tile-transposed buffer) or the staged input row
+            // Hprev half-row: activations of layer l-1 (prefetched from the tile-transposed buffer while the previous
+            // layer's MMAs ran) or the staged input row
             float hp[32];
             if (l > 0) {
-                const float4* src = reinterpret_cast<const float4*>(acts) + ((size_t)(l - 1) * n_tiles + tile) * (kTile * 16);
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const float4 v = __ldcs(src + (half * 8 + q) * kTile + t);
-                    hp[4 * q] = v.x; hp[4 * q + 1] = v.y; hp[4 * q + 2] = v.z; hp[4 * q + 3] = v.w;
-                }
+                for (int i = 0; i < 32; ++i) hp[i] = hp_next[i];
             } else {
                 cp_async_wait<0>();
                 __syncthreads();                                           // every thread's copies of the x tile landed
@@ -444,6 +454,7 @@ net_bwd_umma_kernel(const float* __restrict__ params, const float* __restrict__ 
                 }
                 umma_commit(bar);
             }
+            if (l > 1) load_act_half(acts, (size_t)(l - 2), n_tiles, tile, half, t, hp_next);   // in flight during the MMAs
             mbar_wait(bar, parity);
             parity ^= 1;
             tc_fence_after();
