@@ -415,14 +415,30 @@ class Optimizer:
             sky_idx = None
         return idx, sky_idx
 
-    def build_batch(self, keyframes, ignore_world_cube=False):
-        """One iteration's ray batch: per keyframe index draw + ray construction (optimizer.py:363-424)."""
+    def _fixed_schedule(self, keyframes):
+        """FIXED ray selection (optimizer.py:276-292): one pass over a random permutation of every scan, padded
+        to the longest scan with a second permutation; floor(max_len / num_rays) iterations."""
+        lengths = [len(kf.get_lidar_scan()) for kf in keyframes]
+        max_len = max(lengths)
+        full = torch.zeros((len(keyframes), max_len), dtype=torch.int64, device=self._device)
+        for k, n in enumerate(lengths):
+            full[k] = torch.cat((torch.randperm(n, device=self._device), torch.randperm(max_len - n, device=self._device)))
+        return full, int(max_len // self._num_lidar_samples)
+
+    def build_batch(self, keyframes, ignore_world_cube=False, fixed=None):
+        """One iteration's ray batch: per keyframe index draw + ray construction (optimizer.py:363-424).
+        fixed = (full_indices, it_idx, num_iterations) selects the FIXED-strategy slice (optimizer.py:302-308)."""
         rays, depths = [], []
         # one batched pose -> (R, origin) evaluation for the whole window (autograd reaches every pose leaf)
         poses = torch.stack([(kf._gt_pose if self._use_gt_poses else kf._pose).get_pose_tensor() for kf in keyframes])
         R, o = pose_to_rot_origin(poses, self._world_cube)
         for k, kf in enumerate(keyframes):
             idx, sky_idx = self._select_rays(kf)
+            if fixed is not None:
+                full, it_idx, n_it = fixed
+                nr = self._num_lidar_samples
+                lo, hi = max(int(nr * it_idx - 1), 0), min(int(nr * (it_idx + 1) - 1), int(n_it * nr))
+                idx = full[k, lo:hi]
             r, d = kf.build_lidar_rays(idx, self._ray_range, self._world_cube, self._use_gt_poses,
                                        ignore_world_cube=ignore_world_cube, sky_indices=sky_idx,
                                        rot_origin=(R[k], o[k]))
@@ -487,8 +503,11 @@ class Optimizer:
             self._optimizer = FusedAdam(groups)
             gamma = train.lrate_gamma
             all_params = [p for g in groups for p in g['params']]
+            fixed_full = None
+            if self._settings.rays_selection.strategy == 'FIXED':
+                fixed_full, s.num_iterations = self._fixed_schedule(active)
             for it_idx in range(s.num_iterations):
-                rays, depths = self.build_batch(active)
+                rays, depths = self.build_batch(active, fixed=None if fixed_full is None else (fixed_full, it_idx, s.num_iterations))
                 loss = self.compute_loss(None, (rays, depths), it_idx, tracking=tracking)
                 if self._settings.debug.log_losses:
                     self.losses_log.append(float(loss.detach()))

@@ -273,3 +273,30 @@ def test_eval_drivers_and_state_dict_keys():
     keys = set(opt._model.state_dict().keys())
     assert keys == {"nerf_model._model_sigma.params", "nerf_model._pos_encoding.params",
                     "nerf_model._dir_encoding.params", "nerf_model._model_intensity.params"}
+
+
+def test_fixed_ray_selection_schedule():
+    """FIXED strategy (reference optimizer.py:269-346): floor(max_len / num_rays) iterations over one permutation
+    per scan, slices [max(nr*i-1, 0), min(nr*(i+1)-1, n_it*nr))."""
+    from loner_b200 import mapping as M, synth
+    kfs, scale, shift = synth.make_keyframes(2, ray_range=(1.0, 30.0), seed=4)
+    s = M.default_settings(n_samples_train=64, log2_hashmap_size=14, lidar=4096, sky=0, voxel_size=32, num_iterations=999)
+    s["rays_selection"]["strategy"] = "FIXED"
+    opt = M.Optimizer(s, None, M.WorldCube(scale, shift), DEV)
+    win = [M.KeyFrame(M.LidarScanData(k.directions, k.distances, None), k.pose, device=DEV) for k in kfs]
+    full, n_it = opt._fixed_schedule(win)
+    n = [len(k.get_lidar_scan()) for k in win]
+    assert n_it == max(n) // 4096 and full.shape == (2, max(n))
+    for k in range(2):
+        assert torch.equal(full[k, :n[k]].sort().values, torch.arange(n[k], device=DEV))     # a permutation of the scan
+    seen = 0
+    for it in range(n_it):
+        rays, depths = opt.build_batch(win, ignore_world_cube=True, fixed=(full, it, n_it))
+        per_kf = rays.shape[0] // 2
+        assert per_kf == (4095 if it == 0 else 4096)         # the reference's "-1" offsets
+        seen += per_kf
+    assert seen == n_it * 4096 - 1
+    seen_steps = []
+    opt.compute_loss = (lambda f: (lambda *a, **k: (seen_steps.append(1), f(*a, **k))[1]))(opt.compute_loss)
+    opt.iterate_optimizer(win)
+    assert len(seen_steps) == n_it
