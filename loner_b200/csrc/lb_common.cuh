@@ -71,6 +71,16 @@ int lb_launch_mlp_fwd_umma(const lb_plan* plan, const float* mlp, const float* e
 int lb_launch_mlp_bwd_umma(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
                            const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st);
 
+// lb_encode.cu: leading dense levels of a "dense prefix + power-of-two hashed rest" plan (else -1); whether all levels
+// fit one L2-resident group
+int  lb_encode_dense_prefix(const lb_plan* plan);
+bool lb_encode_single_group(const lb_plan* plan);
+// lb_mlp_umma.cu: MLP backward + encode backward in one kernel (dL/denc never leaves the SM).  Returns 1 when the
+// configuration is not covered (caller runs the two separate kernels), 0 on success, < 0 on error.
+int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* params,
+                              const float* enc, const uint64_t* act, const float* d_sigma, size_t n_points, int n_samples,
+                              float* grad_params, float* d_rays, cudaStream_t st);
+
 static inline lb_level_table lb_make_level_table(const lb_plan* p) {
     lb_level_table t;
     memset(&t, 0, sizeof(t));

@@ -13,93 +13,14 @@
 // backward merges equal-cell runs inside the warp with a segmented shuffle reduction before issuing
 // red.global.add.v2.f32 (warp-aggregated atomics).
 #include "lb_common.cuh"
+#include "lb_encode.cuh"
 
 namespace {
 
+using namespace lb_enc;
+
 constexpr int kThreads = 128;
 constexpr int kPointsPerBlock = kThreads / 2;
-constexpr unsigned kFull = 0xffffffffu;
-
-struct Point {
-    float x, y, z;
-};
-
-template <bool kFromRays>
-__device__ __forceinline__ Point load_point(const float* __restrict__ rays, const float* __restrict__ zv,
-                                            const float* __restrict__ x01, size_t p, int n_samples, float* z_out) {
-    Point q;
-    if (kFromRays) {
-        const uint32_t r = (uint32_t)p / (uint32_t)n_samples;     // P < 2^32 (checked by the launchers)
-        const float* ray = rays + (size_t)r * LB_RAY_STRIDE;
-        const float z = __ldcs(zv + p);                            // use-once stream: evict-first, the tables keep the L2
-        // same roundings as the reference's torch ops (o + d*z, then (xyz+1)/2): at the finest level one
-        // ulp of x01 is 3 % of a cell, so the sample position must match bit for bit
-        q.x = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 0), __fmul_rn(__ldg(ray + 3), z)), 1.0f), 0.5f);
-        q.y = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 1), __fmul_rn(__ldg(ray + 4), z)), 1.0f), 0.5f);
-        q.z = __fmul_rn(__fadd_rn(__fadd_rn(__ldg(ray + 2), __fmul_rn(__ldg(ray + 5), z)), 1.0f), 0.5f);
-        if (z_out) *z_out = z;
-    } else {
-        q.x = __ldcs(x01 + 3 * p + 0);
-        q.y = __ldcs(x01 + 3 * p + 1);
-        q.z = __ldcs(x01 + 3 * p + 2);
-    }
-    return q;
-}
-
-// slow path (out-of-cube points on dense levels, non-power-of-two hashed levels): kept out of line so that the
-// sixteen unrolled level bodies stay small enough for the instruction cache
-__device__ __noinline__ uint4 wrap_indices(uint4 i, uint32_t size) {
-    return make_uint4(i.x % size, i.y % size, i.z % size, i.w % size);
-}
-
-// One lane's view of a level: cell, fractional position, its x-side weight and the entry indices of its four
-// (y,z) corners (k = by + 2*bz), level offset included.
-struct Side {
-    uint32_t idx[4];
-    float wx, wy[2], wz[2];
-    uint32_t cx, cy, cz;         // cell (for run detection)
-};
-
-template <bool kDense>
-__device__ __forceinline__ Side locate_side_t(const lb_level& L, const Point& q, int half) {
-    Side s;
-    const float px = fmaf(L.scale, q.x, 0.5f), py = fmaf(L.scale, q.y, 0.5f), pz = fmaf(L.scale, q.z, 0.5f);
-    const float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
-    s.cx = (uint32_t)(int)flx; s.cy = (uint32_t)(int)fly; s.cz = (uint32_t)(int)flz;
-    const float fx = px - flx, fy = py - fly, fz = pz - flz;
-    s.wx = half ? fx : 1.0f - fx;
-    s.wy[0] = 1.0f - fy; s.wy[1] = fy;
-    s.wz[0] = 1.0f - fz; s.wz[1] = fz;
-    const uint32_t x = s.cx + (uint32_t)half;
-    if (kDense) {
-        // x + y*res + z*res^2; tcnn wraps with "% size", which in-cube points never need
-        const uint32_t a0 = x + s.cy * L.res, a1 = a0 + L.res;
-        const uint32_t z0 = s.cz * L.res2, z1 = z0 + L.res2;
-        s.idx[0] = a0 + z0; s.idx[1] = a1 + z0; s.idx[2] = a0 + z1; s.idx[3] = a1 + z1;
-        if (s.idx[3] >= L.size || s.idx[0] >= L.size) {
-            const uint4 w = wrap_indices(make_uint4(s.idx[0], s.idx[1], s.idx[2], s.idx[3]), L.size);
-            s.idx[0] = w.x; s.idx[1] = w.y; s.idx[2] = w.z; s.idx[3] = w.w;
-        }
-    } else {
-        // coherent prime hash; a hashed level always has size = 2^log2_hashmap_size (lb_plan_create), so the
-        // "% size" of tcnn is a mask
-        const uint32_t y0 = s.cy * 2654435761u, y1 = y0 + 2654435761u;
-        const uint32_t z0 = s.cz * 805459861u, z1 = z0 + 805459861u;
-        s.idx[0] = (x ^ y0 ^ z0) & L.mask; s.idx[1] = (x ^ y1 ^ z0) & L.mask;
-        s.idx[2] = (x ^ y0 ^ z1) & L.mask; s.idx[3] = (x ^ y1 ^ z1) & L.mask;
-    }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) s.idx[k] += L.offset;
-    return s;
-}
-
-// kNDense >= 0: levels [0, kNDense) are dense and the rest hashed, resolved at compile time once the level loop
-// is unrolled (one index formula per level body instead of two); kNDense < 0: decided per level at run time
-template <int kNDense>
-__device__ __forceinline__ Side locate_side(const lb_level& L, const Point& q, int half, int l) {
-    if (kNDense >= 0) return (l < kNDense) ? locate_side_t<true>(L, q, half) : locate_side_t<false>(L, q, half);
-    return L.dense ? locate_side_t<true>(L, q, half) : locate_side_t<false>(L, q, half);
-}
 
 // ------------------------------------------------------------------------------------------
 // forward: enc[p][2l+f] = sum over 8 corners of w_c * table[idx_c][f]
@@ -167,24 +88,6 @@ encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// backward: table scatter-add (warp-aggregated) and optional dL/dx01
-// ------------------------------------------------------------------------------------------
-constexpr int kAggMaxRuns = 12;   // aggregate when the warp's 16 points fall into <= 12 distinct cells
-constexpr int kAggLevels = 8;     // only the coarse levels carry the run-merging code (instruction-cache budget);
-                                  // finer levels always scatter every corner, which is equally correct
-
-// segmented suffix sum over the warp's 16 points (2 lanes each): a run head collects its whole run.  Out of
-// line: one copy instead of 8 values x 8 levels, called convergently by all 32 lanes.
-__device__ __noinline__ float seg_suffix_sum(float v, int dist) {
-#pragma unroll
-    for (int off = 1; off < 16; off <<= 1) {
-        const float t = __shfl_down_sync(kFull, v, 2 * off);
-        if (off < dist) v += t;
-    }
-    return v;
-}
-
 template <bool kFromRays, bool kInputGrad, int kNDense>
 __global__ void __launch_bounds__(kThreads, 6)
 encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
@@ -221,116 +124,8 @@ encode_bwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
 #pragma unroll
             for (int i = 0; i < LB_MLP_IN; ++i) de[i] = 0.0f;
         }
-        // A sample whose upstream gradient row is exactly zero (ReLU-inactive density: dL/dsigma = 0, roughly
-        // every second sample while the field is young) scatters nothing: the L2 atomics are what bounds this
-        // kernel, so such points issue none.
-        uint32_t nz_bits = 0u;
-#pragma unroll
-        for (int i = 0; i < LB_MLP_IN; ++i) nz_bits |= __float_as_uint(de[i]);
-        const bool nonzero = (nz_bits << 1) != 0u;
-        if (__all_sync(kFull, !nonzero)) {                             // warp-uniform: nothing to scatter for these 16 points
-            if (kInputGrad && !kFromRays && valid && !half && l_begin == 0) { d_x01[3 * p + 0] = 0.0f; d_x01[3 * p + 1] = 0.0f; d_x01[3 * p + 2] = 0.0f; }
-            continue;
-        }
-        float gx = 0.0f, gy = 0.0f, gz = 0.0f;
-        bool all_distinct = false;     // once a level has 16 distinct cells, finer levels do too
-#pragma unroll
-        for (int l = 0; l < 16; ++l) {
-            if (l < l_begin || l >= l_end) continue;
-            const lb_level& L = T.lv[l];
-            const Side s = locate_side<kNDense>(L, q, half, l);
-            const float d0 = de[2 * l], d1 = de[2 * l + 1];
-            const uint32_t* idx = s.idx;
-            if (kInputGrad) {
-                float val[4], oth[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float2 v = __ldg(table + idx[k]);
-                    val[k] = fmaf(v.x, d0, v.y * d1);
-                }
-#pragma unroll
-                for (int k = 0; k < 4; ++k) oth[k] = __shfl_xor_sync(kFull, val[k], 1);
-                float tx = 0.0f;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) tx = fmaf(s.wy[k & 1] * s.wz[k >> 1], oth[k] - val[k], tx);
-                if (half) tx = 0.0f;                       // the even lane holds (x+1) - (x)
-                const float ty = s.wx * (s.wz[0] * (val[1] - val[0]) + s.wz[1] * (val[3] - val[2]));
-                const float tz = s.wx * (s.wy[0] * (val[2] - val[0]) + s.wy[1] * (val[3] - val[1]));
-                gx = fmaf(L.scale, tx, gx);
-                gy = fmaf(L.scale, ty, gy);
-                gz = fmaf(L.scale, tz, gz);
-            }
-            if (grad_table) {
-                float a[4], b[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float w = s.wx * s.wy[k & 1] * s.wz[k >> 1];
-                    a[k] = w * d0;
-                    b[k] = w * d1;
-                }
-                bool issue = valid && nonzero;
-                if (l < kAggLevels && !all_distinct) {
-                    // run detection over the warp's 16 points (previous point = lane - 2)
-                    const uint32_t pcx = __shfl_up_sync(kFull, s.cx, 2), pcy = __shfl_up_sync(kFull, s.cy, 2),
-                                   pcz = __shfl_up_sync(kFull, s.cz, 2);
-                    const int pvalid = __shfl_up_sync(kFull, (int)valid, 2);
-                    const bool same = (lane >= 2) && valid && pvalid && pcx == s.cx && pcy == s.cy && pcz == s.cz;
-                    const unsigned heads = __ballot_sync(kFull, !same) & 0x55555555u;
-                    const int runs = __popc(heads);
-                    if (runs == 16) {
-                        all_distinct = true;
-                    } else if (runs <= kAggMaxRuns) {
-                        // segmented suffix sum: the head point of each run collects the whole run
-                        const unsigned rest = (pair < 15) ? (heads >> (2 * pair + 2)) : 0u;
-                        const int dist = rest ? 1 + ((__ffs(rest) - 1) >> 1) : 16 - pair;   // points until the next head
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            a[k] = seg_suffix_sum(a[k], dist);
-                            b[k] = seg_suffix_sum(b[k], dist);
-                        }
-                        issue = valid && !same;      // a run head carries the run's sum (zero rows add zeros)
-                    }
-                }
-                if (issue) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) red_add_f32x2(grad_table + 2 * (size_t)idx[k], a[k], b[k]);
-                }
-            }
-        }
-        if (kInputGrad) {
-            gx += __shfl_xor_sync(kFull, gx, 1);
-            gy += __shfl_xor_sync(kFull, gy, 1);
-            gz += __shfl_xor_sync(kFull, gz, 1);
-            if (kFromRays) {
-                // d_o += G/2, d_d += z*G/2; one set of atomics per warp when it sits inside one ray
-                const bool mine = valid && !half;
-                float v[6] = {0.5f * gx, 0.5f * gy, 0.5f * gz, 0.5f * zval * gx, 0.5f * zval * gy, 0.5f * zval * gz};
-                if (!mine) {
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) v[i] = 0.0f;
-                }
-                const unsigned long long ray = valid ? (unsigned long long)((uint32_t)p / (uint32_t)n_samples) : ~0ull;
-                const unsigned long long r0 = __shfl_sync(kFull, ray, 0);
-                const bool uniform = __all_sync(kFull, !valid || ray == r0) && (r0 != ~0ull);
-                if (uniform) {
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) v[i] = warp_sum(v[i]);
-                    if (lane == 0) {
-#pragma unroll
-                        for (int i = 0; i < 6; ++i) atomicAdd(d_rays + r0 * LB_RAY_STRIDE + i, v[i]);
-                    }
-                } else if (mine) {
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) atomicAdd(d_rays + ray * LB_RAY_STRIDE + i, v[i]);
-                }
-            } else if (valid && !half) {
-                if (l_begin == 0) {
-                    d_x01[3 * p + 0] = gx; d_x01[3 * p + 1] = gy; d_x01[3 * p + 2] = gz;
-                } else {                                   // later level-group passes accumulate
-                    d_x01[3 * p + 0] += gx; d_x01[3 * p + 1] += gy; d_x01[3 * p + 2] += gz;
-                }
-            }
-        }
+        lb_enc::encode_bwd_point<kFromRays, kInputGrad, kNDense>(T, q, zval, de, valid, p, n_samples, table, grad_table,
+                                                                 d_rays, d_x01, l_begin, l_end);
     }
 }
 
@@ -392,6 +187,9 @@ int next_group_end(const lb_plan* plan, int l0) {
 }
 
 }  // namespace
+
+int lb_encode_dense_prefix(const lb_plan* plan) { return dense_prefix(plan); }
+bool lb_encode_single_group(const lb_plan* plan) { return next_group_end(plan, 0) >= plan->cfg.n_levels; }
 
 // internal launchers shared with lb_field.cu
 int lb_launch_encode_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* table,

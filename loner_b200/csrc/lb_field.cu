@@ -36,6 +36,11 @@ extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float*
     LB_REQUIRE(P < (size_t)1 << 32, "n_rays * n_samples must be below 2^32");
     if (P == 0) return LB_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if (rays && !d_x01) {      // one kernel for both stages when the configuration allows it (lb_mlp_umma.cu)
+        const int frc = lb_launch_sigma_bwd_fused(plan, rays, z, params, enc_inout, act, d_sigma, P, n_samples, grad_params,
+                                                  d_rays, st);
+        if (frc <= 0) return frc;
+    }
     int rc = lb_launch_mlp_bwd(plan, params, enc_inout, d_sigma, act, P, grad_params, st);
     if (rc) return rc;
     return lb_launch_encode_bwd(plan, rays, z, x01, params + LB_MLP_PARAMS, enc_inout, P, rays ? n_samples : 1,

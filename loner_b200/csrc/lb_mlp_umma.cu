@@ -26,7 +26,10 @@
 // so that one CTA's conversion / epilogue overlaps another's MMAs and global loads.
 #include <cuda_bf16.h>
 
+#include <stdlib.h>
+
 #include "lb_common.cuh"
+#include "lb_encode.cuh"
 #include "lb_umma.cuh"
 
 namespace {
@@ -437,6 +440,239 @@ mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, cons
     if (warp == 0) tmem_dealloc(tmem, kTmemCols);
 }
 
+// ------------------------------------------------------------------------------------------
+// fused backward: MLP backward + hash-grid scatter in ONE warp-specialised kernel.  dL/denc goes from tensor memory
+// through a shared-memory ring straight into the scatter warps: it is never written to (or re-read from) HBM, and the
+// HBM / tensor-core work of the MLP overlaps the L2-atomic-bound scatter.  One CTA of 768 threads per SM:
+//   warps 0-3  (producer): mlp_bwd_umma_kernel's tile loop -- cp.async-staged raw encoding tile -> E' = ds e as bf16
+//              pieces + mask tile -> MMAs (dE into TMEM, U accumulating) -> epilogue writes ds * dE rows into a ring slot
+//              and arrives on the slot's "full" mbarrier
+//   warps 4-27 (consumers; 4-23 with the dL/dx code): encode_bwd_kernel's per-warp work (16 points x 2 lanes, lb_encode.cuh); warp w takes the
+//              16-row units w, w + 24, ... in tile order, waits for the unit's slot, copies its rows to registers,
+//              releases the slot ("empty" mbarrier, 8 units per tile) and scatters.
+// A symmetric version (every warp alternating between the two phases behind CTA-wide barriers) was measured slower
+// than the two separate kernels (3.03 vs 2.88 ms): the scatter work per warp is data dependent and the barriers made
+// every warp wait for the slowest one on every tile.
+// ------------------------------------------------------------------------------------------
+constexpr int kRing = 3;
+constexpr int kProducerThreads = 128;
+// consumer warps: 24 when the scatter fits 72 registers (table gradient only), 20 with the dL/dx code (80 registers)
+template <bool kInputGrad> struct FusedShape {
+    static constexpr int kConsumerWarps = kInputGrad ? 20 : 24;
+    static constexpr int kThreads = kProducerThreads + 32 * kConsumerWarps;
+};
+struct FusedSmem {
+    static constexpr uint32_t mt = 0, e1 = mt + kMaskT, e2 = e1 + kPieceP, wa = e2 + kPieceP, wb = wa + kPieceW,
+                              raw = wb + kPieceW, ring = raw + 2 * kStage, bars = ring + kRing * kTile * kOutStride,
+                              tmem = bars + 8 * (1 + 2 * kRing), total = tmem + 8;
+};
+
+__device__ __forceinline__ void producer_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+template <bool kInputGrad, int kNDense>
+__global__ void __launch_bounds__(FusedShape<kInputGrad>::kThreads, 1)
+sigma_bwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
+                       const float* __restrict__ mlp, const float2* __restrict__ table, const float* __restrict__ enc,
+                       const float* __restrict__ d_sigma, const unsigned long long* __restrict__ act, size_t n_points,
+                       int n_samples, float* __restrict__ grad_mlp, float* __restrict__ grad_table,
+                       float* __restrict__ d_rays) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t bar_mma = smem_u32(sm + FusedSmem::bars);
+    const uint32_t bar_full = bar_mma + 8, bar_empty = bar_full + 8 * kRing;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + FusedSmem::tmem);
+    const size_t n_tiles = (n_points + kTile - 1) / kTile;
+
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    if (tid == 32) {
+        mbar_init(bar_mma, 1);
+        for (int i = 0; i < kRing; ++i) {
+            mbar_init(bar_full + 8 * i, kProducerThreads);
+            mbar_init(bar_empty + 8 * i, 8);
+        }
+    }
+    if (tid < kProducerThreads) {                                    // W1s[j,k] = w2[j] W1[j,k] as two bf16 pieces
+        const float* w2 = mlp + LB_MLP_W * LB_MLP_IN;
+        for (int it = tid; it < LB_MLP_W * 4; it += kProducerThreads) {
+            const int j = it >> 2, c = it & 3;
+            const float sc = __ldg(w2 + j);
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = __ldg(mlp + j * LB_MLP_IN + c * 8 + e) * sc;
+            uint32_t b1[4], b2[4];
+            split8<false>(v, b1, b2, nullptr);
+            *reinterpret_cast<uint4*>(sm + FusedSmem::wa + tile_off(j, c, kLboW)) = make_uint4(b1[0], b1[1], b1[2], b1[3]);
+            *reinterpret_cast<uint4*>(sm + FusedSmem::wb + tile_off(j, c, kLboW)) = make_uint4(b2[0], b2[1], b2[2], b2[3]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp < 4) {
+        // =============================== producer: MLP backward ===============================
+        const int t = tid;                                           // row of the tile = TMEM lane
+        const float* w2 = mlp + LB_MLP_W * LB_MLP_IN;
+        const uint32_t t_de = tmem, t_u = tmem + 32;
+        const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+        const uint32_t mt = smem_u32(sm + FusedSmem::mt), e1 = smem_u32(sm + FusedSmem::e1), e2 = smem_u32(sm + FusedSmem::e2);
+        const uint32_t wa = smem_u32(sm + FusedSmem::wa), wb = smem_u32(sm + FusedSmem::wb);
+        const uint32_t raw = smem_u32(sm + FusedSmem::raw);
+        constexpr uint32_t idesc_de = umma_idesc(128, LB_MLP_IN, 0, 1);
+        constexpr uint32_t idesc_u = umma_idesc(64, LB_MLP_IN, 1, 1);
+        size_t tile = blockIdx.x;
+        if (tile < n_tiles) stage_tile(enc, tile, n_points, raw);
+        cp_async_commit();
+        uint32_t parity = 0;
+        for (uint32_t kt = 0; tile < n_tiles; tile += gridDim.x, ++kt) {
+            const size_t p = tile * (size_t)kTile + t;
+            float ds = 0.0f;
+            unsigned long long bits = 0ull;
+            if (p < n_points) { ds = __ldg(d_sigma + p); bits = __ldg(act + p); }
+            const size_t next = tile + gridDim.x;
+            if (next < n_tiles) stage_tile(enc, next, n_points, raw + ((kt + 1) & 1u) * kStage);
+            cp_async_commit();
+            cp_async_wait<1>();
+            producer_barrier();                                      // this tile's raw rows have landed
+            {
+                const uint8_t* row = sm + FusedSmem::raw + (kt & 1u) * kStage + t * kRowStride;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {                        // E' = ds e, four 8-column chunks
+                    const float4 a = *reinterpret_cast<const float4*>(row + c * 32);
+                    const float4 b = *reinterpret_cast<const float4*>(row + c * 32 + 16);
+                    const float v[8] = {ds * a.x, ds * a.y, ds * a.z, ds * a.w, ds * b.x, ds * b.y, ds * b.z, ds * b.w};
+                    uint32_t b1[4], b2[4];
+                    split8<false>(v, b1, b2, nullptr);
+                    const uint32_t off = tile_off(t, c, kLboP);
+                    *reinterpret_cast<uint4*>(sm + FusedSmem::e1 + off) = make_uint4(b1[0], b1[1], b1[2], b1[3]);
+                    *reinterpret_cast<uint4*>(sm + FusedSmem::e2 + off) = make_uint4(b2[0], b2[1], b2[2], b2[3]);
+                }
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {                        // mask tile: 8 chunks of 8 hidden units
+                    const uint32_t b = (uint32_t)(bits >> (8 * c)) & 0xffu;
+                    uint4 v;
+                    v.x = ((b & 1u) ? 0x3f80u : 0u) | ((b & 2u) ? 0x3f800000u : 0u);
+                    v.y = ((b & 4u) ? 0x3f80u : 0u) | ((b & 8u) ? 0x3f800000u : 0u);
+                    v.z = ((b & 16u) ? 0x3f80u : 0u) | ((b & 32u) ? 0x3f800000u : 0u);
+                    v.w = ((b & 64u) ? 0x3f80u : 0u) | ((b & 128u) ? 0x3f800000u : 0u);
+                    *reinterpret_cast<uint4*>(sm + FusedSmem::mt + tile_off(t, c, kLboP)) = v;
+                }
+            }
+            fence_async_smem();
+            tc_fence_before();
+            producer_barrier();
+            if (tid == 0) {
+                tc_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {                     // dE = M (128 x 64) . W1s (64 x 32)
+                    const uint64_t da = umma_desc(mt + ks * 2 * kLboP, kLboP, 128);
+                    umma_bf16(t_de, da, umma_desc(wa + ks * 256, 128, kLboW), idesc_de, ks > 0);
+                    umma_bf16(t_de, da, umma_desc(wb + ks * 256, 128, kLboW), idesc_de, 1);
+                }
+                if (grad_mlp) {                                      // U += M^T (64 x 128) . E' (128 x 32)
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks) {
+                        const uint64_t da = umma_desc(mt + ks * 256, 128, kLboP);
+                        umma_bf16(t_u, da, umma_desc(e1 + ks * 256, 128, kLboP), idesc_u, (kt > 0 || ks > 0) ? 1u : 0u);
+                        umma_bf16(t_u, da, umma_desc(e2 + ks * 256, 128, kLboP), idesc_u, 1);
+                    }
+                }
+                umma_commit(bar_mma);
+            }
+            const uint32_t slot = kt % kRing;
+            if (kt >= kRing) mbar_wait(bar_empty + 8 * slot, ((kt / kRing) - 1) & 1u);   // consumers released this slot
+            mbar_wait(bar_mma, parity);
+            parity ^= 1;
+            tc_fence_after();
+            {   // epilogue: ds * dE row t -> ring slot
+                uint32_t r[32];
+                tmem_ld32(t_de + lane_off, r);
+                tmem_ld_wait();
+                float4* dst = reinterpret_cast<float4*>(sm + FusedSmem::ring + slot * (kTile * kOutStride) + t * kOutStride);
+#pragma unroll
+                for (int qd = 0; qd < 8; ++qd)
+                    dst[qd] = make_float4(ds * __uint_as_float(r[4 * qd]), ds * __uint_as_float(r[4 * qd + 1]),
+                                          ds * __uint_as_float(r[4 * qd + 2]), ds * __uint_as_float(r[4 * qd + 3]));
+            }
+            tc_fence_before();
+            mbar_arrive(bar_full + 8 * slot);                        // release: the row above is visible to the waiters
+        }
+        cp_async_wait<0>();
+        producer_barrier();
+        if (grad_mlp && blockIdx.x < n_tiles) {                      // weight gradients from U (M = 64 layout)
+            tc_fence_after();
+            uint32_t r[32];
+            tmem_ld32(t_u + lane_off, r);
+            tmem_ld_wait();
+            if (lane < 16) {
+                const int j = warp * 16 + lane;
+                const float w2j = __ldg(w2 + j);
+                float dw2 = 0.0f;
+#pragma unroll
+                for (int k = 0; k < LB_MLP_IN; ++k) {
+                    const float u = __uint_as_float(r[k]);
+                    atomicAdd(grad_mlp + j * LB_MLP_IN + k, w2j * u);
+                    dw2 = fmaf(__ldg(mlp + j * LB_MLP_IN + k), u, dw2);
+                }
+                atomicAdd(grad_mlp + LB_MLP_W * LB_MLP_IN + j, dw2);
+            }
+        }
+    } else {
+        // =============================== consumers: hash-grid scatter ===============================
+        const int cw = warp - 4;
+        const size_t my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+        for (size_t u = cw; u < my_tiles * 8; u += FusedShape<kInputGrad>::kConsumerWarps) {
+            const uint32_t kt = (uint32_t)(u >> 3);
+            const int row = (int)(u & 7) * 16 + (lane >> 1);
+            const size_t tile = blockIdx.x + (size_t)kt * gridDim.x;
+            const size_t p = tile * (size_t)kTile + row;
+            const bool valid = p < n_points;
+            lb_enc::Point q = {0.5f, 0.5f, 0.5f};
+            float zval = 0.0f;
+            if (valid) q = lb_enc::load_point<true>(rays, zv, nullptr, p, n_samples, &zval);
+            const uint32_t slot = kt % kRing;
+            mbar_wait(bar_full + 8 * slot, (kt / kRing) & 1u);
+            float de[LB_MLP_IN];
+            {
+                const float4* src = reinterpret_cast<const float4*>(sm + FusedSmem::ring + slot * (kTile * kOutStride) + row * kOutStride);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 v = src[i];
+                    de[4 * i] = v.x; de[4 * i + 1] = v.y; de[4 * i + 2] = v.z; de[4 * i + 3] = v.w;
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_empty + 8 * slot);        // this unit's rows are in registers
+            lb_enc::encode_bwd_point<true, kInputGrad, kNDense>(T, q, zval, de, valid, p, n_samples, table, grad_table,
+                                                                d_rays, nullptr, 0, T.n_levels);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, kTmemCols);
+}
+
+template <bool kInputGrad, int kNDense>
+int launch_fused(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* params,
+                 const float* enc, const uint64_t* act, const float* d_sigma, size_t n_points, int n_samples,
+                 float* grad_params, float* d_rays, cudaStream_t st) {
+    auto kern = sigma_bwd_fused_kernel<kInputGrad, kNDense>;
+    int rc = lb_check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FusedSmem::total),
+                           "sigma_bwd_fused smem opt-in");
+    if (rc) return rc;
+    const size_t tiles = (n_points + kTile - 1) / kTile;
+    const size_t cap = (size_t)plan->sm_count;
+    kern<<<(int)(tiles < cap ? tiles : cap), FusedShape<kInputGrad>::kThreads, FusedSmem::total, st>>>(
+        T, rays, z, params, reinterpret_cast<const float2*>(params + LB_MLP_PARAMS), enc, d_sigma,
+        reinterpret_cast<const unsigned long long*>(act), n_points, n_samples, grad_params,
+        grad_params ? grad_params + LB_MLP_PARAMS : nullptr, d_rays);
+    return lb_check_cuda(cudaGetLastError(), "sigma_bwd_fused launch");
+}
+
 int umma_grid(int sm_count, size_t n_points, int ctas_per_sm) {
     const size_t tiles = (n_points + kTile - 1) / kTile;
     const size_t cap = (size_t)sm_count * ctas_per_sm;
@@ -471,4 +707,29 @@ int lb_launch_mlp_bwd_umma(const lb_plan* plan, const float* mlp, float* enc_ino
     mlp_bwd_umma_kernel<<<umma_grid(plan->sm_count, n_points, kBwdCtasPerSm), kThreads, BwdSmem::total, st>>>(
         mlp, enc_inout, d_sigma, reinterpret_cast<const unsigned long long*>(act), n_points, grad_mlp);
     return lb_check_cuda(cudaGetLastError(), "mlp_bwd_umma launch");
+}
+
+int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* params,
+                              const float* enc, const uint64_t* act, const float* d_sigma, size_t n_points, int n_samples,
+                              float* grad_params, float* d_rays, cudaStream_t st) {
+    static int disabled = -1;
+    if (disabled < 0) {
+        const char* e = getenv("LONER_B200_FUSED_BWD");
+        disabled = (e && e[0] == '0') ? 1 : 0;
+    }
+    const int nd = lb_encode_dense_prefix(plan);
+    if (disabled || !rays || !act || nd < 1 || !lb_encode_single_group(plan) || plan->cfg.n_levels != 16) return 1;
+    const lb_level_table T = lb_make_level_table(plan);
+#define LB_FUSED_CASE(ND)                                                                                                   \
+    case ND:                                                                                                                \
+        return d_rays ? launch_fused<true, ND>(plan, T, rays, z, params, enc, act, d_sigma, n_points, n_samples, grad_params, d_rays, st) \
+                      : launch_fused<false, ND>(plan, T, rays, z, params, enc, act, d_sigma, n_points, n_samples, grad_params, d_rays, st);
+    switch (nd) {
+        LB_FUSED_CASE(1)
+        LB_FUSED_CASE(2)
+        LB_FUSED_CASE(3)
+        LB_FUSED_CASE(4)
+        default: return 1;
+    }
+#undef LB_FUSED_CASE
 }
