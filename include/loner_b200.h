@@ -135,10 +135,13 @@ LB_API int lb_encode_bwd(const lb_plan* plan, const float* x01, const float* tab
  * fused with xyz = o + d*z and pos01 = (xyz+1)/2 (src/models/rendering_tcnn.py:390, nerf_tcnn.py:63).
  * Point source: either (rays,z) with P = n_rays*n_samples, or x01 [P,3] when rays == NULL
  * (then n_rays = P, n_samples = 1).  params = [mlp | table] flat fp32 (tcnn layout).
- * sigma [P]; enc [P,32] (required) receives the encodings: it is the hand-off between the encode and
- * the MLP kernel and must be kept for lb_sigma_bwd.  act [P] uint64 receives the ReLU bit mask of the 64
- * hidden units; when non-NULL the MLP runs on the tcgen05 tensor cores (bf16-split operands, fp32
- * accumulate in TMEM) and act must be handed to lb_sigma_bwd; NULL selects the fp32 CUDA-core MLP. */
+ * sigma [P]; enc [P,32] receives the encodings and must be kept for lb_sigma_bwd.  act [P] uint64 receives
+ * the ReLU bit mask of the 64 hidden units; when non-NULL the MLP runs on the tcgen05 tensor cores (exact
+ * tf32 hi/lo split operands, fp32 accumulate in TMEM) and act must be handed to lb_sigma_bwd; NULL selects
+ * the fp32 CUDA-core MLP.  With (rays, z) on a plan for which lb_sigma_fwd_enc_optional() returns 1, gather and
+ * MLP run as ONE kernel (the encodings are handed over in shared memory); enc may then be NULL for inference
+ * (nothing is saved).  In every other case enc is required: it is the hand-off between the two kernels. */
+LB_API int lb_sigma_fwd_enc_optional(const lb_plan* plan);
 LB_API int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
                  const float* params, int n_rays, int n_samples, float* sigma, float* enc,
                  uint64_t* act, void* stream);

@@ -77,6 +77,9 @@ int  lb_encode_dense_prefix(const lb_plan* plan);
 bool lb_encode_single_group(const lb_plan* plan);
 // lb_mlp_umma.cu: MLP backward + encode backward in one kernel (dL/denc never leaves the SM).  Returns 1 when the
 // configuration is not covered (caller runs the two separate kernels), 0 on success, < 0 on error.
+bool lb_sigma_fwd_fused_covers(const lb_plan* plan);
+int lb_launch_sigma_fwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* params, size_t n_points,
+                              int n_samples, float* sigma, float* enc, uint64_t* act, cudaStream_t st);
 int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* params,
                               const float* enc, const uint64_t* act, const float* d_sigma, size_t n_points, int n_samples,
                               float* grad_params, float* d_rays, cudaStream_t st);

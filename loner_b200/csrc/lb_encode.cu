@@ -36,38 +36,10 @@ encode_fwd_kernel(lb_level_table T, const float* __restrict__ rays, const float*
     for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const size_t p = tile * kPointsPerBlock + (threadIdx.x >> 1);
         const bool valid = p < n_points;
-        float part[LB_MLP_IN];
         Point q = {0.5f, 0.5f, 0.5f};
         if (valid) q = load_point<kFromRays>(rays, zv, x01, p, n_samples, nullptr);
-#pragma unroll
-        for (int l = 0; l < 16; ++l) {
-            float a = 0.0f, b = 0.0f;
-            if (l >= l_begin && l < l_end) {                       // level-group pass (whole range when the tables fit L2)
-                const lb_level& L = T.lv[l];
-                const Side s = locate_side<kNDense>(L, q, half, l);
-                float2 v[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) v[k] = __ldg(table + s.idx[k]);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float w = s.wy[k & 1] * s.wz[k >> 1];
-                    a = fmaf(w, v[k].x, a);
-                    b = fmaf(w, v[k].y, b);
-                }
-                a *= s.wx;
-                b *= s.wx;
-            }
-            part[2 * l] = a;
-            part[2 * l + 1] = b;
-        }
-        // pair exchange: the even lane finishes features 0-15, the odd lane features 16-31
         float out[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const float send = half ? part[i] : part[16 + i];
-            const float recv = __shfl_xor_sync(kFull, send, 1);
-            out[i] = (half ? part[16 + i] : part[i]) + recv;
-        }
+        encode_fwd_point<kNDense>(T, q, half, table, l_begin, l_end, out);
         if (valid) {
             if (width == LB_MLP_IN) {
                 // one float4 = two levels; a pass stores only its own columns (passes start on even levels)

@@ -90,6 +90,42 @@ __device__ __forceinline__ Side locate_side(const lb_level& L, const Point& q, i
     return L.dense ? locate_side_t<true>(L, q, half) : locate_side_t<false>(L, q, half);
 }
 
+// One lane's forward: gathers the 4 (y,z) corners of its x-side on every level in [l_begin, l_end), then the pair
+// exchange: the even lane ends up with features 0-15 of the point, the odd lane with features 16-31 (zeros for
+// levels outside the range).  Called convergently by both lanes of a pair.
+template <int kNDense>
+__device__ __forceinline__ void encode_fwd_point(const lb_level_table& T, const Point& q, int half,
+                                                 const float2* __restrict__ table, int l_begin, int l_end, float* out) {
+    float part[LB_MLP_IN];
+#pragma unroll
+    for (int l = 0; l < 16; ++l) {
+        float a = 0.0f, b = 0.0f;
+        if (l >= l_begin && l < l_end) {                       // level-group pass (whole range when the tables fit L2)
+            const lb_level& L = T.lv[l];
+            const Side s = locate_side<kNDense>(L, q, half, l);
+            float2 v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v[k] = __ldg(table + s.idx[k]);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float w = s.wy[k & 1] * s.wz[k >> 1];
+                a = fmaf(w, v[k].x, a);
+                b = fmaf(w, v[k].y, b);
+            }
+            a *= s.wx;
+            b *= s.wx;
+        }
+        part[2 * l] = a;
+        part[2 * l + 1] = b;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float send = half ? part[i] : part[16 + i];
+        const float recv = __shfl_xor_sync(kFull, send, 1);
+        out[i] = (half ? part[16 + i] : part[i]) + recv;
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // backward: table scatter-add (warp-aggregated) and optional dL/dx01
 // ------------------------------------------------------------------------------------------

@@ -9,18 +9,26 @@
 extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
                             const float* params, int n_rays, int n_samples, float* sigma, float* enc,
                             uint64_t* act, void* stream) {
-    LB_REQUIRE(plan && params && sigma && enc, "null pointer (enc [P,32] is required: it is the encode->MLP hand-off)");
+    LB_REQUIRE(plan && params && sigma, "null pointer");
     LB_REQUIRE((rays && z) || x01, "need (rays, z) or x01");
+    LB_REQUIRE(enc || (rays && lb_sigma_fwd_fused_covers(plan)),
+               "enc [P,32] is required: it is the encode->MLP hand-off unless lb_sigma_fwd_enc_optional(plan)");
     LB_REQUIRE(plan->cfg.n_levels * LB_FEATS == LB_MLP_IN, "fused sigma head needs 16 levels x 2 features");
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1, "bad sizes");
     const size_t P = (size_t)n_rays * (size_t)n_samples;
     LB_REQUIRE(P < (size_t)1 << 32, "n_rays * n_samples must be below 2^32");
     if (P == 0) return LB_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if (rays && (act || !enc)) {   // one kernel for both stages when the configuration allows it (lb_mlp_umma.cu)
+        const int frc = lb_launch_sigma_fwd_fused(plan, rays, z, params, P, n_samples, sigma, enc, act, st);
+        if (frc <= 0) return frc;
+    }
     int rc = lb_launch_encode_fwd(plan, rays, z, x01, params + LB_MLP_PARAMS, P, rays ? n_samples : 1, enc, st);
     if (rc) return rc;
     return lb_launch_mlp_fwd(plan, params, enc, P, sigma, act, st);
 }
+
+extern "C" int lb_sigma_fwd_enc_optional(const lb_plan* plan) { return plan && lb_sigma_fwd_fused_covers(plan) ? 1 : 0; }
 
 extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
                             const float* params, float* enc_inout, const uint64_t* act, const float* d_sigma,

@@ -673,6 +673,193 @@ int launch_fused(const lb_plan* plan, const lb_level_table& T, const float* rays
     return lb_check_cuda(cudaGetLastError(), "sigma_bwd_fused launch");
 }
 
+// ------------------------------------------------------------------------------------------
+// fused forward: hash-grid gather + MLP in one launch.
+//
+// 24 gather warps (the 2-lanes-per-point walk of lb_encode.cu, 16 points per warp-unit) write their rows into a
+// 4-tile shared-memory ring (and to `enc` for the backward when it is non-NULL); 4 MLP warps take each full tile
+// through the tf32 / TMEM-operand pipeline of mlp_fwd_umma_kernel.  The hand-off never leaves the SM, so the MLP's
+// re-read of the encodings (128 B per point) and its launch disappear behind the gather, which stays bound by L2
+// sector fills.  A / H are double-buffered in TMEM: the MMAs of tile k run under the epilogue of tile k - 1.
+// ------------------------------------------------------------------------------------------
+constexpr int kFwdRing = 4;
+constexpr int kGatherWarps = 24;
+constexpr int kFusedFwdThreads = kProducerThreads + 32 * kGatherWarps;
+constexpr uint32_t kFusedFwdTmemCols = 256;        // H0 64 | H1 64 | A0 hi 32 lo 32 | A1 hi 32 lo 32
+struct FusedFwdSmem {
+    static constexpr uint32_t ring = 0, whi = ring + kFwdRing * kStage, wlo = whi + 8 * kLboW, w2 = wlo + 8 * kLboW,
+                              v = w2 + 64 * 4, bars = v + 32 * 4, tmem = bars + 8 * (2 + 2 * kFwdRing), total = tmem + 8;
+};
+
+template <int kNDense>
+__global__ void __launch_bounds__(kFusedFwdThreads, 1)
+sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
+                       const float* __restrict__ mlp, const float2* __restrict__ table, size_t n_points, int n_samples,
+                       float* __restrict__ sigma, float* __restrict__ enc, unsigned long long* __restrict__ act) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t bar_mma = smem_u32(sm + FusedFwdSmem::bars);
+    const uint32_t bar_full = bar_mma + 16, bar_empty = bar_full + 8 * kFwdRing;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + FusedFwdSmem::tmem);
+    float* w2s = reinterpret_cast<float*>(sm + FusedFwdSmem::w2);
+    float* vs = reinterpret_cast<float*>(sm + FusedFwdSmem::v);
+    const size_t n_tiles = (n_points + kTile - 1) / kTile;
+    const size_t my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kFusedFwdTmemCols);
+    if (tid == 32) {
+        mbar_init(bar_mma, 1);
+        mbar_init(bar_mma + 8, 1);
+        for (int i = 0; i < kFwdRing; ++i) {
+            mbar_init(bar_full + 8 * i, 8);
+            mbar_init(bar_empty + 8 * i, 4);
+        }
+    }
+    if (tid < kProducerThreads) {
+        convert_weights_tf32(mlp, sm + FusedFwdSmem::whi, sm + FusedFwdSmem::wlo);
+        if (tid < LB_MLP_W) w2s[tid] = 0.5f * __ldg(mlp + LB_MLP_W * LB_MLP_IN + tid);
+        if (tid >= 64 && tid < 64 + LB_MLP_IN) {                     // v = W1^T w2 / 2 (see mlp_fwd_umma_kernel)
+            const int k = tid - 64;
+            float a = 0.0f;
+            for (int j = 0; j < LB_MLP_W; ++j)
+                a = fmaf(0.5f * __ldg(mlp + LB_MLP_W * LB_MLP_IN + j), __ldg(mlp + j * LB_MLP_IN + k), a);
+            vs[k] = a;
+        }
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp < 4) {
+        // =============================== MLP warps ===============================
+        const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+        const uint32_t bhi = smem_u32(sm + FusedFwdSmem::whi), blo = smem_u32(sm + FusedFwdSmem::wlo);
+        constexpr uint32_t idesc = umma_idesc_tf32(128, LB_MLP_W);
+        float lin_prev = 0.0f;
+        for (uint32_t kt = 0; kt <= my_tiles; ++kt) {
+            const uint32_t b = kt & 1u;
+            float lin = 0.0f;
+            if (kt < my_tiles) {
+                const uint32_t slot = kt % kFwdRing;
+                const uint32_t t_ahi = tmem + 128 + b * 64, t_alo = t_ahi + 32;
+                mbar_wait(bar_full + 8 * slot, (kt / kFwdRing) & 1u);
+                const uint8_t* row = sm + FusedFwdSmem::ring + slot * kStage + tid * kRowStride;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t hi[16], lo[16];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float4 v = *reinterpret_cast<const float4*>(row + (h * 4 + q) * 16);
+                        const float4 c = *reinterpret_cast<const float4*>(vs + (h * 4 + q) * 4);
+                        lin = fmaf(v.x, c.x, lin); lin = fmaf(v.y, c.y, lin);
+                        lin = fmaf(v.z, c.z, lin); lin = fmaf(v.w, c.w, lin);
+                        uint4 a, d;
+                        split_tf32(v, a, d);
+                        hi[4 * q] = a.x; hi[4 * q + 1] = a.y; hi[4 * q + 2] = a.z; hi[4 * q + 3] = a.w;
+                        lo[4 * q] = d.x; lo[4 * q + 1] = d.y; lo[4 * q + 2] = d.z; lo[4 * q + 3] = d.w;
+                    }
+                    tmem_st16(t_ahi + lane_off + h * 16, hi);
+                    tmem_st16(t_alo + lane_off + h * 16, lo);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_empty + 8 * slot);    // the rows of this warp are in registers / TMEM
+                tmem_st_wait();
+            }
+            tc_fence_before();
+            producer_barrier();        // A[b] complete; every thread's epilogue of tile kt - 2 (the last user of H[b]) is done
+            if (tid == 0 && kt < my_tiles) {
+                tc_fence_after();
+                const uint32_t t_h = tmem + b * 64, t_ahi = tmem + 128 + b * 64, t_alo = t_ahi + 32;
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const uint64_t dbh = umma_desc(bhi + ks * 2 * kLboW, kLboW, 128);
+                    const uint64_t dbl = umma_desc(blo + ks * 2 * kLboW, kLboW, 128);
+                    umma_tf32_ts(t_h, t_ahi + ks * 8, dbh, idesc, ks > 0);
+                    umma_tf32_ts(t_h, t_ahi + ks * 8, dbl, idesc, 1);
+                    umma_tf32_ts(t_h, t_alo + ks * 8, dbh, idesc, 1);
+                }
+                umma_commit(bar_mma + 8 * b);
+            }
+            if (kt > 0) {              // epilogue of tile kt - 1 while the tensor pipe works on tile kt
+                const uint32_t pb = b ^ 1u, pk = kt - 1;
+                mbar_wait(bar_mma + 8 * pb, (pk >> 1) & 1u);
+                tc_fence_after();
+                float s = lin_prev;
+                unsigned long long bits = 0ull;
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    uint32_t r[32];
+                    tmem_ld32(tmem + pb * 64 + lane_off + half * 32, r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int g = 0; g < 2; ++g) {
+                        float mf = 0.0f;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const float h = __uint_as_float(r[g * 16 + j]);
+                            s = fmaf(w2s[half * 32 + g * 16 + j], fabsf(h), s);
+                            mf = fmaf(__saturatef(h * 8.507059173e37f), (float)(1u << j), mf);
+                        }
+                        const uint32_t m16 = __float_as_uint(mf + 8388608.0f) & 0xffffu;
+                        bits |= (unsigned long long)m16 << (32 * half + 16 * g);
+                    }
+                }
+                const size_t p = (blockIdx.x + (size_t)pk * gridDim.x) * (size_t)kTile + tid;
+                if (p < n_points) {
+                    sigma[p] = s;
+                    if (act) act[p] = bits;
+                }
+            }
+            lin_prev = lin;
+        }
+    } else {
+        // =============================== gather warps ===============================
+        const int cw = warp - 4, half = lane & 1;
+        for (size_t u = cw; u < my_tiles * 8; u += kGatherWarps) {
+            const uint32_t kt = (uint32_t)(u >> 3);
+            const int row = (int)(u & 7) * 16 + (lane >> 1);
+            const size_t p = (blockIdx.x + (size_t)kt * gridDim.x) * (size_t)kTile + row;
+            const bool valid = p < n_points;
+            lb_enc::Point q = {0.5f, 0.5f, 0.5f};
+            if (valid) q = lb_enc::load_point<true>(rays, zv, nullptr, p, n_samples, nullptr);
+            float out[16];
+            lb_enc::encode_fwd_point<kNDense>(T, q, half, table, 0, 16, out);
+            const uint32_t slot = kt % kFwdRing;
+            if (kt >= kFwdRing) mbar_wait(bar_empty + 8 * slot, ((kt / kFwdRing) - 1) & 1u);
+            float4* dst = reinterpret_cast<float4*>(sm + FusedFwdSmem::ring + slot * kStage + row * kRowStride + half * 64);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dst[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_full + 8 * slot);
+            if (enc && valid) {
+                float4* g = reinterpret_cast<float4*>(enc + p * LB_MLP_IN + half * 16);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) __stcs(g + i, make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]));
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, kFusedFwdTmemCols);
+}
+
+template <int kNDense>
+int launch_fused_fwd(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* params,
+                     size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act, cudaStream_t st) {
+    auto kern = sigma_fwd_fused_kernel<kNDense>;
+    int rc = lb_check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FusedFwdSmem::total),
+                           "sigma_fwd_fused smem opt-in");
+    if (rc) return rc;
+    const size_t tiles = (n_points + kTile - 1) / kTile;
+    const size_t cap = (size_t)plan->sm_count;
+    kern<<<(int)(tiles < cap ? tiles : cap), kFusedFwdThreads, FusedFwdSmem::total, st>>>(
+        T, rays, z, params, reinterpret_cast<const float2*>(params + LB_MLP_PARAMS), n_points, n_samples, sigma, enc,
+        reinterpret_cast<unsigned long long*>(act));
+    return lb_check_cuda(cudaGetLastError(), "sigma_fwd_fused launch");
+}
+
 int umma_grid(int sm_count, size_t n_points, int ctas_per_sm) {
     const size_t tiles = (n_points + kTile - 1) / kTile;
     const size_t cap = (size_t)sm_count * ctas_per_sm;
@@ -732,4 +919,27 @@ int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const floa
         default: return 1;
     }
 #undef LB_FUSED_CASE
+}
+
+bool lb_sigma_fwd_fused_covers(const lb_plan* plan) {
+    static int disabled = -1;
+    if (disabled < 0) {
+        const char* e = getenv("LONER_B200_FUSED_FWD");
+        disabled = (e && e[0] == '0') ? 1 : 0;
+    }
+    return !disabled && lb_encode_dense_prefix(plan) >= 1 && lb_encode_single_group(plan) && plan->cfg.n_levels == 16;
+}
+
+// returns 1 when the configuration is not covered (the caller then runs the two-kernel path)
+int lb_launch_sigma_fwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* params, size_t n_points,
+                              int n_samples, float* sigma, float* enc, uint64_t* act, cudaStream_t st) {
+    if (!rays || !lb_sigma_fwd_fused_covers(plan)) return 1;
+    const lb_level_table T = lb_make_level_table(plan);
+    switch (lb_encode_dense_prefix(plan)) {
+        case 1: return launch_fused_fwd<1>(plan, T, rays, z, params, n_points, n_samples, sigma, enc, act, st);
+        case 2: return launch_fused_fwd<2>(plan, T, rays, z, params, n_points, n_samples, sigma, enc, act, st);
+        case 3: return launch_fused_fwd<3>(plan, T, rays, z, params, n_points, n_samples, sigma, enc, act, st);
+        case 4: return launch_fused_fwd<4>(plan, T, rays, z, params, n_points, n_samples, sigma, enc, act, st);
+        default: return 1;
+    }
 }

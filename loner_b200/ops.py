@@ -46,6 +46,7 @@ class Plan:
         self.n_params = a.value + b.value
         self.n_levels = n_levels
         self.n_enc = n_levels * n_features_per_level
+        self.enc_optional = bool(_lib.load().lb_sigma_fwd_enc_optional(self._h))
 
     @classmethod
     def from_tcnn_config(cls, encoding_config, network_config=None):
@@ -158,10 +159,11 @@ def sigma_fwd(plan, params, rays=None, z=None, x01=None, save_enc=True, tensor_c
         n, s = x01.shape[0], 1
         shape = (n,)
     sigma = torch.empty(shape, device=params.device, dtype=torch.float32)
-    # the encodings are the encode -> MLP hand-off, so the buffer always exists; `save_enc` only says whether
-    # the caller intends to keep it (and the ReLU masks) for lb_sigma_bwd
-    enc = torch.empty(n * s, plan.n_enc, device=params.device, dtype=torch.float32)
-    act = torch.empty(n * s, device=params.device, dtype=torch.int64) if tensor_cores else None
+    # the encodings are the encode -> MLP hand-off of the two-kernel path; the fused gather + MLP kernel needs
+    # neither buffer when nothing is kept for lb_sigma_bwd
+    inference = (not save_enc) and rays is not None and tensor_cores and plan.enc_optional
+    enc = None if inference else torch.empty(n * s, plan.n_enc, device=params.device, dtype=torch.float32)
+    act = torch.empty(n * s, device=params.device, dtype=torch.int64) if (tensor_cores and not inference) else None
     _lib.call("lb_sigma_fwd", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
               _p(params, name="params"), n, s, _p(sigma), _p(enc), _p(act, torch.int64), _stream())
     return sigma, ((enc, act) if save_enc else None)

@@ -177,6 +177,36 @@ def test_sigma_fwd_bwd_golden(name, tc, dev, ops, O):
     assert rel_err(dr3, dr) < 1e-5
 
 
+@pytest.mark.parametrize("n,s", [(1, 1), (3, 7), (5, 128), (300, 129), (4099, 64)])
+def test_fused_sigma_forward_matches_two_kernel_path(n, s, dev, ops):
+    """The one-kernel gather + MLP forward (rays, ring hand-off in shared memory) against the two-kernel path (x01
+    point source): identical encodings, sigma and masks; ragged tiles, many tiles per CTA; and the inference call
+    that saves nothing returns the same sigma."""
+    gen = torch.Generator().manual_seed(n * 1000 + s)
+    plan = ops.Plan(log2_hashmap_size=15)
+    assert plan.enc_optional
+    params = ((torch.rand(plan.n_params, generator=gen) - 0.5) * 0.6).to(dev)
+    rays = torch.zeros(n, 13)
+    rays[:, 0:3] = (torch.rand(n, 3, generator=gen) - 0.5) * 0.4
+    d = torch.randn(n, 3, generator=gen)
+    rays[:, 3:6] = d / d.norm(dim=1, keepdim=True)
+    z = torch.rand(n, s, generator=gen).sort(dim=1).values * 0.7
+    rays, z = rays.to(dev), z.to(dev)
+    sig, (enc, act) = ops.sigma_fwd(plan, params, rays=rays, z=z)
+    x01 = ((rays[:, None, 0:3] + rays[:, None, 3:6] * z[..., None]).reshape(-1, 3) + 1) / 2
+    enc2 = ops.encode_fwd(plan, x01.contiguous(), params[plan.n_mlp_params:])
+    assert rel_err(enc, enc2) < 1e-5                 # xyz is formed with an fma inside the kernel
+    sig2, (_, act2) = ops.sigma_fwd(plan, params, x01=x01.contiguous())
+    assert rel_err(sig.view(-1), sig2) < 1e-4
+    sig3, saved = ops.sigma_fwd(plan, params, rays=rays, z=z, save_enc=False)
+    assert saved is None
+    assert torch.equal(sig3, sig)
+    # masks agree except at rounding ties of the hidden pre-activation (the two point sources round xyz differently)
+    x = act ^ act2
+    flips = sum(int(((x >> b) & 1).sum()) for b in range(64))
+    assert flips <= max(1, int(1e-4 * 64 * n * s))
+
+
 @pytest.mark.parametrize("P", [1, 127, 128, 129, 5000, 128 * 700 + 5])
 def test_mlp_tensor_cores_match_fp32(P, dev, ops, O):
     """tcgen05 MLP (bf16-split operands, fp32 TMEM accumulators) against the oracle's fp32 MLP and the fp32
