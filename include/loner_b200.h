@@ -110,6 +110,16 @@ LB_API int lb_build_lidar_rays_bwd(const float* directions, const int64_t* indic
                             const float* rot, const float* origin, float far_max, const float* d_rays,
                             float* d_rot, float* d_origin, void* stream);
 
+/* CameraRayDirections.build_rays (src/common/ray_utils.py:168-206) as called by KeyFrame.build_camera_rays
+ * (src/mapping/keyframe.py:108-128), with the pixel selection of src/mapping/optimizer.py:626-651 fused in.
+ * directions [n,3] (camera frame, one per pixel), pix_i / pix_j [n] pixel grid coordinates (NULL: zeros),
+ * image [n,n_colors] (NULL: no intensities), indices [m] int64 (NULL: identity); rot [9] / origin [3] of the
+ * (detached) camera pose as for the LiDAR rays.  rays [m,13] = [o, d, -d, pix_i, pix_j, near, cube exit];
+ * intensities [m,n_colors] = image[indices].  No backward: the reference detaches the camera pose. */
+LB_API int lb_build_camera_rays(const float* directions, const float* pix_i, const float* pix_j, const float* image,
+                         int n_colors, const int64_t* indices, int n, int m, const float* rot,
+                         const float* origin, float near, float* rays, float* intensities, void* stream);
+
 /* ---- R2: sampling ------------------------------------------------------------------------ */
 /* OccGridRaySampler.get_samples (src/models/ray_sampling.py:53-92) incl. OccupancyGridModel.interpolate
  * (src/models/model_tcnn.py:126-134) and sample_pdf (src/models/rendering_tcnn.py:19-68).
@@ -148,8 +158,9 @@ LB_API int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, 
 /* Backward of the above: d_sigma [P] -> grad_params += (MLP grads, table scatter-add; NULL to skip);
  * d_rays [N,13] += (origin/direction gradients through the grid input) when non-NULL
  * (or d_x01 [P,3] when the point source is x01).  enc_inout = enc as written by lb_sigma_fwd; it is
- * CONSUMED: on return it holds dL/d_enc.  act = the mask written by lb_sigma_fwd (NULL: fp32 CUDA-core MLP,
- * which recomputes the hidden layer). */
+ * CONSUMED: its contents are undefined on return (the two-kernel path overwrites it with dL/d_enc, the
+ * one-kernel path leaves it alone).  act = the mask written by lb_sigma_fwd (NULL: fp32 CUDA-core MLP, which
+ * recomputes the hidden layer). */
 LB_API int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
                  const float* params, float* enc_inout, const uint64_t* act, const float* d_sigma,
                  int n_rays, int n_samples, float* grad_params, float* d_rays, float* d_x01, void* stream);

@@ -1,9 +1,11 @@
 // R4: the fused sigma head = hash-grid encode (lb_encode.cu) + 32-64-1 MLP (lb_mlp.cu), forward and backward.
 //
 // Replaces tcnn.NetworkWithInputEncoding(3 -> 1) as used by DecoupledNeRF (reference
-// src/models/nerf_tcnn.py:35-38,63-72).  Two launches per direction; the encodings [P,32] are the only
-// intermediate that touches HBM (written once by the forward, read by the MLP and kept for the backward,
-// where the MLP backward overwrites them IN PLACE with dL/d_enc for the scatter kernel).
+// src/models/nerf_tcnn.py:35-38,63-72).  With (rays, z) and tables that fit the L2, each direction is ONE
+// warp-specialised kernel (lb_mlp_umma.cu: gather warps <-> tcgen05 MLP warps through a shared-memory ring); `enc`
+// [P,32] is then written once by the forward and read once by the backward.  Otherwise (x01 point source, level-group
+// passes, fp32 CUDA-core MLP) two launches per direction with `enc` as the hand-off, overwritten IN PLACE with
+// dL/d_enc by the MLP backward for the scatter kernel.
 #include "lb_common.cuh"
 
 extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,

@@ -141,6 +141,37 @@ build_rays_bwd_kernel(const float* __restrict__ directions, const long long* __r
     }
 }
 
+// Camera rays (reference CameraRayDirections.build_rays, src/common/ray_utils.py:168-206, called through
+// KeyFrame.build_camera_rays, src/mapping/keyframe.py:108-128, with the pixel selection of
+// src/mapping/optimizer.py:626-651 fused in): directions [n,3] per pixel (camera frame), pixel grid coordinates,
+// optional image [n,C] to gather the target intensities from.  far = cube exit only (no range clamp); the camera
+// pose is detached in the reference (detach_rgb_from_poses), so there is no backward.
+//   rays[i] = [o, d, -d, pix_i, pix_j, near, exit(o, d)];  intensities[i] = image[idx_i]
+__global__ void __launch_bounds__(kThreads)
+build_camera_rays_kernel(const float* __restrict__ directions, const float* __restrict__ pix_i,
+                         const float* __restrict__ pix_j, const float* __restrict__ image, int n_colors,
+                         const long long* __restrict__ indices, int n, int m, const float* __restrict__ rot,
+                         const float* __restrict__ origin, float near, float* __restrict__ rays,
+                         float* __restrict__ intensities) {
+    const int i = blockIdx.x * kThreads + threadIdx.x;
+    if (i >= m) return;
+    const Pose p = load_pose(rot, origin);
+    long long j = indices ? indices[i] : (long long)i;
+    if (j < 0) j += n;
+    const float* dir = directions + 3 * (size_t)j;
+    const RayGeom g = ray_geometry(p, __ldg(dir), __ldg(dir + 1), __ldg(dir + 2));
+    float* r = rays + (size_t)i * LB_RAY_STRIDE;
+    r[0] = p.o[0]; r[1] = p.o[1]; r[2] = p.o[2];
+    r[3] = g.d[0]; r[4] = g.d[1]; r[5] = g.d[2];
+    r[6] = -g.d[0]; r[7] = -g.d[1]; r[8] = -g.d[2];
+    r[9] = pix_i ? __ldg(pix_i + j) : 0.0f;
+    r[10] = pix_j ? __ldg(pix_j + j) : 0.0f;
+    r[11] = near;
+    r[12] = g.exit_t;
+    if (image)
+        for (int c = 0; c < n_colors; ++c) intensities[(size_t)i * n_colors + c] = __ldg(image + (size_t)j * n_colors + c);
+}
+
 }  // namespace
 
 extern "C" int lb_build_lidar_rays(const float* directions, const float* distances, const int64_t* indices, int n,
@@ -167,5 +198,19 @@ extern "C" int lb_build_lidar_rays_bwd(const float* directions, const int64_t* i
     build_rays_bwd_kernel<<<blocks, kThreads, 0, (cudaStream_t)stream>>>(
         directions, reinterpret_cast<const long long*>(indices), n, m, rot, origin, far_max, d_rays, d_rot, d_origin);
     LB_LAUNCH_CHECK("lb_build_lidar_rays_bwd");
+    return LB_OK;
+}
+
+extern "C" int lb_build_camera_rays(const float* directions, const float* pix_i, const float* pix_j, const float* image,
+                                    int n_colors, const int64_t* indices, int n, int m, const float* rot,
+                                    const float* origin, float near, float* rays, float* intensities, void* stream) {
+    LB_REQUIRE(directions && rot && origin && rays, "null pointer");
+    LB_REQUIRE(n > 0 && m >= 0, "bad sizes");
+    LB_REQUIRE(!image || (intensities && n_colors >= 1), "image needs an intensities output and n_colors >= 1");
+    if (m == 0) return LB_OK;
+    build_camera_rays_kernel<<<(m + kThreads - 1) / kThreads, kThreads, 0, (cudaStream_t)stream>>>(
+        directions, pix_i, pix_j, image, n_colors, reinterpret_cast<const long long*>(indices), n, m, rot, origin, near,
+        rays, intensities);
+    LB_LAUNCH_CHECK("lb_build_camera_rays");
     return LB_OK;
 }

@@ -190,13 +190,19 @@ class LidarScanData:
 class KeyFrame:
     """reference src/mapping/keyframe.py: owns one scan and its (optimisable) pose, builds rays."""
 
-    def __init__(self, scan: LidarScanData, pose6, gt_pose6=None, time=0.0, device="cuda"):
+    def __init__(self, scan: LidarScanData, pose6, gt_pose6=None, time=0.0, device="cuda", image=None, mask=None,
+                 lidar_to_camera=None):
         self._scan = LidarScanData(scan.ray_directions.to(device), scan.distances.to(device),
                                    None if scan.sky_rays is None else scan.sky_rays.to(device))
         self._pose = PoseHandle(pose6.to(device))
         self._gt_pose = PoseHandle((gt_pose6 if gt_pose6 is not None else pose6).to(device))
         self._time = time
         self.is_anchored = False
+        # camera side (reference src/common/frame.py: image, mask, lidar_to_camera extrinsic): image [H,W,C] in
+        # [0,1], mask [H,W] bool (pixels allowed for colour optimisation) or None, lidar_to_camera 4x4 or 6-vector
+        self.image = None if image is None else image.to(device).float()
+        self.mask = None if mask is None else mask.to(device).bool()
+        self._lidar_to_camera = None if lidar_to_camera is None else lidar_to_camera.to(device).float()
 
     def get_lidar_scan(self):
         return self._scan
@@ -222,6 +228,23 @@ class KeyFrame:
                                               const_depth=_range_host(ray_range)[1] + 1.0, rot_origin=sky_ro)
             rays, depths = torch.cat((rays, srays)), torch.cat((depths, sdepths))
         return rays, depths
+
+
+    def get_camera_pose(self, use_gt_poses=False):
+        """reference frame.py:152-153: T_camera = T_lidar @ T_lidar_to_camera (4x4)."""
+        from .camera import pose_matrix
+        T = pose_matrix((self._gt_pose if use_gt_poses else self._pose).get_pose_tensor())
+        if self._lidar_to_camera is None:
+            return T
+        return T @ pose_matrix(self._lidar_to_camera)
+
+    def build_camera_rays(self, first_camera_indices, ray_range, cam_ray_directions, world_cube, use_gt_poses=False,
+                          detach_rgb_from_poses=True):
+        """reference keyframe.py:108-128."""
+        if not detach_rgb_from_poses:
+            raise LonerB200Error("build_camera_rays: only detach_rgb_from_poses=True (the reference default) is built")
+        return cam_ray_directions.build_rays(first_camera_indices, self.get_camera_pose(use_gt_poses).detach(),
+                                             self.image, world_cube, ray_range)
 
 
 class RayDataParallel:
@@ -461,6 +484,98 @@ class Optimizer:
         result = self._do_iterate_optimizer(keyframe_window, schedule, optimizer_settings)
         self._keyframe_count += 1
         return result
+
+    # -- colour optimisation ------------------------------------------------
+    def iterate_optimizer_camera(self, keyframe_window, optimizer_settings=None):
+        """reference optimizer.py:517-539: schedule lookup, then the colour-head optimisation below."""
+        iteration_schedule = None
+        cumulative = 0
+        for item in self._keyframe_schedule:
+            kf_count = item["num_keyframes"]
+            iteration_schedule = item["iteration_schedule"]
+            cumulative += kf_count
+            if cumulative >= self._keyframe_count + 1 or kf_count == -1:
+                break
+        result = self._do_iterate_optimizer_camera(keyframe_window, iteration_schedule, optimizer_settings)
+        self._keyframe_count += 1
+        return result
+
+    def _camera_schedule(self, keyframes, n_pixels):
+        """optimizer.py:575-598 (FULL_CONFIG): one pass over a random permutation of every keyframe's masked
+        pixels; floor(min masked-pixel count / num_rays) iterations (W*H iterations when there is no mask, as the
+        reference has it).  Returns (full_indices [K, n_it * num_rays] int64 on the device, n_it)."""
+        num_rays = self._num_lidar_samples
+        if keyframes[0].mask is not None:
+            n_it = min(int(kf.mask.sum()) // num_rays for kf in keyframes)
+        else:
+            n_it = n_pixels
+        full = torch.zeros((len(keyframes), n_it * num_rays), dtype=torch.int64, device=self._device)
+        for k, kf in enumerate(keyframes):
+            if kf.mask is not None:
+                idx = torch.arange(n_pixels, device=self._device)[kf.mask.flatten()]
+            else:
+                idx = torch.arange(n_pixels, device=self._device)
+            idx = idx[torch.randperm(len(idx), device=self._device)][:n_it * num_rays]
+            full[k, :len(idx)] = idx
+        return full, n_it
+
+    def build_camera_batch(self, keyframes, cam_ray_directions, full_indices, it_idx, n_it):
+        """One iteration's camera batch (optimizer.py:614-651): per keyframe slice of the permutation, ray build and
+        intensity gather on the device."""
+        num_rays = self._num_lidar_samples
+        lo, hi = max(int(num_rays * it_idx - 1), 0), min(int(num_rays * (it_idx + 1) - 1), int(n_it * num_rays))
+        rays, inten = [], []
+        for k, kf in enumerate(keyframes):
+            r, c = kf.build_camera_rays(full_indices[k, lo:hi], self._ray_range, cam_ray_directions, self._world_cube,
+                                        self._use_gt_poses)
+            rays.append(r)
+            inten.append(c)
+        return torch.vstack(rays), torch.cat(inten)
+
+    def _do_iterate_optimizer_camera(self, keyframe_window, iteration_schedule, optimizer_settings=None):
+        """reference optimizer.py:541-688: sigma head and poses frozen, colour head trained with Adam(lrate_rgb) on
+        an L1 photometric loss over a fixed per-keyframe pixel permutation."""
+        from .camera import CameraRayDirections
+        if self._lidar_only:
+            raise LonerB200Error("iterate_optimizer_camera needs an Optimizer built with lidar_only=False")
+        if len(keyframe_window) == 1:
+            keyframe_window[0].is_anchored = True
+        if len(iteration_schedule) > 1 and self._settings.skip_pose_refinement:
+            iteration_schedule = iteration_schedule[1:]
+        if optimizer_settings is not None:
+            self._optimization_settings = optimizer_settings
+        self._settings['freeze_poses'] = True
+        self._settings['detach_rgb_from_sigma'] = True
+        train = self._model_config.train
+        cam = CameraRayDirections(self._calibration, device=self._device)     # built once (the reference: per keyframe per step)
+        loss = None
+        for _ in iteration_schedule:
+            s = self._optimization_settings
+            s.freeze_sigma_mlp, s.freeze_poses, s.freeze_rgb_mlp = True, True, False
+            self._model.freeze_sigma_head(True)
+            self._model.freeze_rgb_head(False)
+            params = self._model.get_rgb_parameters()
+            self._optimizer = FusedAdam([{'params': params, 'lr': train.lrate_rgb}])
+            gamma = train.lrate_gamma
+            full, n_it = self._camera_schedule(keyframe_window, len(cam))
+            s.num_iterations = n_it
+            for it_idx in range(n_it):
+                samples = self.build_camera_batch(keyframe_window, cam, full, it_idx, n_it)
+                loss = self.compute_loss_camera(samples, None, it_idx, tracking=False)
+                loss.backward()
+                self._dp.all_reduce_grads(params)
+                self._global_step += 1
+                self._optimizer.step()
+                if gamma != 1.0:
+                    for g in self._optimizer.param_groups:
+                        g['lr'] *= gamma
+                self._optimizer.zero_grad(set_to_none=True)
+                if self._settings.debug.log_losses:
+                    self.losses_log.append(float(loss.detach()))
+            if gamma != 1.0:
+                for g in self._optimizer.param_groups:
+                    g['lr'] *= gamma
+        return None if loss is None else float(loss.detach())
 
     def _do_iterate_optimizer(self, keyframe_window, iteration_schedule, optimizer_settings=None):
         """reference optimizer.py:193-511 (RANDOM / MASK ray selection)."""

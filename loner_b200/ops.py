@@ -94,6 +94,21 @@ def build_lidar_rays(directions, distances, indices, rot, origin, near, far_max,
     return rays, depths
 
 
+def build_camera_rays(directions, pix_i, pix_j, indices, rot, origin, near, image=None):
+    """Camera rays.  directions [n,3]; pix_i / pix_j [n] or None; image [n,C] or None; indices [m] int64 or None.
+    Returns (rays [m,13], intensities [m,C] or None)."""
+    n = directions.shape[0]
+    m = n if indices is None else indices.shape[0]
+    dev = directions.device
+    rays = torch.empty(m, 13, device=dev, dtype=torch.float32)
+    c = 0 if image is None else image.shape[1]
+    inten = None if image is None else torch.empty(m, c, device=dev, dtype=torch.float32)
+    _lib.call("lb_build_camera_rays", _p(directions, name="directions"), _p(pix_i, name="pix_i"), _p(pix_j, name="pix_j"),
+              _p(image, name="image"), c, _p(indices, torch.int64, name="indices"), n, m, _p(rot, name="rot"),
+              _p(origin, name="origin"), float(near), _p(rays), _p(inten), _stream())
+    return rays, inten
+
+
 def build_lidar_rays_bwd(directions, indices, rot, origin, far_max, d_rays, d_rot, d_origin):
     """R0 backward: accumulates into d_rot [9] and d_origin [3]."""
     n = directions.shape[1]

@@ -440,3 +440,48 @@ def build_lidar_rays(directions, distances, pose6, shift, scale, ray_range):
     rays = torch.cat([o, dirs, -dirs, torch.zeros_like(o[:, :2]), near, far], 1)
     valid = (far > (near + 1. / scale))[..., 0]
     return rays[valid], (distances / scale)[valid]
+
+
+# --------------------------------------------------------------------------------------------
+# f2: camera rays  (src/common/ray_utils.py:62-124,168-206; kornia undistort_points restated in
+#     oracle/stubs/kornia/geometry/calibration.py -- parity unpinned for distorted intrinsics)
+# --------------------------------------------------------------------------------------------
+
+
+def camera_directions(H, W, new_k, dist=None, K=None):
+    """get_ray_directions (ray_utils.py:62-124), sppd = 1: (directions [H*W,3], pix_i [H*W,1], pix_j [H*W,1])."""
+    xs = torch.linspace(0, W - 1., W)
+    ys = torch.linspace(0, H - 1., H)
+    gx, gy = torch.meshgrid([xs, ys], indexing="ij")
+    gx = gx.permute(1, 0).reshape(-1, 1)
+    gy = gy.permute(1, 0).reshape(-1, 1)
+    nx, ny = gx, gy
+    if dist is not None:
+        import importlib.util
+        import os
+        spec = importlib.util.spec_from_file_location(
+            "_oracle_kornia_calibration",
+            os.path.join(os.path.dirname(os.path.abspath(__file__)), "stubs", "kornia", "geometry", "calibration.py"))
+        cal = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(cal)
+        und = cal.undistort_points(torch.cat([gx, gy], -1).unsqueeze(0), K.reshape(1, 3, 3), dist.reshape(1, -1),
+                                   new_k.reshape(1, 3, 3))
+        nx, ny = und[0, :, 0:1], und[0, :, 1:2]
+    d = torch.cat([(nx - new_k[0, 2]) / new_k[0, 0], (ny - new_k[1, 2]) / new_k[1, 1], torch.ones_like(gx)], -1)
+    return d, gx, gy
+
+
+def build_camera_rays(directions, pix_i, pix_j, indices, T, shift, scale, near_m, image=None):
+    """CameraRayDirections.build_rays (ray_utils.py:168-206): T = camera-to-world 4x4; returns
+    (rays [m,13] = [o, d, -d, pix_i, pix_j, near, cube exit], intensities [m,C] | None)."""
+    d = directions[indices]
+    R = T[:3, :3].float()
+    o = ((T[:3, 3] + shift) / scale).float()
+    rd = d @ R.T
+    rd = rd / torch.norm(rd, dim=-1, keepdim=True)
+    ro = o.reshape(1, 3).expand(rd.shape[0], 3)
+    near = near_m / scale * torch.ones_like(ro[:, :1])
+    far = far_val(ro, rd)
+    rays = torch.cat([ro, rd, -rd, pix_i[indices], pix_j[indices], near, far], 1).float()
+    inten = None if image is None else image.reshape(-1, image.shape[-1])[indices]
+    return rays, inten

@@ -1,3 +1,2 @@
-"""ORACLE / TEST INFRASTRUCTURE ONLY: stand-in for kornia.geometry (camera undistortion; not on the LiDAR path)."""
-from _anything import Anything as _A
-calibration = _A()
+"""ORACLE / TEST INFRASTRUCTURE ONLY: stand-in for kornia.geometry (only calibration.undistort_points is restated)."""
+from . import calibration  # noqa: F401

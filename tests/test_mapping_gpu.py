@@ -300,3 +300,87 @@ def test_fixed_ray_selection_schedule():
     opt.compute_loss = (lambda f: (lambda *a, **k: (seen_steps.append(1), f(*a, **k))[1]))(opt.compute_loss)
     opt.iterate_optimizer(win)
     assert len(seen_steps) == n_it
+
+
+class _Calib(dict):
+    __getattr__ = dict.__getitem__
+
+
+def _calibration(g, distorted):
+    ci = _Calib(k=g["K"] if distorted else g["new_k"], distortion=g["dist"] if distorted else None, new_k=g["new_k"],
+                width=g["W"], height=g["H"])
+    return _Calib(camera_intrinsic=ci)
+
+
+@pytest.mark.parametrize("kind", ["pinhole", "distorted"])
+def test_camera_rays_match_reference(kind):
+    """lb_build_camera_rays behind CameraRayDirections.build_rays / fetch_chunk_rays against the reference's own
+    run (tests/golden/camera_rays.pt): ray tensor [o, d, -d, pix_i, pix_j, near, far] and gathered intensities."""
+    from loner_b200 import camera as Cm, mapping as M
+    g = load_golden("camera_rays")
+    c = g[kind]
+    crd = Cm.CameraRayDirections(_calibration(g, kind == "distorted"), device=DEV)
+    assert len(crd) == g["H"] * g["W"] and crd.num_chunks == 3
+    assert (crd.directions.cpu() - c["directions"]).abs().max() < 1e-6
+    wc = M.WorldCube(g["scale"], g["shift"])
+    rays, inten = crd.build_rays(g["indices"].to(DEV), g["T"].to(DEV), g["image"].to(DEV), wc, g["ray_range"])
+    assert rays.shape == c["rays"].shape
+    assert (rays.cpu() - c["rays"]).abs().max() < 2e-6
+    assert torch.equal(rays[:, 9:11].cpu(), c["rays"][:, 9:11])
+    assert torch.equal(inten.cpu(), c["intensities"])
+    chunk = crd.fetch_chunk_rays(1, g["T"].to(DEV), wc, g["ray_range"])
+    assert (chunk.cpu() - c["chunk1"]).abs().max() < 2e-6
+    # keyframe path: T_camera = T_lidar @ T_lidar_to_camera, detached
+    l2c = torch.eye(4)
+    l2c[:3, :3] = M.axis_angle_to_matrix(torch.tensor([0.1, 0.2, -0.3]))
+    l2c[:3, 3] = torch.tensor([0.05, -0.02, 0.1])
+    T_lidar = g["T"] @ torch.linalg.inv(l2c)
+    lidar_R = T_lidar[:3, :3]
+    # the lidar pose 6-vector whose matrix is T_lidar: axis-angle from R
+    ang = torch.acos(((lidar_R.trace() - 1) / 2).clamp(-1, 1))
+    axis = torch.stack([lidar_R[2, 1] - lidar_R[1, 2], lidar_R[0, 2] - lidar_R[2, 0], lidar_R[1, 0] - lidar_R[0, 1]]) / (2 * torch.sin(ang))
+    pose6 = torch.cat([T_lidar[:3, 3], axis * ang])
+    scan = M.LidarScanData(torch.zeros(3, 1), torch.zeros(1))
+    kf = M.KeyFrame(scan, pose6, device=DEV, image=g["image"], lidar_to_camera=l2c)
+    assert (kf.get_camera_pose().cpu() - g["T"]).abs().max() < 1e-5
+    r2, i2 = kf.build_camera_rays(g["indices"].to(DEV), g["ray_range"], crd, wc)
+    assert (r2.cpu() - c["rays"]).abs().max() < 2e-5 and torch.equal(i2.cpu(), c["intensities"])
+
+
+def test_iterate_optimizer_camera_learns_colours():
+    """Colour optimisation loop (reference optimizer.py:517-688): sigma head and poses frozen, one pass over a pixel
+    permutation per keyframe restricted to the mask, Adam on the colour head; the photometric loss goes down."""
+    from loner_b200 import mapping as M, synth
+    H, W, num_rays = 48, 64, 256
+    kfs, scale, shift = synth.make_keyframes(2, ray_range=(1.0, 30.0), seed=5)
+    s = M.default_settings(n_samples_train=64, log2_hashmap_size=14, lidar=num_rays, sky=0, voxel_size=32, strategy="UNIFORM")
+    s["model_config"]["model"]["nerf_config"]["pos_encoding_intensity"]["log2_hashmap_size"] = 14
+    s["debug"]["log_losses"] = True
+    ci = _Calib(k=torch.tensor([[50.0, 0, 32], [0, 50.0, 24], [0, 0, 1]]), distortion=torch.zeros(5), new_k=None, width=W, height=H)
+    opt = M.Optimizer(s, _Calib(camera_intrinsic=ci), M.WorldCube(scale, shift), DEV, lidar_only=False)
+    gen = torch.Generator().manual_seed(0)
+    win = []
+    for k in kfs:
+        yy, xx = torch.meshgrid(torch.linspace(0, 1, H), torch.linspace(0, 1, W), indexing="ij")
+        img = torch.stack([xx, yy, 0.5 * torch.ones_like(xx)], -1)
+        mask = torch.rand(H, W, generator=gen) < 0.8
+        win.append(M.KeyFrame(M.LidarScanData(k.directions, k.distances, None), k.pose, device=DEV, image=img, mask=mask))
+    sigma_before = opt._model.nerf_model._model_sigma.params.detach().clone()
+    pose_before = win[1].get_lidar_pose().get_pose_tensor().detach().clone()
+    from loner_b200.camera import CameraRayDirections
+    full, n_it = opt._camera_schedule(win, H * W)
+    assert n_it == min(int(k.mask.sum()) for k in win) // num_rays and full.shape == (2, n_it * num_rays)
+    for k in range(2):
+        assert win[k].mask.flatten()[full[k]].all() and full[k].unique().numel() == full.shape[1]
+    cam = CameraRayDirections(opt._calibration, device=DEV)
+    rays, inten = opt.build_camera_batch(win, cam, full, 0, n_it)
+    assert rays.shape == (2 * (num_rays - 1), 13) and inten.shape == (2 * (num_rays - 1), 3)
+    rays, inten = opt.build_camera_batch(win, cam, full, 1, n_it)
+    assert rays.shape == (2 * num_rays, 13)
+    last = opt.iterate_optimizer_camera(win)
+    assert len(opt.losses_log) == opt._optimization_settings.num_iterations >= 5
+    assert last == pytest.approx(opt.losses_log[-1])
+    assert sum(opt.losses_log[-3:]) < 0.9 * sum(opt.losses_log[:3])
+    assert torch.equal(opt._model.nerf_model._model_sigma.params.detach(), sigma_before)
+    assert torch.equal(win[1].get_lidar_pose().get_pose_tensor().detach(), pose_before)
+    assert opt._keyframe_count == 1 and opt._settings['freeze_poses'] is True

@@ -160,3 +160,36 @@ def test_colour_branch_against_reference():
     assert abs(table.grad.double().norm().item() - g["table_int_grad_norm"]) < 1e-4 * g["table_int_grad_norm"]
     torch.testing.assert_close(rays.grad, g["rays_grad"], rtol=1e-4, atol=1e-7)
     assert g["sigma_grad_is_none"]          # detach_sigma=True: the camera loss does not touch the sigma head
+
+
+@pytest.mark.parametrize("kind", ["pinhole", "distorted"])
+def test_camera_rays_against_reference(kind):
+    """Camera ray construction: oracle restatement and the product's host-side direction table
+    against the reference's own get_ray_directions / CameraRayDirections.build_rays (tests/golden/camera_rays.pt)."""
+    from loner_b200 import camera as Cm
+    g = load_golden("camera_rays")
+    c = g[kind]
+    dist, K = (None, None) if kind == "pinhole" else (g["dist"], g["K"])
+    d, gi, gj = O.camera_directions(g["H"], g["W"], g["new_k"], dist, K)
+    assert torch.equal(gi, g["pinhole"]["pix_i"]) and torch.equal(gj, g["pinhole"]["pix_j"])
+    assert (d - c["directions"]).abs().max() < 1e-6
+    rays, inten = O.build_camera_rays(d, gi, gj, g["indices"], g["T"], g["shift"], g["scale"], g["ray_range"][0], g["image"])
+    assert (rays - c["rays"]).abs().max() < 2e-6
+    assert torch.equal(inten, c["intensities"])
+    # product host logic (torch, device-agnostic): direction table and pixel order
+    d2, gi2, gj2 = Cm.get_ray_directions(g["H"], g["W"], g["new_k"], dist, K, with_indices=True)
+    assert torch.equal(gi2, gi) and torch.equal(gj2, gj)
+    assert (d2 - c["directions"]).abs().max() < 1e-6
+    # the undistortion restatements invert the forward distortion model (a property kornia's has by construction)
+    if kind == "distorted":
+        k1, k2, p1, p2, k3 = g["dist"].tolist()
+        xy = (torch.rand(200, 2) - 0.5) * 0.8
+        x, y = xy[:, 0], xy[:, 1]
+        r2 = x * x + y * y
+        rad = 1 + k1 * r2 + k2 * r2 * r2 + k3 * r2 ** 3
+        xd = x * rad + 2 * p1 * x * y + p2 * (r2 + 2 * x * x)
+        yd = y * rad + p1 * (r2 + 2 * y * y) + 2 * p2 * x * y
+        K_ = g["K"]
+        pts = torch.stack([K_[0, 0] * xd + K_[0, 2], K_[1, 1] * yd + K_[1, 2]], -1).unsqueeze(0)
+        und = Cm.undistort_points(pts, K_.reshape(1, 3, 3), g["dist"].reshape(1, -1), torch.eye(3).reshape(1, 3, 3))
+        assert (und[0] - xy).abs().max() < 2e-4
