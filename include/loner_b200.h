@@ -236,6 +236,16 @@ LB_API int lb_composite_rgb_bwd(const float* weights, const float* colors, const
                          int n_samples, int n_colors, int white_bkgd, float* d_weights, float* d_colors,
                          void* stream);
 
+/* ---- f3: eval helpers --------------------------------------------------------------------------- */
+/* The mesher's max-weight voxel splat (analysis/mesher.py:137-180): for every sample point o + d*z of every ray with
+ * ray_mask != 0 (NULL: all rays) that lies inside [bounds[0], bounds[n-1]] on all three axes, volume[voxel] =
+ * max(volume[voxel], weight) with voxel = bucketize(x)*nz + bucketize(y)*nx*nz + bucketize(z) (torch.bucketize,
+ * right=False, fp64 boundaries).  volume [ny*nx*nz] fp32 is accumulated into (caller zero-fills once per mesh);
+ * weights must be >= 0 (compositing weights are). */
+LB_API int lb_voxel_splat_max(const float* rays, const float* z, const float* weights, const uint8_t* ray_mask,
+                       int n_rays, int n_samples, const double* x_bounds, int nx, const double* y_bounds, int ny,
+                       const double* z_bounds, int nz, float* volume, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

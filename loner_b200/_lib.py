@@ -43,6 +43,7 @@ SIGNATURES = {
     "lb_plan_level": (_I, [_P, _I, C.POINTER(_F), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32),
                            C.POINTER(C.c_uint32), C.POINTER(C.c_int32)]),
     "lb_build_lidar_rays": (_I, [_P, _P, _P, _I, _I, _P, _P, _F, _F, _F, _F, _P, _P, _P]),
+    "lb_voxel_splat_max": (_I, [_P, _P, _P, _P, _I, _I, _P, _I, _P, _I, _P, _I, _P, _P]),
     "lb_build_camera_rays": (_I, [_P, _P, _P, _P, _I, _P, _I, _I, _P, _P, _F, _P, _P, _P]),
     "lb_build_lidar_rays_bwd": (_I, [_P, _P, _I, _I, _P, _P, _F, _P, _P, _P, _P]),
     "lb_sample_occ": (_I, [_P, _P, _I, _P, _P, _P, _I, _I, _F, _P, _P, _P, _P]),

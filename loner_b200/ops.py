@@ -320,3 +320,16 @@ def composite_rgb_bwd(weights, colors, g_rgb, white_bkgd, need_dw=True, need_dc=
     _lib.call("lb_composite_rgb_bwd", _p(weights, name="weights"), _p(colors, name="colors"), _p(g_rgb, name="g_rgb"),
               N, S, Cn, 1 if white_bkgd else 0, _p(dw), _p(dc), _stream())
     return dw, dc
+
+
+def voxel_splat_max(rays, z, weights, x_bounds, y_bounds, z_bounds, volume, ray_mask=None):
+    """f3: max-weight voxel splat into volume [ny, nx, nz] (fp32, accumulated in place).  Bounds are fp64 device
+    tensors (the axis grid coordinates); ray_mask [N] uint8 / bool or None."""
+    n, s_ = z.shape
+    if ray_mask is not None and ray_mask.dtype == torch.bool:
+        ray_mask = ray_mask.to(torch.uint8)
+    _lib.call("lb_voxel_splat_max", _p(rays, name="rays"), _p(z, name="z"), _p(weights, name="weights"),
+              _p(ray_mask, torch.uint8, name="ray_mask"), n, s_, _p(x_bounds, torch.float64, name="x_bounds"),
+              x_bounds.numel(), _p(y_bounds, torch.float64, name="y_bounds"), y_bounds.numel(),
+              _p(z_bounds, torch.float64, name="z_bounds"), z_bounds.numel(), _p(volume, name="volume"), _stream())
+    return volume

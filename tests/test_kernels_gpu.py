@@ -4,6 +4,7 @@
 Bars (BASELINE.json north_star): occupancy bits and sample indices bit-exact; everything
 floating-point within 1e-3 relative (we assert much tighter where fp32 allows).
 """
+import numpy as np
 import pytest
 import torch
 
@@ -490,3 +491,50 @@ def test_level_group_passes_match_single_pass(monkeypatch):
     ops.sigma_bwd(plan1, params, sv1, ds, rays=rays, z=z, grad_params=gp1, d_rays=dr1)
     ops.sigma_bwd(planN, params, svN, ds, rays=rays, z=z, grad_params=gpN, d_rays=drN)
     assert rel_err(gpN, gp1) < 1e-5 and rel_err(drN, dr1) < 1e-4
+
+
+@pytest.mark.parametrize("n,s,dims", [(1, 1, (3, 2, 4)), (37, 65, (17, 9, 23)), (2000, 128, (60, 40, 31))])
+def test_voxel_splat_max_matches_bucketize_amax(n, s, dims, dev, ops):
+    """lb_voxel_splat_max (mesher.py:137-180) against torch.bucketize + scatter amax on the same points: bound filter,
+    fp64 boundaries, voxel index layout [y][x][z], exact maxima, ray mask; accumulation over two calls."""
+    gen = torch.Generator().manual_seed(n + s)
+    rays = torch.zeros(n, 13)
+    rays[:, 0:3] = (torch.rand(n, 3, generator=gen) - 0.5) * 0.6
+    d = torch.randn(n, 3, generator=gen)
+    rays[:, 3:6] = d / d.norm(dim=1, keepdim=True)
+    z = torch.rand(n, s, generator=gen).sort(dim=1).values * 1.2
+    w = torch.rand(n, s, generator=gen) * (torch.rand(n, s, generator=gen) < 0.7)
+    mask = torch.rand(n, generator=gen) < 0.8
+    nx, ny, nz = dims
+    xb = torch.from_numpy(np.linspace(-0.61, 0.52, nx))
+    yb = torch.from_numpy(np.linspace(-0.3, 0.45, ny))
+    zb = torch.from_numpy(np.linspace(-0.2, 0.7, nz))
+    # put a few points exactly on boundaries (bucketize right=False edge) and on the bound limits
+    if n > 1:
+        rays[0, 0:3] = torch.tensor([xb[1], yb[0], zb[nz - 1]]).float()
+        z[0, 0] = 0.0
+        w[0, 0] = 0.5
+        mask[0] = True
+
+    def reference(vol, m):
+        pts = rays[:, None, 0:3] + rays[:, None, 3:6] * z[..., None]
+        pts, ww = pts[m].reshape(-1, 3), w[m].reshape(-1)
+        good = torch.ones(pts.shape[0], dtype=torch.bool)
+        for a, b in enumerate((xb, yb, zb)):
+            good &= (pts[:, a].double() >= b[0]) & (pts[:, a].double() <= b[-1])
+        pts, ww = pts[good], ww[good]
+        idx = torch.bucketize(pts[:, 0].double().contiguous(), xb) * nz + \
+            torch.bucketize(pts[:, 1].double().contiguous(), yb) * nx * nz + torch.bucketize(pts[:, 2].double().contiguous(), zb)
+        ok = idx < vol.numel()
+        return vol.view(-1).scatter_reduce(0, idx[ok], ww[ok], "amax", include_self=True).view(ny, nx, nz)
+
+    vol = torch.zeros(ny, nx, nz, device=dev)
+    ops.voxel_splat_max(rays.to(dev), z.to(dev), w.to(dev), xb.to(dev), yb.to(dev), zb.to(dev), vol, ray_mask=mask.to(dev))
+    ref = reference(torch.zeros(ny, nx, nz), mask)
+    assert torch.equal(vol.cpu(), ref)
+    ops.voxel_splat_max(rays.to(dev), z.to(dev), (w * 0.5).to(dev), xb.to(dev), yb.to(dev), zb.to(dev), vol)    # accumulate, no mask
+    w_keep = w
+    w = w * 0.5
+    ref2 = reference(ref.clone(), torch.ones(n, dtype=torch.bool))
+    w = w_keep
+    assert torch.equal(vol.cpu(), ref2)

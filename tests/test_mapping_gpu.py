@@ -384,3 +384,41 @@ def test_iterate_optimizer_camera_learns_colours():
     assert torch.equal(opt._model.nerf_model._model_sigma.params.detach(), sigma_before)
     assert torch.equal(win[1].get_lidar_pose().get_pose_tensor().detach(), pose_before)
     assert opt._keyframe_count == 1 and opt._settings['freeze_poses'] is True
+
+
+def test_mesher_volume_from_virtual_scans():
+    """Mesher.splat_volume (analysis/mesher.py:100-180): virtual scans from keyframe poses -> max
+    compositing weight per voxel, against a torch bucketize / amax replay of the same forward passes."""
+    from loner_b200 import eval as E, mapping as M
+    g = load_golden("c1_ogm_l1js")
+    opt, _ = make_optimizer(g)
+    model = opt._model
+    mesher = E.Mesher(model, opt._world_cube, opt._ray_range, resolution=1.0, marching_cubes_bound=((-8, 8), (-6, 6), (-2, 4)))
+    xyz = mesher.get_grid_uniform()
+    assert [len(a) for a in xyz] == [16, 12, 6]
+    poses = [torch.tensor([0.5, 0.2, 0.1, 0.0, 0.0, 0.3]), torch.tensor([-0.7, 0.4, 0.0, 0.02, -0.01, 1.2])]
+    intr = {"vertical_fov": (-20.0, 20.0), "vertical_resolution": 2.5, "horizontal_resolution": 3.0}
+    d = E.build_lidar_scan(intr, DEV)
+    assert d.shape == (3, 16 * 120) and (d.norm(dim=0) - 1).abs().max() < 1e-6
+    torch.manual_seed(5)
+    vol, _ = mesher.splat_volume(opt._ray_sampler, poses, lidar_intrinsics=intr)
+    assert vol.shape == (16, 12, 6) and vol.max() <= 1.0 and (vol > 0).sum() > 10
+    # replay with torch ops
+    torch.manual_seed(5)
+    ref = torch.zeros(12 * 16 * 6, device=DEV)
+    bx, by, bz = (torch.from_numpy(a).to(DEV) for a in xyz)
+    model.cfg["render"]["retraw"] = True
+    for p in poses:
+        rays, _ = M.build_lidar_rays(d, None, p.to(DEV), opt._world_cube, opt._ray_range, const_depth=1.0)
+        res = model(rays, opt._ray_sampler, opt._scale_factor, testing=False, camera=False, return_variance=True)
+        ok = res["depth_fine"].view(-1) < opt._ray_range[1] - 0.25
+        pts = (rays[:, None, 0:3] + rays[:, None, 3:6] * res["samples_fine"][..., None])[ok].reshape(-1, 3)
+        w = res["weights_fine"][ok].reshape(-1)
+        good = torch.ones_like(w, dtype=torch.bool)
+        for a, b in enumerate((bx, by, bz)):
+            good &= (pts[:, a].double() >= b[0]) & (pts[:, a].double() <= b[-1])
+        pts, w = pts[good], w[good]
+        idx = torch.bucketize(pts[:, 0].double().contiguous(), bx) * 6 + torch.bucketize(pts[:, 1].double().contiguous(), by) * 16 * 6 + \
+            torch.bucketize(pts[:, 2].double().contiguous(), bz)
+        ref = ref.scatter_reduce(0, idx, w, "amax", include_self=True)
+    assert torch.equal(vol, ref.view(12, 16, 6).permute(1, 0, 2))
