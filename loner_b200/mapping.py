@@ -198,6 +198,7 @@ class KeyFrame:
         self._gt_pose = PoseHandle((gt_pose6 if gt_pose6 is not None else pose6).to(device))
         self._time = time
         self.is_anchored = False
+        self._tracked_pose6 = pose6.detach().clone().float().cpu()     # keyframe.py: the pose as tracked, never optimised
         # camera side (reference src/common/frame.py: image, mask, lidar_to_camera extrinsic): image [H,W,C] in
         # [0,1], mask [H,W] bool (pixels allowed for colour optimisation) or None, lidar_to_camera 4x4 or 6-vector
         self.image = None if image is None else image.to(device).float()
