@@ -49,19 +49,31 @@ sgd_kernel(float* __restrict__ p, float* __restrict__ g, size_t n, float lr, int
 }
 
 // occ_grad[corner] += w_corner * u, u = +0.25 if zm-g < -2, -2.5 if |zm-g| < 2 (strict), else 0
+//
+// A warp takes 32 consecutive samples.  Samples are depth-sorted along their ray and a 100^3 voxel holds several of
+// them (the sampler concentrates them at the surfaces), so neighbouring lanes mostly address the same 8 corners: runs
+// of lanes with the same base cell are summed by a segmented shuffle reduction and only the run head issues the
+// atomics (the grid is 4 MB, the cost of this kernel is same-address L2 atomics).
 __global__ void __launch_bounds__(256)
 occ_grad_kernel(const float* __restrict__ rays, const float* __restrict__ zv, const float* __restrict__ depth_gt,
                 float scale, size_t n_points, int S, int D, float* __restrict__ occ_grad) {
+    const unsigned kFull = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_points; p += stride) {
-        const size_t r = p / (size_t)S;
-        const float* ray = rays + r * LB_RAY_STRIDE;
-        const float z = __ldg(zv + p);
-        const float x = z * scale - __ldg(depth_gt + r) * scale;
-        float u = 0.0f;
-        if (x < -2.0f) u = 0.25f;
-        else if (x > -2.0f && x < 2.0f) u = -2.5f;
-        if (u == 0.0f) continue;
+    const size_t n_round = (n_points + 31) & ~(size_t)31;          // whole warps stay in the loop together
+    for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_round; p += stride) {
+        float u = 0.0f, z = 0.0f;
+        const float* ray = rays;
+        if (p < n_points) {
+            const size_t r = p / (size_t)S;
+            ray = rays + r * LB_RAY_STRIDE;
+            z = __ldg(zv + p);
+            const float x = z * scale - __ldg(depth_gt + r) * scale;
+            if (x < -2.0f) u = 0.25f;
+            else if (x > -2.0f && x < 2.0f) u = -2.5f;
+        }
+        const bool active = (u != 0.0f);
+        if (!__any_sync(kFull, active)) continue;
         const float px = __ldg(ray + 0) + __ldg(ray + 3) * z;
         const float py = __ldg(ray + 1) + __ldg(ray + 4) * z;
         const float pz = __ldg(ray + 2) + __ldg(ray + 5) * z;
@@ -70,15 +82,38 @@ occ_grad_kernel(const float* __restrict__ rays, const float* __restrict__ zv, co
                     iz = ((pz + 1.0f) * fD - 1.0f) * 0.5f;
         const float x0f = floorf(ix), y0f = floorf(iy), z0f = floorf(iz);
         const float fx = ix - x0f, fy = iy - y0f, fz = iz - z0f;
-        const int x0 = (int)x0f, y0 = (int)y0f, z0 = (int)z0f;
+        // clamp far-out cells to one sentinel layer outside the grid: no corner of such a cell is inside anyway
+        const int x0 = (int)fminf(fmaxf(x0f, -2.0f), (float)D), y0 = (int)fminf(fmaxf(y0f, -2.0f), (float)D),
+                  z0 = (int)fminf(fmaxf(z0f, -2.0f), (float)D);
+        float w[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const int bx = c & 1, by = (c >> 1) & 1, bz = (c >> 2) & 1;
+            w[c] = active ? (bx ? fx : 1.0f - fx) * (by ? fy : 1.0f - fy) * (bz ? fz : 1.0f - fz) * u : 0.0f;
+        }
+        // runs of equal base cells among consecutive lanes (inactive lanes join their neighbour's run with zeros)
+        const int px0 = __shfl_up_sync(kFull, x0, 1), py0 = __shfl_up_sync(kFull, y0, 1), pz0 = __shfl_up_sync(kFull, z0, 1);
+        const bool same = lane > 0 && px0 == x0 && py0 == y0 && pz0 == z0;
+        const unsigned heads = __ballot_sync(kFull, !same);
+        if (heads != kFull) {
+            const unsigned rest = (lane < 31) ? (heads >> (lane + 1)) : 0u;
+            const int dist = rest ? __ffs(rest) : 32 - lane;          // lanes until the next head
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const float t = __shfl_down_sync(kFull, w[c], off);
+                    if (off < dist) w[c] += t;
+                }
+            }
+        }
+        if (same) continue;
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
             const int bx = c & 1, by = (c >> 1) & 1, bz = (c >> 2) & 1;
             const int X = x0 + bx, Y = y0 + by, Z = z0 + bz;
-            if (X >= 0 && X < D && Y >= 0 && Y < D && Z >= 0 && Z < D) {
-                const float w = (bx ? fx : 1.0f - fx) * (by ? fy : 1.0f - fy) * (bz ? fz : 1.0f - fz);
-                atomicAdd(occ_grad + ((size_t)Z * D + Y) * D + X, w * u);
-            }
+            if (w[c] != 0.0f && X >= 0 && X < D && Y >= 0 && Y < D && Z >= 0 && Z < D)
+                atomicAdd(occ_grad + ((size_t)Z * D + Y) * D + X, w[c]);
         }
     }
 }

@@ -97,6 +97,60 @@ __device__ __forceinline__ void warp_bitonic_sort(float* buf, int n_pow2, int la
     }
 }
 
+// The same compare-exchange network on n = 32*R floats held in registers, element i = r*32 + lane: partners at
+// distance j < 32 are a lane shuffle, j >= 32 another register of the same lane.  Same swap rule as above.
+template <int R>
+__device__ __forceinline__ void warp_bitonic_sort_regs(float (&v)[R], int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32 * R; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j >= 32; j >>= 1) {            // in-lane stages (k >= 64): all indices static
+            const int jr = j >> 5, kr = k >> 5;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if ((r & jr) == 0) {
+                    const bool up = ((r & kr) == 0);
+                    const float a = v[r], b = v[r | jr];
+                    if ((a > b) == up) { v[r] = b; v[r | jr] = a; }
+                }
+            }
+        }
+#pragma unroll 1
+        for (int j = (k >> 1) < 16 ? (k >> 1) : 16; j > 0; j >>= 1) {   // lane-exchange stages
+            const bool lower = (lane & j) == 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const bool up = ((((r << 5) | lane) & k) == 0);
+                const float mine = v[r], other = __shfl_xor_sync(0xffffffffu, mine, j);
+                const float a = lower ? mine : other, b = lower ? other : mine;
+                if ((a > b) == up) v[r] = other;
+            }
+        }
+    }
+}
+
+// number of entries of the ascending array a[0, n) that are < x (strict) / <= x
+__device__ __forceinline__ int count_less(const float* a, int n, float x) {
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (a[mid] < x) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+__device__ __forceinline__ int count_less_equal(const float* a, int n, float x) {
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (a[mid] <= x) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// R > 0: the S/2 fine depths stay in registers (S/2 <= 32*R), are sorted there and merged with the coarse depths,
+// which the stratified draw already produced in ascending order (checked; any other input takes the full sort).
+// R == 0: every depth goes through the shared-memory bitonic sort.
+template <int R>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 sample_occ_kernel(const float* __restrict__ rays, const float* __restrict__ occ, int D,
                   const float* __restrict__ t_steps, const float* __restrict__ u1,
@@ -156,7 +210,7 @@ sample_occ_kernel(const float* __restrict__ rays, const float* __restrict__ occ,
 
     // inverse-CDF draw of the S2 fine depths (searchsorted right=True, rendering_tcnn.py:53-67)
     const int n_cdf = S2 - 1;
-    for (int k = lane; k < S2; k += 32) {
+    auto draw = [&](int k) -> float {
         const float u = __ldg(u2r + k);
         int lo = 0, hi = n_cdf;
         while (lo < hi) {
@@ -168,15 +222,62 @@ sample_occ_kernel(const float* __restrict__ rays, const float* __restrict__ occ,
         float denom = __fsub_rn(ca, cb);
         if (denom < 1e-5f) denom = 1.0f;
         const float bb = bins[below], ba = bins[above];
-        const float zf = __fadd_rn(bb, __fmul_rn(__fdiv_rn(__fsub_rn(u, cb), denom), __fsub_rn(ba, bb)));
         if (inds_out) inds_out[(size_t)ray * S2 + k] = (int64_t)lo;
-        sortbuf[S2 + k] = zf;   // overwrites prob[k], dead since the __syncwarp above
+        return __fadd_rn(bb, __fmul_rn(__fdiv_rn(__fsub_rn(u, cb), denom), __fsub_rn(ba, bb)));
+    };
+    const float kInf = __int_as_float(0x7f800000);
+    float* zo = z_out + (size_t)ray * S;
+    if constexpr (R > 0) {
+        float zf[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int k = r * 32 + lane;
+            zf[r] = (k < S2) ? draw(k) : kInf;
+        }
+        // are the coarse depths ascending?  (always, for the reference's stratified draw with near < far)
+        bool ok = true;
+        for (int k = lane; k < S2 - 1; k += 32) ok = ok && (sortbuf[k] <= sortbuf[k + 1]);
+        ok = __all_sync(0xffffffffu, ok);
+        __syncwarp();                                       // all reads of cdf / bins / prob are done
+        if (ok) {
+            warp_bitonic_sort_regs<R>(zf, lane);
+            float* fine = sortbuf + S2;                     // prob's home, dead
+            float* merged = cdf;                            // cdf | bins: S contiguous floats, dead
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int k = r * 32 + lane;
+                if (k < S2) fine[k] = zf[r];
+            }
+            __syncwarp();
+            // merge by rank: ties place the coarse depth first, so the S positions are a permutation
+            for (int k = lane; k < S2; k += 32) {
+                const float c = sortbuf[k];
+                merged[k + count_less(fine, S2, c)] = c;
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int k = r * 32 + lane;
+                if (k < S2) merged[k + count_less_equal(sortbuf, S2, zf[r])] = zf[r];
+            }
+            __syncwarp();
+            for (int i = lane; i < S; i += 32) zo[i] = merged[i];
+            return;
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int k = r * 32 + lane;
+            if (k < S2) sortbuf[S2 + k] = zf[r];
+        }
+    } else {
+        for (int k = lane; k < S2; k += 32) {
+            const float zf = draw(k);
+            sortbuf[S2 + k] = zf;   // overwrites prob[k]: draw() reads cdf / bins only
+        }
     }
-    for (int i = S + lane; i < SP; i += 32) sortbuf[i] = __int_as_float(0x7f800000);
+    for (int i = S + lane; i < SP; i += 32) sortbuf[i] = kInf;
     __syncwarp();
 
     warp_bitonic_sort(sortbuf, SP, lane);
-    float* zo = z_out + (size_t)ray * S;
     for (int i = lane; i < S; i += 32) zo[i] = sortbuf[i];
 }
 
@@ -204,14 +305,26 @@ extern "C" int lb_sample_occ(const float* rays, const float* occ, int occ_dim, c
     while (SP < n_samples) SP <<= 1;
     const size_t smem = (size_t)kWarpsPerBlock * (SP + n_samples) * sizeof(float);
     LB_REQUIRE(smem <= 227 * 1024, "n_samples too large for the shared-memory sort buffer");
-    if (smem > 48 * 1024) {
-        int rc = lb_check_cuda(cudaFuncSetAttribute(sample_occ_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
-                               "lb_sample_occ: smem opt-in");
-        if (rc) return rc;
-    }
     const int blocks = (n_rays + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    sample_occ_kernel<<<blocks, kWarpsPerBlock * 32, smem, (cudaStream_t)stream>>>(
-        rays, occ, occ_dim, t_steps, u1, u2, n_rays, n_samples, SP, perturb, z_out, occ_bits, inds);
+    const int S2 = n_samples / 2;
+#define LB_SAMPLE_LAUNCH(R)                                                                                             \
+    do {                                                                                                                \
+        if (smem > 48 * 1024) {                                                                                         \
+            int rc = lb_check_cuda(cudaFuncSetAttribute(sample_occ_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                                        (int)smem), "lb_sample_occ: smem opt-in");                     \
+            if (rc) return rc;                                                                                          \
+        }                                                                                                               \
+        sample_occ_kernel<R><<<blocks, kWarpsPerBlock * 32, smem, (cudaStream_t)stream>>>(                              \
+            rays, occ, occ_dim, t_steps, u1, u2, n_rays, n_samples, SP, perturb, z_out, occ_bits, inds);                \
+    } while (0)
+    if (S2 <= 32) LB_SAMPLE_LAUNCH(1);
+    else if (S2 <= 64) LB_SAMPLE_LAUNCH(2);
+    else if (S2 <= 128) LB_SAMPLE_LAUNCH(4);
+    else if (S2 <= 256) LB_SAMPLE_LAUNCH(8);
+    else if (S2 <= 512) LB_SAMPLE_LAUNCH(16);
+    else if (S2 <= 1024) LB_SAMPLE_LAUNCH(32);
+    else LB_SAMPLE_LAUNCH(0);
+#undef LB_SAMPLE_LAUNCH
     LB_LAUNCH_CHECK("lb_sample_occ");
     return LB_OK;
 }
