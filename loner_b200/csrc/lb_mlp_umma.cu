@@ -151,6 +151,20 @@ struct BwdSmem {      // the fp32 dE staging tile reuses the mask / E' operand t
 // tile (coalesced, padded rows), thread t reads row t conflict-free, splits it into tf32 hi / lo and writes both
 // to TMEM lane t with tcgen05.st; only the 2 x 8 KB weight tiles are read from shared memory by the MMAs.
 // ------------------------------------------------------------------------------------------
+// Tile walked by this CTA in round kt of the two fused sigma kernels.  A plain stripe (blockIdx.x + kt * gridDim.x)
+// gives every CTA the same segment of its rays in every round whenever gridDim.x is a multiple of the tiles per ray
+// (148 SMs, 512 samples = 4 tiles): the occupancy-guided sampler packs half of the samples around the surface, so
+// the far segments cost a different time than the near ones and whole CTAs finish early / late (measured: forward
+// 1.60 ms on uniform depths, 1.77 ms on surface-concentrated depths).  Rotating the stripe by one CTA per round walks
+// every CTA through all segments.  Rounds run to ceil(n_tiles / gridDim.x) for every CTA; a tile >= n_tiles in the
+// last round is empty (all points invalid).
+__device__ __forceinline__ size_t fused_tile(uint32_t kt) {
+    return (size_t)kt * gridDim.x + (blockIdx.x + kt) % gridDim.x;
+}
+__device__ __forceinline__ uint32_t fused_rounds(size_t n_tiles) {
+    return (uint32_t)((n_tiles + gridDim.x - 1) / gridDim.x);
+}
+
 __device__ __forceinline__ void stage_tile(const float* __restrict__ enc, size_t tile, size_t n_points, uint32_t dst) {
     const float4* base = reinterpret_cast<const float4*>(enc) + tile * (size_t)(kTile * 8);
     const size_t first = tile * (size_t)kTile;
@@ -524,17 +538,17 @@ sigma_bwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
         const uint32_t raw = smem_u32(sm + FusedSmem::raw);
         constexpr uint32_t idesc_de = umma_idesc(128, LB_MLP_IN, 0, 1);
         constexpr uint32_t idesc_u = umma_idesc(64, LB_MLP_IN, 1, 1);
-        size_t tile = blockIdx.x;
-        if (tile < n_tiles) stage_tile(enc, tile, n_points, raw);
+        const uint32_t rounds = fused_rounds(n_tiles);
+        if (rounds > 0) stage_tile(enc, fused_tile(0), n_points, raw);
         cp_async_commit();
         uint32_t parity = 0;
-        for (uint32_t kt = 0; tile < n_tiles; tile += gridDim.x, ++kt) {
+        for (uint32_t kt = 0; kt < rounds; ++kt) {
+            const size_t tile = fused_tile(kt);
             const size_t p = tile * (size_t)kTile + t;
             float ds = 0.0f;
             unsigned long long bits = 0ull;
             if (p < n_points) { ds = __ldg(d_sigma + p); bits = __ldg(act + p); }
-            const size_t next = tile + gridDim.x;
-            if (next < n_tiles) stage_tile(enc, next, n_points, raw + ((kt + 1) & 1u) * kStage);
+            if (kt + 1 < rounds) stage_tile(enc, fused_tile(kt + 1), n_points, raw + ((kt + 1) & 1u) * kStage);
             cp_async_commit();
             cp_async_wait<1>();
             producer_barrier();                                      // this tile's raw rows have landed
@@ -624,11 +638,11 @@ sigma_bwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
     } else {
         // =============================== consumers: hash-grid scatter ===============================
         const int cw = warp - 4;
-        const size_t my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+        const size_t my_tiles = fused_rounds(n_tiles);
         for (size_t u = cw; u < my_tiles * 8; u += FusedShape<kInputGrad>::kConsumerWarps) {
             const uint32_t kt = (uint32_t)(u >> 3);
             const int row = (int)(u & 7) * 16 + (lane >> 1);
-            const size_t tile = blockIdx.x + (size_t)kt * gridDim.x;
+            const size_t tile = fused_tile(kt);
             const size_t p = tile * (size_t)kTile + row;
             const bool valid = p < n_points;
             lb_enc::Point q = {0.5f, 0.5f, 0.5f};
@@ -704,7 +718,7 @@ sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
     float* w2s = reinterpret_cast<float*>(sm + FusedFwdSmem::w2);
     float* vs = reinterpret_cast<float*>(sm + FusedFwdSmem::v);
     const size_t n_tiles = (n_points + kTile - 1) / kTile;
-    const size_t my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const size_t my_tiles = fused_rounds(n_tiles);
 
     if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kFusedFwdTmemCols);
     if (tid == 32) {
@@ -806,7 +820,7 @@ sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
                         bits |= (unsigned long long)m16 << (32 * half + 16 * g);
                     }
                 }
-                const size_t p = (blockIdx.x + (size_t)pk * gridDim.x) * (size_t)kTile + tid;
+                const size_t p = fused_tile(pk) * (size_t)kTile + tid;
                 if (p < n_points) {
                     sigma[p] = s;
                     if (act) act[p] = bits;
@@ -820,7 +834,7 @@ sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
         for (size_t u = cw; u < my_tiles * 8; u += kGatherWarps) {
             const uint32_t kt = (uint32_t)(u >> 3);
             const int row = (int)(u & 7) * 16 + (lane >> 1);
-            const size_t p = (blockIdx.x + (size_t)kt * gridDim.x) * (size_t)kTile + row;
+            const size_t p = fused_tile(kt) * (size_t)kTile + row;
             const bool valid = p < n_points;
             lb_enc::Point q = {0.5f, 0.5f, 0.5f};
             if (valid) q = lb_enc::load_point<true>(rays, zv, nullptr, p, n_samples, nullptr);
