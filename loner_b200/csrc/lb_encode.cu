@@ -207,7 +207,8 @@ int lb_launch_encode_bwd(const lb_plan* plan, const float* rays, const float* z,
 
 extern "C" int lb_encode_fwd(const lb_plan* plan, const float* x01, const float* table, int64_t n_points,
                              float* enc, void* stream) {
-    LB_REQUIRE(plan && x01 && table && enc, "null pointer");
+    LB_REQUIRE(plan, "null pointer");
+    LB_REQUIRE(n_points == 0 || (x01 && table && enc), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n_points >= 0 && n_points < (int64_t)1 << 32, "n_points must be in [0, 2^32)");
     if (n_points == 0) return LB_OK;
     return lb_launch_encode_fwd(plan, nullptr, nullptr, x01, table, (size_t)n_points, 1, enc, (cudaStream_t)stream);
@@ -215,7 +216,8 @@ extern "C" int lb_encode_fwd(const lb_plan* plan, const float* x01, const float*
 
 extern "C" int lb_encode_bwd(const lb_plan* plan, const float* x01, const float* table, const float* d_enc,
                              int64_t n_points, float* grad_table, float* d_x01, void* stream) {
-    LB_REQUIRE(plan && x01 && table && d_enc, "null pointer");
+    LB_REQUIRE(plan, "null pointer");
+    LB_REQUIRE(n_points == 0 || (x01 && table && d_enc), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(grad_table || d_x01, "nothing to compute");
     LB_REQUIRE(n_points >= 0 && n_points < (int64_t)1 << 32, "n_points must be in [0, 2^32)");
     if (n_points == 0) return LB_OK;

@@ -52,7 +52,7 @@ voxel_splat_max_kernel(const float* __restrict__ rays, const float* __restrict__
 extern "C" int lb_voxel_splat_max(const float* rays, const float* z, const float* weights, const uint8_t* ray_mask,
                                   int n_rays, int n_samples, const double* x_bounds, int nx, const double* y_bounds,
                                   int ny, const double* z_bounds, int nz, float* volume, void* stream) {
-    LB_REQUIRE(rays && z && weights && x_bounds && y_bounds && z_bounds && volume, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (rays && z && weights && x_bounds && y_bounds && z_bounds && volume), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1 && nx >= 1 && ny >= 1 && nz >= 1, "bad sizes");
     if (n_rays == 0) return LB_OK;
     const size_t total = (size_t)n_rays * n_samples;

@@ -11,9 +11,10 @@
 extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
                             const float* params, int n_rays, int n_samples, float* sigma, float* enc,
                             uint64_t* act, void* stream) {
-    LB_REQUIRE(plan && params && sigma, "null pointer");
-    LB_REQUIRE((rays && z) || x01, "need (rays, z) or x01");
-    LB_REQUIRE(enc || (rays && lb_sigma_fwd_fused_covers(plan)),
+    LB_REQUIRE(plan, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (params && sigma), "null pointer");   // an empty batch may pass NULL buffers
+    LB_REQUIRE(n_rays == 0 || (rays && z) || x01, "need (rays, z) or x01");
+    LB_REQUIRE(n_rays == 0 || enc || (rays && lb_sigma_fwd_fused_covers(plan)),
                "enc [P,32] is required: it is the encode->MLP hand-off unless lb_sigma_fwd_enc_optional(plan)");
     LB_REQUIRE(plan->cfg.n_levels * LB_FEATS == LB_MLP_IN, "fused sigma head needs 16 levels x 2 features");
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1, "bad sizes");
@@ -36,11 +37,12 @@ extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float*
                             const float* params, float* enc_inout, const uint64_t* act, const float* d_sigma,
                             int n_rays, int n_samples, float* grad_params, float* d_rays, float* d_x01,
                             void* stream) {
-    LB_REQUIRE(plan && params && enc_inout && d_sigma, "null pointer");
-    LB_REQUIRE((rays && z) || x01, "need (rays, z) or x01");
+    LB_REQUIRE(plan, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (params && enc_inout && d_sigma), "null pointer");   // an empty batch may pass NULL buffers
+    LB_REQUIRE(n_rays == 0 || (rays && z) || x01, "need (rays, z) or x01");
     LB_REQUIRE(plan->cfg.n_levels * LB_FEATS == LB_MLP_IN, "fused sigma head needs 16 levels x 2 features");
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1, "bad sizes");
-    LB_REQUIRE(grad_params || d_rays || d_x01, "nothing to compute");
+    LB_REQUIRE(n_rays == 0 || grad_params || d_rays || d_x01, "nothing to compute");
     LB_REQUIRE(!(rays && d_x01) && !(!rays && d_rays), "d_rays goes with (rays, z), d_x01 with x01");
     const size_t P = (size_t)n_rays * (size_t)n_samples;
     LB_REQUIRE(P < (size_t)1 << 32, "n_rays * n_samples must be below 2^32");

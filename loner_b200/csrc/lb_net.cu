@@ -97,7 +97,7 @@ composite_rgb_bwd_kernel(const float* __restrict__ w, const float* __restrict__ 
 }  // namespace
 
 extern "C" int lb_sh4_fwd(const float* d01, int64_t n_points, float* out, void* stream) {
-    LB_REQUIRE(d01 && out, "null pointer");
+    LB_REQUIRE(n_points == 0 || (d01 && out), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n_points >= 0, "negative size");
     if (n_points == 0) return LB_OK;
     sh4_fwd_kernel<<<(unsigned)((n_points + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d01, (size_t)n_points, out);
@@ -106,7 +106,7 @@ extern "C" int lb_sh4_fwd(const float* d01, int64_t n_points, float* out, void* 
 }
 
 extern "C" int lb_sh4_bwd(const float* d01, const float* d_out, int64_t n_points, float* d_d01, void* stream) {
-    LB_REQUIRE(d01 && d_out && d_d01, "null pointer");
+    LB_REQUIRE(n_points == 0 || (d01 && d_out && d_d01), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n_points >= 0, "negative size");
     if (n_points == 0) return LB_OK;
     sh4_bwd_kernel<<<(unsigned)((n_points + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d01, d_out, (size_t)n_points,
@@ -118,7 +118,7 @@ extern "C" int lb_sh4_bwd(const float* d01, const float* d_out, int64_t n_points
 extern "C" int lb_net_bwd(const float* x, int64_t n_points, int n_in, int n_hidden, int n_out, int out_act,
                           const float* params, const float* acts, const float* out, const float* d_out,
                           float* grad_params, float* d_x, void* stream) {
-    LB_REQUIRE(x && params && acts && d_out, "null pointer");
+    LB_REQUIRE(n_points == 0 || (x && params && acts && d_out), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(grad_params || d_x, "nothing to compute");
     LB_REQUIRE(n_points >= 0, "negative size");
     LB_REQUIRE(n_in >= 16 && n_in <= 64 && n_in % 16 == 0, "n_in must be 16, 32, 48 or 64");
@@ -137,7 +137,7 @@ extern "C" int lb_net_bwd(const float* x, int64_t n_points, int n_in, int n_hidd
 
 extern "C" int lb_composite_rgb_fwd(const float* weights, const float* colors, int n_rays, int n_samples, int n_colors,
                                     int white_bkgd, float* rgb, void* stream) {
-    LB_REQUIRE(weights && colors && rgb, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (weights && colors && rgb), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_colors >= 1 && n_colors <= 4, "bad sizes (n_colors in [1, 4])");
     if (n_rays == 0) return LB_OK;
     composite_rgb_fwd_kernel<<<(n_rays + 7) / 8, 256, 0, (cudaStream_t)stream>>>(weights, colors, n_rays, n_samples,
@@ -149,7 +149,7 @@ extern "C" int lb_composite_rgb_fwd(const float* weights, const float* colors, i
 extern "C" int lb_composite_rgb_bwd(const float* weights, const float* colors, const float* g_rgb, int n_rays,
                                     int n_samples, int n_colors, int white_bkgd, float* d_weights, float* d_colors,
                                     void* stream) {
-    LB_REQUIRE(weights && colors && g_rgb, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (weights && colors && g_rgb), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(d_weights || d_colors, "nothing to compute");
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_colors >= 1 && n_colors <= 4, "bad sizes (n_colors in [1, 4])");
     if (n_rays == 0) return LB_OK;

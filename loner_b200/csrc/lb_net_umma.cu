@@ -543,7 +543,7 @@ int lb_launch_net_bwd_umma(const float* x, size_t n_points, int n_in, int n_hidd
 // backward pass will follow (NULL for inference); out_act: 0 = none, 1 = sigmoid (nerf_tcnn.py:93 fused).
 extern "C" int lb_net_fwd(const float* x, int64_t n_points, int n_in, int n_hidden, int n_out, int out_act,
                           const float* params, float* out, float* acts, void* stream) {
-    LB_REQUIRE(x && params && out, "null pointer");
+    LB_REQUIRE(n_points == 0 || (x && params && out), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n_points >= 0, "negative size");
     LB_REQUIRE(n_in >= 16 && n_in <= 64 && n_in % 16 == 0, "n_in must be 16, 32, 48 or 64 (pad the input to a multiple of 16)");
     LB_REQUIRE(n_hidden >= 1 && n_hidden <= kMaxHidden, "n_hidden_layers must be in [1, 6]");

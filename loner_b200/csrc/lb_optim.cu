@@ -128,7 +128,7 @@ int blocks_for(size_t n, int per_block) {
 
 extern "C" int lb_adam_step(float* p, float* g, float* m, float* v, int64_t n, double lr, double beta1,
                             double beta2, double eps, int step, float grad_scale, int zero_grad, void* stream) {
-    LB_REQUIRE(p && g && m && v, "null pointer");
+    LB_REQUIRE(n == 0 || (p && g && m && v), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n >= 0 && step >= 1, "bad size / step");
     LB_REQUIRE((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "buffers must be 16-byte aligned");
     if (n == 0) return LB_OK;
@@ -144,7 +144,7 @@ extern "C" int lb_adam_step(float* p, float* g, float* m, float* v, int64_t n, d
 }
 
 extern "C" int lb_sgd_step(float* p, float* g, int64_t n, float lr, int zero_grad, void* stream) {
-    LB_REQUIRE(p && g, "null pointer");
+    LB_REQUIRE(n == 0 || (p && g), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n >= 0, "negative size");
     if (n == 0) return LB_OK;
     sgd_kernel<<<blocks_for((size_t)n, 256), 256, 0, (cudaStream_t)stream>>>(p, g, (size_t)n, lr, zero_grad);
@@ -154,7 +154,7 @@ extern "C" int lb_sgd_step(float* p, float* g, int64_t n, float lr, int zero_gra
 
 extern "C" int lb_occ_grad(const float* rays, const float* z, const float* depth_gt, float scale_factor,
                            int n_rays, int n_samples, int occ_dim, float* occ_grad, void* stream) {
-    LB_REQUIRE(rays && z && depth_gt && occ_grad, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (rays && z && depth_gt && occ_grad), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1 && occ_dim >= 1, "bad sizes");
     const size_t P = (size_t)n_rays * (size_t)n_samples;
     if (P == 0) return LB_OK;

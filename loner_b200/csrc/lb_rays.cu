@@ -177,7 +177,7 @@ build_camera_rays_kernel(const float* __restrict__ directions, const float* __re
 extern "C" int lb_build_lidar_rays(const float* directions, const float* distances, const int64_t* indices, int n,
                                    int m, const float* rot, const float* origin, float near, float far_max,
                                    float inv_scale, float const_depth, float* rays, float* depths, void* stream) {
-    LB_REQUIRE(directions && rot && origin && rays && depths, "null pointer");
+    LB_REQUIRE(m == 0 || (directions && rot && origin && rays && depths), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n > 0 && m >= 0, "bad sizes");
     if (m == 0) return LB_OK;
     build_rays_kernel<<<(m + kThreads - 1) / kThreads, kThreads, 0, (cudaStream_t)stream>>>(
@@ -190,7 +190,7 @@ extern "C" int lb_build_lidar_rays(const float* directions, const float* distanc
 extern "C" int lb_build_lidar_rays_bwd(const float* directions, const int64_t* indices, int n, int m,
                                        const float* rot, const float* origin, float far_max, const float* d_rays,
                                        float* d_rot, float* d_origin, void* stream) {
-    LB_REQUIRE(directions && rot && origin && d_rays && d_rot && d_origin, "null pointer");
+    LB_REQUIRE(m == 0 || (directions && rot && origin && d_rays && d_rot && d_origin), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n > 0 && m >= 0, "bad sizes");
     if (m == 0) return LB_OK;
     int blocks = (m + kThreads - 1) / kThreads;
@@ -204,7 +204,7 @@ extern "C" int lb_build_lidar_rays_bwd(const float* directions, const int64_t* i
 extern "C" int lb_build_camera_rays(const float* directions, const float* pix_i, const float* pix_j, const float* image,
                                     int n_colors, const int64_t* indices, int n, int m, const float* rot,
                                     const float* origin, float near, float* rays, float* intensities, void* stream) {
-    LB_REQUIRE(directions && rot && origin && rays, "null pointer");
+    LB_REQUIRE(m == 0 || (directions && rot && origin && rays), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n > 0 && m >= 0, "bad sizes");
     LB_REQUIRE(!image || (intensities && n_colors >= 1), "image needs an intensities output and n_colors >= 1");
     if (m == 0) return LB_OK;

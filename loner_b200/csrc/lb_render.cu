@@ -459,7 +459,7 @@ static int check_rs(int n_rays, int n_samples) {
 extern "C" int lb_composite_fwd(const float* sigma, const float* z, const float* rays, const float* noise,
                                 int n_rays, int n_samples, int strategy, float* weights, float* depth,
                                 float* opacity, float* variance, void* stream) {
-    LB_REQUIRE(sigma && z && rays && weights && depth && opacity, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (sigma && z && rays && weights && depth && opacity), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(strategy == 0 || strategy == 1, "strategy must be 0 (default) or 1 (adjusted)");
     if (int rc = check_rs(n_rays, n_samples)) return rc;
     if (n_rays == 0) return LB_OK;
@@ -473,7 +473,7 @@ extern "C" int lb_composite_bwd(const float* sigma, const float* z, const float*
                                 const float* g_w, const float* g_depth, const float* g_opacity,
                                 const float* g_variance, int n_rays, int n_samples, float* d_sigma,
                                 float* d_rays, void* stream) {
-    LB_REQUIRE(sigma && z && rays && d_sigma, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (sigma && z && rays && d_sigma), "null pointer");   // an empty batch may pass NULL buffers
     if (int rc = check_rs(n_rays, n_samples)) return rc;
     if (n_rays == 0) return LB_OK;
     composite_bwd_kernel<<<(n_rays + kWarps - 1) / kWarps, kWarps * 32, 0, (cudaStream_t)stream>>>(
@@ -487,7 +487,8 @@ extern "C" int lb_composite_loss(const float* sigma, const float* z, const float
                                  int n_rays, int n_samples,
                                  float* weights, float* depth, float* opacity, float* variance, float* js,
                                  float* eps, float* loss_parts, float* d_sigma, float* d_rays, void* stream) {
-    LB_REQUIRE(sigma && z && rays && depth_gt && cfg && weights && depth && opacity && loss_parts, "null pointer");
+    LB_REQUIRE(cfg, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (sigma && z && rays && depth_gt && weights && depth && opacity && loss_parts), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(cfg->kind >= LB_LOSS_L1_JS && cfg->kind <= LB_LOSS_L2_LOS, "unknown loss kind");
     LB_REQUIRE(cfg->scale_factor > 0.0f && cfg->min_depth_eps > 0.0f, "scale_factor and min_depth_eps must be positive");
     if (int rc = check_rs(n_rays, n_samples)) return rc;
@@ -503,7 +504,7 @@ extern "C" int lb_composite_loss(const float* sigma, const float* z, const float
 }
 
 extern "C" int lb_count_opaque(const float* rays, const float* depth_gt, int n_rays, float* count, void* stream) {
-    LB_REQUIRE(rays && depth_gt && count, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (rays && depth_gt && count), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n_rays >= 0, "negative size");
     if (n_rays == 0) return LB_OK;
     count_opaque_kernel<<<(n_rays + 255) / 256, 256, 0, (cudaStream_t)stream>>>(rays, depth_gt, n_rays, count);

@@ -296,8 +296,8 @@ __global__ void sample_uniform_kernel(const float* __restrict__ rays, const floa
 extern "C" int lb_sample_occ(const float* rays, const float* occ, int occ_dim, const float* t_steps,
                              const float* u1, const float* u2, int n_rays, int n_samples, float perturb,
                              float* z_out, uint8_t* occ_bits, int64_t* inds, void* stream) {
-    LB_REQUIRE(rays && occ && t_steps && u2 && z_out, "null pointer");
-    LB_REQUIRE(perturb <= 0.0f || u1, "perturb > 0 needs u1");
+    LB_REQUIRE(n_rays == 0 || (rays && occ && t_steps && u2 && z_out), "null pointer");   // an empty batch may pass NULL buffers
+    LB_REQUIRE(n_rays == 0 || perturb <= 0.0f || u1, "perturb > 0 needs u1");
     LB_REQUIRE(n_rays >= 0 && occ_dim > 0, "bad sizes");
     LB_REQUIRE(n_samples >= 8 && (n_samples % 2) == 0 && n_samples <= 8192, "n_samples must be even, in [8, 8192]");
     if (n_rays == 0) return LB_OK;
@@ -331,8 +331,8 @@ extern "C" int lb_sample_occ(const float* rays, const float* occ, int occ_dim, c
 
 extern "C" int lb_sample_uniform(const float* rays, const float* t_steps, const float* u, int n_rays,
                                  int n_samples, float perturb, float* z_out, void* stream) {
-    LB_REQUIRE(rays && t_steps && z_out, "null pointer");
-    LB_REQUIRE(perturb <= 0.0f || u, "perturb > 0 needs u");
+    LB_REQUIRE(n_rays == 0 || (rays && t_steps && z_out), "null pointer");   // an empty batch may pass NULL buffers
+    LB_REQUIRE(n_rays == 0 || perturb <= 0.0f || u, "perturb > 0 needs u");
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1, "bad sizes");
     if (n_rays == 0) return LB_OK;
     const size_t total = (size_t)n_rays * n_samples;
