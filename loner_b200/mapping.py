@@ -248,6 +248,27 @@ class KeyFrame:
                                              self.image, world_cube, ray_range)
 
 
+class _ChunkedResults(dict):
+    """Result dict of a chunked forward (the reference concatenates every key of every chunk, model_tcnn.py:103-107):
+    the concatenation of a key happens on its first read."""
+
+    def __init__(self, chunks, index, **ready):
+        super().__init__(ready)
+        self._chunks, self._index = chunks, index
+
+    def __missing__(self, key):
+        k = self._index[key]                       # KeyError for unknown keys, like a plain dict
+        v = self._chunks[0][k] if len(self._chunks) == 1 else torch.cat([c[k] for c in self._chunks], 0)
+        self[key] = v
+        return v
+
+    def __contains__(self, key):
+        return dict.__contains__(self, key) or key in self._index
+
+    def keys(self):
+        return list(dict.keys(self)) + [k for k in self._index if not dict.__contains__(self, k)]
+
+
 class RayDataParallel:
     """Ray data-parallel context: rays shard over ranks, parameters are replicated, and
     one NCCL all-reduce(SUM) per iteration carries {sigma-head gradient, pose gradients}; the global
@@ -313,7 +334,6 @@ class Optimizer:
         self._num_lidar_samples = settings.num_samples.lidar
         self._enable_sky_segmentation = enable_sky_segmentation
         self._results_lidar = None
-        self._eps_dev = None
         self.losses_log = []
 
     # -- bookkeeping mirrors --------------------------------------------------------------
@@ -329,6 +349,14 @@ class Optimizer:
         """reference optimizer.py:767 computes np.average(eps.cpu()) every iteration (a host sync);
         here the device mean is read back only when somebody asks."""
         return float(self._eps_dev.mean().item()) if self._eps_dev is not None else float("nan")
+
+    @property
+    def _eps_dev(self):
+        return self._results_lidar['depth_eps'] if self._results_lidar is not None else None
+
+    @property
+    def _js_score(self):
+        return self._results_lidar['js_score'] if self._results_lidar is not None else None
 
     def _los_lambda(self):
         L = self._model_config.loss
@@ -374,11 +402,10 @@ class Optimizer:
                 sigma, z, r_c, noise, d_c, cfg, n_op, (L.depthloss_lambda, los_lambda, n_total))
             loss = loss + l_c
             outs.append((z, w, depth, opac, var, js, eps))
-        cat = (lambda k: outs[0][k]) if len(outs) == 1 else (lambda k: torch.cat([o[k] for o in outs], 0))
-        # side effects the occupancy step and callers rely on (reference optimizer.py:730-736)
-        self._results_lidar = {'samples_fine': cat(0), 'weights_fine': cat(1), 'depth_fine': cat(2),
-                               'opacity_fine': cat(3), 'variance': cat(4), 'rays': rays_d}
-        self._js_score, self._eps_dev = cat(5), cat(6)
+        # side effects the occupancy step and callers rely on (reference optimizer.py:730-736); the per-chunk pieces
+        # are concatenated when a key is first read (the occupancy step reads them every 10th iteration only)
+        self._results_lidar = _ChunkedResults(outs, {'samples_fine': 0, 'weights_fine': 1, 'depth_fine': 2, 'opacity_fine': 3,
+                                                     'variance': 4, 'js_score': 5, 'depth_eps': 6}, rays=rays_d)
         self._lidar_depths_gt_cube = depths
         return loss
 
@@ -449,13 +476,30 @@ class Optimizer:
             full[k] = torch.cat((torch.randperm(n, device=self._device), torch.randperm(max_len - n, device=self._device)))
         return full, int(max_len // self._num_lidar_samples)
 
+    def _window_rot_origin(self, pose_tensors):
+        """(R [K,3,3], origin [K,3]) of the window's poses.  While no pose is being optimised (map-only phases,
+        reference defaults.yaml:80-84) the result is reused until a pose tensor is replaced or modified in place
+        (tensor identity + version counter): the ~25 tiny launches of the axis-angle chain are per-iteration
+        latency, not work.  With a trainable pose the chain runs every iteration so autograd reaches the leaves."""
+        if any(t.requires_grad for t in pose_tensors):
+            self._rot_origin_cache = None
+            return pose_to_rot_origin(torch.stack(pose_tensors), self._world_cube)
+        key = tuple((id(t), t._version) for t in pose_tensors)
+        cache = getattr(self, "_rot_origin_cache", None)
+        if cache is None or cache[0] != key:
+            with torch.no_grad():
+                R, o = pose_to_rot_origin(torch.stack(pose_tensors), self._world_cube)
+            cache = (key, list(pose_tensors), R, o)       # holds the tensors: their ids cannot be recycled
+            self._rot_origin_cache = cache
+        return cache[2], cache[3]
+
     def build_batch(self, keyframes, ignore_world_cube=False, fixed=None):
         """One iteration's ray batch: per keyframe index draw + ray construction (optimizer.py:363-424).
         fixed = (full_indices, it_idx, num_iterations) selects the FIXED-strategy slice (optimizer.py:302-308)."""
         rays, depths = [], []
         # one batched pose -> (R, origin) evaluation for the whole window (autograd reaches every pose leaf)
-        poses = torch.stack([(kf._gt_pose if self._use_gt_poses else kf._pose).get_pose_tensor() for kf in keyframes])
-        R, o = pose_to_rot_origin(poses, self._world_cube)
+        pose_tensors = [(kf._gt_pose if self._use_gt_poses else kf._pose).get_pose_tensor() for kf in keyframes]
+        R, o = self._window_rot_origin(pose_tensors)
         for k, kf in enumerate(keyframes):
             idx, sky_idx = self._select_rays(kf)
             if fixed is not None:
