@@ -129,9 +129,17 @@ __device__ __forceinline__ void encode_fwd_point(const lb_level_table& T, const 
 // ------------------------------------------------------------------------------------------
 // backward: table scatter-add (warp-aggregated) and optional dL/dx01
 // ------------------------------------------------------------------------------------------
-constexpr int kAggMaxRuns = 12;   // aggregate when the warp's 16 points fall into <= 12 distinct cells
-constexpr int kAggLevels = 8;     // only the coarse levels carry the run-merging code (instruction-cache budget);
-                                  // finer levels always scatter every corner, which is equally correct
+// Run merging of the backward scatter: a level below kAggLevels merges the warp's 16 points into runs of equal cells
+// when they fall into <= kAggMaxRuns distinct cells; only those levels carry the merging code (instruction-cache
+// budget).  Tuned per kernel on uniform and surface-concentrated depths (profiles/README.md, "run-merging sweep"):
+// the stand-alone scatter kernel is fastest with (8, 15), the fused MLP + scatter kernel -- timed inside the bench
+// step, whose d_sigma has the real sparsity -- with (7, 8).
+constexpr int kAggLevelsScatter = 8, kAggMaxRunsScatter = 15;
+#ifndef LB_AGG_LEVELS_FUSED
+#define LB_AGG_LEVELS_FUSED 7
+#define LB_AGG_MAX_RUNS_FUSED 8
+#endif
+constexpr int kAggLevelsFused = LB_AGG_LEVELS_FUSED, kAggMaxRunsFused = LB_AGG_MAX_RUNS_FUSED;
 
 // segmented suffix sum over the warp's 16 points (2 lanes each): a run head collects its whole run.  Out of line (one
 // copy instead of one per level), called convergently by all 32 lanes, and on all eight values of a level at once:
@@ -164,7 +172,7 @@ static __device__ __noinline__ Float8 seg_suffix_sum8(Float8 x, int dist) {
 
 // One point's backward given its upstream gradient row de[32] (zero outside [l_begin, l_end)).  Called convergently
 // by all 32 lanes of a warp (16 points x 2 lanes); lane parity = x-side.
-template <bool kFromRays, bool kInputGrad, int kNDense>
+template <bool kFromRays, bool kInputGrad, int kNDense, int kAggLevels = kAggLevelsScatter, int kAggMaxRuns = kAggMaxRunsScatter>
 __device__ __forceinline__ void encode_bwd_point(const lb_level_table& T, const Point& q, float zval, const float* de,
                                                  bool valid, size_t p, int n_samples, const float2* __restrict__ table,
                                                  float* __restrict__ grad_table, float* __restrict__ d_rays,

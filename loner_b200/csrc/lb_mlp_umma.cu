@@ -661,7 +661,8 @@ sigma_bwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_empty + 8 * slot);        // this unit's rows are in registers
-            lb_enc::encode_bwd_point<true, kInputGrad, kNDense>(T, q, zval, de, valid, p, n_samples, table, grad_table,
+            lb_enc::encode_bwd_point<true, kInputGrad, kNDense, lb_enc::kAggLevelsFused, lb_enc::kAggMaxRunsFused>(
+                T, q, zval, de, valid, p, n_samples, table, grad_table,
                                                                 d_rays, nullptr, 0, T.n_levels);
         }
     }
