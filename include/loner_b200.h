@@ -20,6 +20,8 @@
  *     (reference src/common/ray_utils.py:313-315), per-sample arrays [N,S].
  *   - a plan is immutable and may be shared between threads; calls are not re-entrant on the same
  *     output buffers.
+ *   - an empty batch (n_rays == 0 / n_points == 0 / n == 0) is a successful no-op and may pass NULL data
+ *     buffers (an empty torch tensor has a NULL data pointer); handles (plan, cfg) must still be valid.
  */
 #ifndef LONER_B200_H
 #define LONER_B200_H

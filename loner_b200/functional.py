@@ -40,28 +40,51 @@ class BuildLidarRays(torch.autograd.Function):
         return d_rot, d_org, None, None, None, None, None, None, None
 
 
+class GradSink:
+    """Shared by the SigmaFromRays nodes of one chunked forward pass whose outputs ALL feed the loss
+    (Optimizer.compute_loss): the chunks' backward kernels accumulate into one parameter-gradient buffer and the
+    node that runs last hands it to autograd, instead of one zero-filled 57 MB buffer per chunk plus autograd's adds."""
+
+    def __init__(self):
+        self.buf, self.pending = None, 0
+
+
 class SigmaFromRays(torch.autograd.Function):
     """Fused xyz=o+d*z -> hash grid -> 32-64-1 MLP (reference rendering_tcnn.py:390-392, nerf_tcnn.py:63-72)."""
 
     @staticmethod
-    def forward(ctx, plan, params, rays, z):
+    def forward(ctx, plan, params, rays, z, sink=None):
         rays_c, z_c = rays.detach().contiguous(), z.detach().contiguous()
         need_grad = params.requires_grad or rays.requires_grad
         sigma, saved = ops.sigma_fwd(plan, params.detach(), rays=rays_c, z=z_c, save_enc=need_grad)
         ctx.plan = plan
         ctx.save_for_backward(params.detach(), rays_c, z_c, *(saved or (None, None)))
         ctx.need = (params.requires_grad, rays.requires_grad)
+        ctx.sink = sink if (sink is not None and params.requires_grad) else None
+        if ctx.sink is not None:
+            ctx.sink.pending += 1
         return sigma
 
     @staticmethod
     def backward(ctx, d_sigma):
         params, rays, z, enc, act = ctx.saved_tensors
         need_p, need_r = ctx.need
-        gp = torch.zeros_like(params) if need_p else None
+        sink = ctx.sink
+        if sink is not None:
+            if sink.buf is None:
+                sink.buf = torch.zeros_like(params)
+            gp = sink.buf
+        else:
+            gp = torch.zeros_like(params) if need_p else None
         dr = torch.zeros_like(rays) if need_r else None
         if need_p or need_r:
             ops.sigma_bwd(ctx.plan, params, (enc, act), d_sigma.contiguous(), rays=rays, z=z, grad_params=gp, d_rays=dr)
-        return None, gp, dr, None
+        if sink is not None:
+            sink.pending -= 1
+            gp = None
+            if sink.pending == 0:
+                gp, sink.buf = sink.buf, None
+        return None, gp, dr, None, None
 
 
 class SigmaFromPoints(torch.autograd.Function):

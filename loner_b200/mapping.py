@@ -19,7 +19,7 @@ import torch.nn as nn
 
 from . import ops
 from ._lib import LonerB200Error
-from .functional import BuildLidarRays, RenderLoss
+from .functional import BuildLidarRays, GradSink, RenderLoss
 from .models import Model, OccupancyGridModel, OccGridRaySampler, UniformRaySampler
 from .optim import FusedAdam
 
@@ -393,11 +393,16 @@ class Optimizer:
                                    L.JS_loss.alpha, L.min_depth_eps, fixed_eps, los_lambda, L.depthloss_lambda)
         nerf = self._model.nerf_model
         loss, outs = 0, []
+        sink = GradSink() if n_rays > render.chunk else None       # every chunk's loss is summed below
         for i in range(0, n_rays, render.chunk):
             r_c, d_c = rays[i:i + render.chunk], depths[i:i + render.chunk]
             z = self._ray_sampler.get_samples(r_c, S, render.perturb)
-            sigma = nerf.sigma_from_rays(r_c, z)
-            noise = torch.randn(z.shape, device=z.device) * render.raw_noise_std if render.raw_noise_std > 0 else None
+            sigma = nerf.sigma_from_rays(r_c, z, sink)
+            noise = None
+            if render.raw_noise_std > 0:
+                noise = torch.randn(z.shape, device=z.device)
+                if render.raw_noise_std != 1.0:
+                    noise = noise * render.raw_noise_std
             l_c, w, depth, opac, var, js, eps = RenderLoss.apply(
                 sigma, z, r_c, noise, d_c, cfg, n_op, (L.depthloss_lambda, los_lambda, n_total))
             loss = loss + l_c

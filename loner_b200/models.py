@@ -44,11 +44,11 @@ class DecoupledNeRF(nn.Module):
         self._max_float = torch.finfo(self._model_intensity.dtype).max
         self._min_float = torch.finfo(self._model_intensity.dtype).min
 
-    def sigma_from_rays(self, rays, z):
+    def sigma_from_rays(self, rays, z, sink=None):
         """Fused sample-point construction + sigma head: [N,13], [N,S] -> [N,S].
         (rendering_tcnn.py:390-392 + nerf_tcnn.py:63,71-72; the intensity hash grid that the reference
         evaluates and discards on sigma-only calls, nerf_tcnn.py:64, is skipped.)"""
-        return SigmaFromRays.apply(self._model_sigma.plan, self._model_sigma.params, rays, z)
+        return SigmaFromRays.apply(self._model_sigma.plan, self._model_sigma.params, rays, z, sink)
 
     def forward(self, pos, dir, sigma_only=False, detach_sigma=True):
         pos = (pos + 1) / 2

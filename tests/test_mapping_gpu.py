@@ -422,3 +422,45 @@ def test_mesher_volume_from_virtual_scans():
             torch.bucketize(pts[:, 2].double().contiguous(), bz)
         ref = ref.scatter_reduce(0, idx, w, "amax", include_self=True)
     assert torch.equal(vol, ref.view(12, 16, 6).permute(1, 0, 2))
+
+
+def test_chunked_backward_shares_one_gradient_buffer():
+    """Several chunks per iteration (the bench runs 2 x 16384 rays): the chunks' backward kernels accumulate into one
+    buffer (functional.GradSink) that the last node hands to autograd.  Same seed, same chunking, with and without
+    the sink: loss identical, parameter and pose gradients equal up to the order of the atomics; and a chunked run
+    agrees with the sum of its chunks' losses."""
+    from loner_b200 import mapping as M, synth
+    kfs, scale, shift = synth.make_keyframes(3, ray_range=(1.0, 30.0), seed=5)
+
+    def run(use_sink):
+        torch.manual_seed(11)
+        s = M.default_settings(n_samples_train=64, log2_hashmap_size=14, ray_range=(1.0, 30.0), lidar=200, sky=0,
+                               voxel_size=32, chunk=256, freeze_poses=False)
+        opt = M.Optimizer(s, None, M.WorldCube(scale, shift), DEV)
+        window = [M.KeyFrame(M.LidarScanData(k.directions, k.distances, None), k.pose, device=DEV) for k in kfs]
+        for i, kf in enumerate(window):
+            kf.is_anchored = i == 0
+            kf.get_lidar_pose().set_fixed(i == 0)
+        opt._model.freeze_sigma_head(False)
+        with torch.no_grad():
+            opt._model.nerf_model._model_sigma.params[3072:] *= 2e3      # a field with structure, active ReLUs
+        orig = M.GradSink
+        if not use_sink:
+            M.GradSink = lambda: None
+        try:
+            rays, depths = opt.build_batch(window, ignore_world_cube=True)      # 600 rays -> chunks of 256, 256, 88
+            loss = opt.compute_loss(None, (rays, depths), 0)
+            loss.backward()
+        finally:
+            M.GradSink = orig
+        p = opt._model.nerf_model._model_sigma.params
+        poses = [kf.get_lidar_pose().get_pose_tensor().grad.clone() for kf in window[1:]]
+        return loss.item(), p.grad.clone(), poses
+
+    l0, g0, q0 = run(False)
+    l1, g1, q1 = run(True)
+    assert l0 == l1
+    assert g1.abs().max() > 0
+    assert (g0 - g1).abs().max() <= 1e-5 * g0.abs().max()
+    for a, b in zip(q0, q1):
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6 * float(a.abs().max()))
