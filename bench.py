@@ -34,9 +34,10 @@ WORKLOADS = {
     # configs[2]: joint keyframe pose refinement (gradients to ray origins / directions -> pose 6-vectors)
     "c3": dict(name="fusionportable_shaped_C3_pose_refinement", keyframes=8, rays_per_keyframe=4096, sky_per_keyframe=0,
                n_samples=512, log2_hashmap_size=19, chunk=16384, ray_range=(1.0, 50.0), voxel_size=100, pose_grad=True),
-    # configs[3]: 2^22 hash tables, 32768 rays per GPU (262144 rays/iter at 8 GPUs)
+    # configs[3]: 2^22 hash tables, 32768 rays per GPU (262144 rays/iter at 8 GPUs); chunk and ray range as in the
+    # reference's haveri_hpk configuration (cfg/haveri_hpk/02_02_04_submaps.yaml:60,71)
     "c4": dict(name="haveri_hpk_shaped_C4_T22", keyframes=8, rays_per_keyframe=4096, sky_per_keyframe=0, n_samples=512,
-               log2_hashmap_size=22, chunk=16384, ray_range=(2.5, 45.0), voxel_size=100, pose_grad=False),
+               log2_hashmap_size=22, chunk=32768, ray_range=(2.5, 45.0), voxel_size=100, pose_grad=False),
 }
 WORKLOAD = WORKLOADS["c2"]
 METRIC = "mapping rays/sec (fwd+bwd)"

@@ -459,7 +459,7 @@ def test_chunked_backward_shares_one_gradient_buffer():
 
     l0, g0, q0 = run(False)
     l1, g1, q1 = run(True)
-    assert l0 == l1
+    assert abs(l0 - l1) <= 1e-6 * abs(l0)          # the loss sums are accumulated with atomics: last-bit differences
     assert g1.abs().max() > 0
     assert (g0 - g1).abs().max() <= 1e-5 * g0.abs().max()
     for a, b in zip(q0, q1):
