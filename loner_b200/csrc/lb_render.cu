@@ -141,6 +141,25 @@ __device__ __forceinline__ float second_moment(const float* __restrict__ w_row, 
     return warp_sum(acc);
 }
 
+// both second moments the loss needs in one sweep over (w, z): about D in cube units (the variance output) and about
+// the weighted mean in metres (the JS score).  Same operations per accumulator as two second_moment calls.
+__device__ __forceinline__ float2 second_moment2(const float* __restrict__ w_row, const float* __restrict__ zr, int S,
+                                                 bool vec, int lane, float c0, float c1, float zscale1) {
+    float a0 = 0.0f, a1 = 0.0f;
+    for (int i0 = lane * kE; i0 < S; i0 += kChunk) {
+        float w[kE], z[kE];
+        load4(w_row, i0, S, vec, 0.0f, w);
+        load4(zr, i0, S, vec, 0.0f, z);
+#pragma unroll
+        for (int e = 0; e < kE; ++e) {
+            const float d0 = c0 - z[e] * 1.0f, d1 = c1 - z[e] * zscale1;
+            a0 = fmaf(w[e], d0 * d0, a0);
+            a1 = fmaf(w[e], d1 * d1, a1);
+        }
+    }
+    return make_float2(warp_sum(a0), warp_sum(a1));
+}
+
 // Reverse pass: given g_i = dL/dw_i (functor), produce d_sigma and the |d| / far partials.
 //   B_k = sum_{i>k} g_i w_i ;  dL/dalpha_k = g_k T_k - B_k / q_k
 //   dL/dsigma_k = dalpha_k * delta_k * exp(-delta_k r_k) * [sigma_k + n_k > 0]
@@ -332,9 +351,10 @@ composite_loss_kernel(const float* __restrict__ sigma, const float* __restrict__
         const bool opaque = (dg > 0.0f) && !(dg > ray.far);        // optimizer.py:724-727
 
         // pass 2: variance about D (output) and std about the weighted mean (JS score)
-        const float V = second_moment(w_row, zr, S, vec, lane, D, 1.0f);
         const float mean = (s.wz * sc) / (A + 1e-10f);             // optimizer.py:739
-        const float var = second_moment(w_row, zr, S, vec, lane, mean, sc) / (A + 1e-10f) + 1e-10f;
+        const float2 m2 = second_moment2(w_row, zr, S, vec, lane, D, mean, sc);
+        const float V = m2.x;
+        const float var = m2.y / (A + 1e-10f) + 1e-10f;
         const float sd = sqrtf(var);
 
         // JS divergence between N(g, (eps_min/3)^2) and N(mean, sd^2)  (optimizer.py:744-746, 922-925)

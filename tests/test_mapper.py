@@ -138,3 +138,24 @@ def test_mapper_checkpoints_round_trip(tmp_path):
     assert torch.equal(d1, d2)
     with pytest.raises(Exception):
         MP.load_checkpoint(opt2, str(tmp_path / "checkpoints" / "nope.tar"))
+
+
+def test_chunked_results_concatenate_on_first_read():
+    """Optimizer._results_lidar keeps the reference's dict contract (optimizer.py:730-736) while concatenating the
+    per-chunk pieces lazily."""
+    import torch
+    from loner_b200.mapping import _ChunkedResults
+    chunks = [(torch.ones(2, 3), torch.zeros(2)), (2 * torch.ones(1, 3), torch.ones(1))]
+    res = _ChunkedResults(chunks, {"samples_fine": 0, "depth_fine": 1}, rays=torch.arange(3))
+    assert "samples_fine" in res and "rays" in res and "nope" not in res
+    assert set(res.keys()) == {"rays", "samples_fine", "depth_fine"}
+    z = res["samples_fine"]
+    assert z.shape == (3, 3) and z[2, 0] == 2 and res["samples_fine"] is z       # cached after the first read
+    assert res["depth_fine"].tolist() == [0.0, 0.0, 1.0]
+    single = _ChunkedResults(chunks[:1], {"samples_fine": 0})
+    assert single["samples_fine"] is chunks[0][0]                                # one chunk: no copy
+    try:
+        res["nope"]
+        assert False
+    except KeyError:
+        pass

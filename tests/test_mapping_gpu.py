@@ -464,3 +464,32 @@ def test_chunked_backward_shares_one_gradient_buffer():
     assert (g0 - g1).abs().max() <= 1e-5 * g0.abs().max()
     for a, b in zip(q0, q1):
         assert torch.allclose(a, b, rtol=1e-4, atol=1e-6 * float(a.abs().max()))
+
+
+def test_fixed_pose_rot_origin_cache_follows_pose_updates():
+    """(R, origin) of fixed poses are cached across iterations (Optimizer._window_rot_origin): an in-place pose update
+    or a replaced pose tensor must invalidate the cache; a trainable pose bypasses it."""
+    from loner_b200 import mapping as M, synth
+    torch.manual_seed(0)
+    kfs, scale, shift = synth.make_keyframes(2, ray_range=(1.0, 30.0), seed=3)
+    s = M.default_settings(n_samples_train=64, log2_hashmap_size=14, ray_range=(1.0, 30.0), lidar=128, sky=0, voxel_size=32)
+    opt = M.Optimizer(s, None, M.WorldCube(scale, shift), DEV)
+    window = [M.KeyFrame(M.LidarScanData(k.directions, k.distances, None), k.pose, device=DEV) for k in kfs]
+    for kf in window:
+        kf.is_anchored = True
+        kf.get_lidar_pose().set_fixed(True)
+    r0, _ = opt.build_batch(window, ignore_world_cube=True)
+    cache = opt._rot_origin_cache
+    r1, _ = opt.build_batch(window, ignore_world_cube=True)
+    assert opt._rot_origin_cache is cache, "unchanged fixed poses must reuse the cached (R, origin)"
+    o0 = r0[:128, 0:3].mean(0)
+    assert torch.allclose(r1[:128, 0:3].mean(0), o0)
+    with torch.no_grad():
+        window[0].get_lidar_pose().get_pose_tensor()[0] += 0.5          # move keyframe 0 by 0.5 m along x, in place
+    r2, _ = opt.build_batch(window, ignore_world_cube=True)
+    assert opt._rot_origin_cache is not cache
+    shift_x = (r2[:128, 0].mean() - o0[0]).item()
+    assert abs(shift_x - 0.5 / float(scale)) < 1e-5
+    window[1].get_lidar_pose().set_fixed(False)                          # trainable pose: autograd chain every time
+    r3, _ = opt.build_batch(window, ignore_world_cube=True)
+    assert opt._rot_origin_cache is None and r3.requires_grad
