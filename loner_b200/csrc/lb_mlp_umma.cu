@@ -692,12 +692,18 @@ int launch_fused(const lb_plan* plan, const lb_level_table& T, const float* rays
 // fused forward: hash-grid gather + MLP in one launch.
 //
 // 24 gather warps (the 2-lanes-per-point walk of lb_encode.cu, 16 points per warp-unit) write their rows into a
-// 4-tile shared-memory ring (and to `enc` for the backward when it is non-NULL); 4 MLP warps take each full tile
+// 2-tile shared-memory ring (and to `enc` for the backward when it is non-NULL); 4 MLP warps take each full tile
 // through the tf32 / TMEM-operand pipeline of mlp_fwd_umma_kernel.  The hand-off never leaves the SM, so the MLP's
 // re-read of the encodings (128 B per point) and its launch disappear behind the gather, which stays bound by L2
 // sector fills.  A / H are double-buffered in TMEM: the MMAs of tile k run under the epilogue of tile k - 1.
 // ------------------------------------------------------------------------------------------
-constexpr int kFwdRing = 4;
+// Ring depth: the gather warps issue their loads before they wait for a slot, so depth buys nothing (2 / 3 / 4 / 6 / 8
+// slots: lb_sigma_fwd 3.16 / 3.19 / 3.19 / 3.27 / 3.36 ms per bench step) while every 18 KB slot comes out of the L1 that
+// serves the gathers; two slots fit the 64 KB shared-memory carve-out.
+#ifndef LB_FWD_RING
+#define LB_FWD_RING 2
+#endif
+constexpr int kFwdRing = LB_FWD_RING;
 constexpr int kGatherWarps = 24;
 constexpr int kFusedFwdThreads = kProducerThreads + 32 * kGatherWarps;
 constexpr uint32_t kFusedFwdTmemCols = 256;        // H0 64 | H1 64 | A0 hi 32 lo 32 | A1 hi 32 lo 32

@@ -3,10 +3,8 @@
 cp loner_b200/lib/libloner_b200.so /tmp/lib_default.so
 for v in loner_b200/lib/variants/*.so; do
   cp $v loner_b200/lib/libloner_b200.so
-  for w in c2 c3; do
-  python bench.py --no-cpu-baseline --steps 20 --warmup 5 --workload $w 2>/dev/null | python -c "
-import json,sys;d=json.loads(sys.stdin.read().strip().splitlines()[-1]);k=d['roofline']['kernels_ms_per_step'];print('$(basename $v)', '$w', 'step', round(d['ms_per_step'],3), 'sigma_bwd', k['lb_sigma_bwd'], 'sigma_fwd', k['lb_sigma_fwd'])"
-  done
-  python profiles/bench_levels_z.py 2>&1 | sed -n 2,4p
+  python bench.py --no-cpu-baseline --steps 20 --warmup 5 2>/dev/null | python -c "
+import json,sys;d=json.loads(sys.stdin.read().strip().splitlines()[-1]);k=d['roofline']['kernels_ms_per_step'];print('$(basename $v)', 'step', round(d['ms_per_step'],3), 'sigma_bwd', k['lb_sigma_bwd'], 'sigma_fwd', k['lb_sigma_fwd'])"
+  python profiles/bench_levels_z.py 2>&1 | sed -n 2,3p
 done
 cp /tmp/lib_default.so loner_b200/lib/libloner_b200.so
