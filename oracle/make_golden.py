@@ -29,7 +29,7 @@ GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 TABLE_SCALE = 2000.0   # tables are U(-1e-4,1e-4) at init; scale them to "trained" magnitudes (+-0.2)
 
 
-def model_cfg(ns, n_samples, log2_T, voxel, ray_range, loss_selection="L1_JS", min_js=1.0):
+def model_cfg(ns, n_samples, log2_T, voxel, ray_range, loss_selection="L1_JS", min_js=1.0, chunk=16384):
     A = ns.settings.Settings
     nerf = dict(enable_view_dependence=True,
                 dir_encoding_intensity=dict(degree=4, otype="SphericalHarmonics"),
@@ -45,7 +45,7 @@ def model_cfg(ns, n_samples, log2_T, voxel, ray_range, loss_selection="L1_JS", m
         data=dict(ray_range=list(ray_range)),
         model=dict(num_colors=3, model_type="nerf_decoupled", nerf_config=nerf, ray_range=list(ray_range),
                    render=dict(N_samples_train=n_samples, N_samples_test=n_samples * 2, retraw=True, lindisp=False,
-                               perturb=1.0, white_bkgd=False, raw_noise_std=1.0, chunk=16384, netchunk=0),
+                               perturb=1.0, white_bkgd=False, raw_noise_std=1.0, chunk=chunk, netchunk=0),
                    occ_model=dict(voxel_size=voxel, lr=1e-4, N_iters_acc=10)),
         train=dict(lrate_sigma_mlp=0.01, lrate_rgb=0.01, lrate_pose=0.001, lrate_gamma=1.0),
         loss=dict(loss_selection=loss_selection,

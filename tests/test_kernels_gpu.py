@@ -50,9 +50,10 @@ def test_sample_occ_bit_exact_golden(name, dev, ops, O):
     assert torch.equal(bits.cpu().bool(), ref["occ_bits"]), "occupancy bits differ from oracle"
     assert torch.equal(inds.cpu(), ref["inds"]), "searchsorted indices differ from oracle"
     assert torch.equal(z.cpu(), ref["z"]), "sorted depths differ from oracle"
-    # and against the reference's own run (same tolerance the oracle is pinned with)
+    # and against the reference's own run: bit-exact (the benchmark-shaped fixture, where 5 of 524288 draws sit on a
+    # cdf knot, is covered in test_reference_chain_gpu.py)
     assert torch.equal(bits.cpu().bool(), g["occ_bits"])
-    assert (inds.cpu() != g["inds"]).float().mean().item() < 1e-3
+    assert torch.equal(inds.cpu(), g["inds"])
 
 
 @pytest.mark.parametrize("S,N,D,perturb", [(512, 1024, 100, 1.0), (64, 777, 33, 1.0), (256, 300, 50, 0.0), (2048, 64, 100, 0.0)])

@@ -118,6 +118,44 @@ def test_occ_update_against_reference(name):
     assert (occ != g["occ"]).any()
 
 
+def test_c2_shape_oracle_against_reference():
+    """The oracle at the benchmark shape (2048 rays x 512 samples, T = 2^19, warmed 100^3 grid, two chunks) against
+    the reference's own run recorded by oracle/make_golden_c2.py."""
+    from conftest import c2_shape_random, c2_shape_params
+    g = load_golden("c2_shape_ogm_l1js")
+    rnd = c2_shape_random(g)
+    zs, inds, bits = [], [], []
+    for c, (u1, u2, _) in enumerate(rnd):
+        s = O.sample_occ(g["rays"][c * g["chunk"]:(c + 1) * g["chunk"]], g["occ"], u1, u2, g["n_samples"], 1.0)
+        zs.append(s["z"]); inds.append(s["inds"]); bits.append(s["occ_bits"])
+    z, inds, bits = torch.cat(zs), torch.cat(inds), torch.cat(bits)
+    gold_bits = torch.from_numpy(np.unpackbits(g["occ_bits_packed"].numpy(), axis=1)).bool()
+    assert torch.equal(bits, gold_bits) and int(bits.sum()) == g["occ_bits_count"]
+    d_inds = (inds - g["inds"].long()).abs()
+    assert (d_inds != 0).sum().item() <= 16 and d_inds.max().item() <= 1       # measured: 5 of 524288 (see oracle header)
+    dz = (z - g["z"]).abs()
+    assert (dz > 1e-6).float().mean().item() < 1e-3 and dz.max().item() < 5e-3
+    # gradient chain on the reference's own depths ("trained" tables)
+    st = g["states"][2000]
+    p = c2_shape_params(g, 2000).requires_grad_(True)
+    rays = g["rays"].clone().requires_grad_(True)
+    noise = torch.cat([r[2] for r in rnd])
+    zg = g["z"]
+    xyz = rays[:, None, 0:3] + rays[:, None, 3:6] * zg[..., None]
+    sigma = O.sigma_field(xyz.reshape(-1, 3), p, g["log2_T"]).view(zg.shape)
+    torch.testing.assert_close(sigma[::g["row_stride"]].detach(), st["sigma_rows"], rtol=1e-5, atol=1e-6)
+    c = O.composite(sigma, zg, rays[:, 3:6], rays[:, -1:], noise)
+    ls = O.depth_loss(c["weights"], c["depth"], c["opacity"], zg, rays[:, -1:], g["depths"], g["scale"],
+                      dict(loss_selection="L1_JS", min_js_score=g["min_js"]))
+    torch.testing.assert_close(ls["loss"].detach(), st["loss"], rtol=1e-5, atol=1e-6)
+    ls["loss"].backward()
+    torch.testing.assert_close(p.grad[:3072], st["mlp_grad"], rtol=1e-4, atol=1e-7)
+    tg = p.grad[3072:]
+    torch.testing.assert_close(tg[st["table_grad_idx"]], st["table_grad_val"], rtol=1e-4, atol=1e-8)
+    assert int((tg != 0).sum()) == st["table_grad_nnz"]
+    torch.testing.assert_close(rays.grad, st["rays_grad"], rtol=1e-4, atol=1e-6)
+
+
 def test_adam_matches_torch():
     torch.manual_seed(0)
     p = torch.randn(1000); p0 = p.clone().requires_grad_(True)
