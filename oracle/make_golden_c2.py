@@ -6,7 +6,8 @@ Optimizer.compute_loss (src/mapping/optimizer.py:701-859) -> Model.forward chunk
 
     2048 rays (1792 lidar + 256 sky) x 512 samples, 16-level hash grid T = 2^19, 100^3 occupancy grid warmed by the
     reference's own update rule, cfg.render.chunk = 1024 (two chunks, so the per-chunk RNG draws and the concatenation
-    are exercised), L1_JS loss, pose gradient on; two parameter states: tables x1 (initialisation) and x2000 ("trained").
+    are exercised), pose gradient on; states: L1_JS with tables x1 (initialisation) and x2000 ("trained"), and L2_JS
+    with tables x2000 (the same pipeline without the sign discontinuity of the L1 line-of-sight term).
 
 The random tensors come from oracle/portable_rng.py (patched over torch.rand / torch.randn while the reference runs),
 so the fixture stores none of them: tests regenerate the same bits.  Stored in full: rays, occupancy grid, sample
@@ -114,7 +115,10 @@ def main():
                kf_pose=kfs[1].pose.clone(), kf_directions=kfs[1].directions[:, idx].clone(),
                kf_distances=kfs[1].distances[idx].clone(), occ=occ_before, states={})
     from oracle import loner_oracle as O
-    for table_scale in (2000.0, 1.0):
+    # L1_JS at both parameter states; L2_JS (a loss without the sign discontinuity of |w - w_gt|) at the trained state
+    for key, table_scale, loss_sel in ((2000, 2000.0, "L1_JS"), (1, 1.0, "L1_JS"), ("l2js_2000", 2000.0, "L2_JS")):
+        opt._model_config["loss"]["loss_selection"] = loss_sel      # raw dict access: attribute reads return wrapped copies
+        assert opt._model_config.loss.loss_selection == loss_sel
         p = O.init_sigma_params(LOG2_T, 1337)
         p[O.MLP_PARAMS:] *= table_scale
         with torch.no_grad():
@@ -125,7 +129,7 @@ def main():
         assert torch.equal(opt._occupancy_grid.detach(), occ_before)
         rays.grad = None
         st, rng, log_ss, z = golden_iteration(ns, opt, rays, depths, pose, 0)
-        st.update(table_scale=table_scale, params_checksum=p.double().sum().item())
+        st.update(table_scale=table_scale, loss_selection=loss_sel, params_checksum=p.double().sum().item())
         # sampler outputs do not depend on the parameters: stored once, asserted equal for the second state
         inds = torch.cat(log_ss, 0)
         if "z" not in out:
@@ -157,8 +161,8 @@ def main():
         top = torch.topk(delta.abs(), 16384).indices.sort().values
         st.update(occ_delta_idx=top, occ_delta_val=delta[top].clone(), occ_delta_norm=delta.double().norm().item(),
                   occ_delta_nnz=int((delta != 0).sum()))
-        out["states"][int(table_scale)] = st
-        print(f"state x{table_scale:g}: loss {float(st['loss']):.6f} eps {st['depth_eps']:.4f} "
+        out["states"][key] = st
+        print(f"state {key} ({loss_sel}, tables x{table_scale:g}): loss {float(st['loss']):.6f} eps {st['depth_eps']:.4f} "
               f"|table grad| {st['table_grad_norm']:.4e} nnz {st['table_grad_nnz']}", flush=True)
     path = os.path.join(G.GOLDEN_DIR, f"{NAME}.pt")
     torch.save(out, path)

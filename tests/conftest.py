@@ -71,10 +71,11 @@ def c2_shape_random(g):
     return out
 
 
-def c2_shape_params(g, table_scale):
+def c2_shape_params(g, state):
+    """Flat sigma parameters of a state of the benchmark-shaped fixture (keys 2000, 1, "l2js_2000")."""
     from oracle import loner_oracle as O
+    st = g["states"][state]
     p = O.init_sigma_params(g["log2_T"], g["param_seed"])
-    p[O.MLP_PARAMS:] *= float(table_scale)
-    st = g["states"][int(table_scale)]
+    p[O.MLP_PARAMS:] *= float(st["table_scale"])
     assert abs(p.double().sum().item() - st["params_checksum"]) < 1e-6 * max(1.0, abs(st["params_checksum"]))
     return p
