@@ -57,7 +57,7 @@ def model_cfg(ns, n_samples, log2_T, voxel, ray_range, loss_selection="L1_JS", m
                   depthloss_lambda=0.005, cam_lambda=1, std_lambda=0.0)))
 
 
-def bare_optimizer(ns, cfg, scale, sampler="OGM"):
+def bare_optimizer(ns, cfg, scale, sampler="OGM", device="cpu"):
     """A reference Optimizer with only the state compute_loss/_step_occupancy_grid read
     (its __init__ needs calibration/settings plumbing that is outside the hot path)."""
     Opt = ns.optimizer.Optimizer
@@ -66,14 +66,14 @@ def bare_optimizer(ns, cfg, scale, sampler="OGM"):
                               "write_ray_point_clouds", "draw_comp_graph", "log_losses")}
     o._settings = ns.settings.Settings(dict(debug=dbg, samples_selection=dict(strategy=sampler)))
     o._model_config = cfg
-    o._device = "cpu"
+    o._device = device
     o._scale_factor = scale
     o._optimization_settings = ns.optimizer.OptimizationSettings()
     o._global_step = 0
     o._keyframe_count = 0
-    o._model = ns.model_tcnn.Model(cfg.model)
+    o._model = ns.model_tcnn.Model(cfg.model).to(device)
     if sampler == "OGM":
-        o._occupancy_grid_model = ns.model_tcnn.OccupancyGridModel(cfg.model.occ_model)
+        o._occupancy_grid_model = ns.model_tcnn.OccupancyGridModel(cfg.model.occ_model).to(device)
         o._occupancy_grid = o._occupancy_grid_model()
         o._occupancy_grid_optimizer = torch.optim.SGD(o._occupancy_grid_model.parameters(), lr=cfg.model.occ_model.lr)
         o._ray_sampler = ns.ray_sampling.OccGridRaySampler()
