@@ -83,6 +83,9 @@ typedef struct {
 
 /* ------------------------------------------------------------------------------------------ */
 LB_API int         lb_version(void);
+/* bit 0: built with -DLB_TEST_SWITCHES (fp32 CUDA-core MLP cross-check and the LONER_B200_* environment switches
+ * exist); the shipped library returns 0: one implementation per operation, no run-time backend selection. */
+LB_API int         lb_build_flags(void);
 LB_API const char* lb_last_error(void);
 
 /* Immutable level table (scale, resolution, offset, size, dense|hash) following tiny-cuda-nn's
@@ -90,6 +93,9 @@ LB_API const char* lb_last_error(void);
  * (src/models/nerf_tcnn.py:35-40). */
 LB_API int  lb_plan_create(const lb_grid_config* cfg, lb_plan** out);
 LB_API void lb_plan_destroy(lb_plan* plan);
+/* Overrides the device L2 size the plan was created with.  The encode launchers walk the levels in groups whose tables
+ * fit 55 % of it (lb_encode.cu); tests use a tiny value to exercise the level-group passes on small tables. */
+LB_API int  lb_plan_set_l2_bytes(lb_plan* plan, int64_t l2_bytes);
 /* number of fp32 scalars: MLP matrices (W1[64,32] then W2[16,64], row-major [out,in]) and tables */
 LB_API int  lb_plan_param_counts(const lb_plan* plan, int64_t* n_mlp, int64_t* n_table);
 LB_API int  lb_plan_level(const lb_plan* plan, int level, float* scale, uint32_t* resolution,
@@ -188,14 +194,17 @@ LB_API int lb_composite_bwd(const float* sigma, const float* z, const float* ray
  * Outputs: weights [N,S], depth/opacity/variance [N], per-ray js [N] (clamped score), eps [N],
  * loss_parts [4] += {sum_opaque (s*D-g)^2, sum_all |w-w_gt| (or squared), sum_opaque |A-1|, n_opaque_local},
  * d_sigma [N,S] = dL/dsigma for grad_output 1, d_rays [N,13] (overwritten; |d| and far terms).
- * cfg->n_opaque / n_total_samples carry the GLOBAL normalisers (see lb_count_opaque); when
- * n_opaque_dev (device float[1]) is non-NULL it overrides cfg->n_opaque without a host round trip. */
+ * cfg->n_opaque / n_total_samples carry the GLOBAL normalisers; when norm_dev (device float[2] =
+ * {opaque-ray count, ray count}, filled by lb_count_opaque and summed over chunks / ranks) is non-NULL it
+ * overrides them without a host round trip: n_opaque = norm_dev[0], n_total_samples = norm_dev[1] * S
+ * (norm_dev[1] <= 0 keeps cfg->n_total_samples). */
 LB_API int lb_composite_loss(const float* sigma, const float* z, const float* rays, const float* noise,
-                      const float* depth_gt, const lb_loss_config* cfg, const float* n_opaque_dev,
+                      const float* depth_gt, const lb_loss_config* cfg, const float* norm_dev,
                       int n_rays, int n_samples,
                       float* weights, float* depth, float* opacity, float* variance, float* js,
                       float* eps, float* loss_parts, float* d_sigma, float* d_rays, void* stream);
-/* count of opaque rays (depth_gt > 0 and depth_gt <= far; optimizer.py:724-727) -> count[0] (float, +=) */
+/* count of opaque rays (depth_gt > 0 and depth_gt <= far; optimizer.py:724-727): count[0] += opaque rays,
+ * count[1] += n_rays (device float[2]: the norm_dev of lb_composite_loss) */
 LB_API int lb_count_opaque(const float* rays, const float* depth_gt, int n_rays, float* count, void* stream);
 
 /* ---- O1/O2: optimiser step and occupancy update ------------------------------------------ */

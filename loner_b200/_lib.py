@@ -39,6 +39,8 @@ SIGNATURES = {
     "lb_last_error": (C.c_char_p, []),
     "lb_plan_create": (_I, [C.POINTER(GridConfig), C.POINTER(_P)]),
     "lb_plan_destroy": (None, [_P]),
+    "lb_plan_set_l2_bytes": (_I, [_P, _L]),
+    "lb_build_flags": (_I, []),
     "lb_plan_param_counts": (_I, [_P, C.POINTER(_L), C.POINTER(_L)]),
     "lb_plan_level": (_I, [_P, _I, C.POINTER(_F), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32),
                            C.POINTER(C.c_uint32), C.POINTER(C.c_int32)]),
@@ -103,7 +105,12 @@ def check(rc, what=""):
 # the per-kernel device time for the roofline figures).
 LAUNCHES = {}
 TIMING = {"on": False, "events": []}
-_HOST_ONLY = {"lb_plan_create", "lb_plan_param_counts", "lb_plan_level"}
+_HOST_ONLY = {"lb_plan_create", "lb_plan_param_counts", "lb_plan_level", "lb_plan_set_l2_bytes"}
+
+
+def test_switches():
+    """True for a library built with -DLB_TEST_SWITCHES (fp32 CUDA-core MLP cross-check available)."""
+    return bool(load().lb_build_flags() & 1)
 
 
 def call(name, *args):

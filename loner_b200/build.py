@@ -39,7 +39,14 @@ def up_to_date():
     return all(os.path.getmtime(s) <= t for s in _deps())
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, test_switches=False):
+    """test_switches: compile with -DLB_TEST_SWITCHES (fp32 CUDA-core MLP + LONER_B200_* environment switches for the
+    cross-check tests and profiles/ experiments).  The default, shipped build has neither."""
+    flag_file = os.path.join(LIB_DIR, "build_flags.txt")
+    want = "test-switches" if test_switches else "shipped"
+    have = open(flag_file).read().strip() if os.path.exists(flag_file) else None
+    if have != want:
+        force = True
     if not force and up_to_date():
         return LIB_PATH
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
@@ -54,7 +61,8 @@ def build(force=False, verbose=False):
         obj = os.path.join(OBJ_DIR, os.path.basename(src)[:-3] + ".o")
         if not force and os.path.exists(obj) and os.path.getmtime(obj) >= max(os.path.getmtime(src), t_hdr):
             return obj, ""
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        cmd = [nvcc] + NVCC_FLAGS + (["-DLB_TEST_SWITCHES"] if test_switches else []) + \
+            (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
@@ -69,8 +77,10 @@ def build(force=False, verbose=False):
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+    with open(flag_file, "w") as f:
+        f.write(want + "\n")
     return LIB_PATH
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, test_switches="--test-switches" in sys.argv))

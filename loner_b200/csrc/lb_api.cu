@@ -79,16 +79,26 @@ extern "C" int lb_plan_create(const lb_grid_config* cfg, lb_plan** out) {
         if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sm > 0) p->sm_count = sm;
         if (cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, dev) == cudaSuccess && l2 > 0) p->l2_bytes = l2;
     }
-    if (const char* e = getenv("LONER_B200_L2_BYTES")) {   // tests force level-group passes on small tables
-        const long long v = atoll(e);
-        if (v > 0) p->l2_bytes = v;
-    }
     cudaGetLastError();  // plan creation must work without a device (host-only tests)
     *out = p;
     return LB_OK;
 }
 
 extern "C" void lb_plan_destroy(lb_plan* plan) { free(plan); }
+
+extern "C" int lb_plan_set_l2_bytes(lb_plan* plan, int64_t l2_bytes) {
+    LB_REQUIRE(plan && l2_bytes > 0, "null plan or non-positive size");
+    plan->l2_bytes = l2_bytes;
+    return LB_OK;
+}
+
+extern "C" int lb_build_flags(void) {
+#ifdef LB_TEST_SWITCHES
+    return 1;
+#else
+    return 0;
+#endif
+}
 
 extern "C" int lb_plan_param_counts(const lb_plan* plan, int64_t* n_mlp, int64_t* n_table) {
     LB_REQUIRE(plan, "null plan");

@@ -78,11 +78,12 @@ bool lb_encode_single_group(const lb_plan* plan);
 // lb_mlp_umma.cu: MLP backward + encode backward in one kernel (dL/denc never leaves the SM).  Returns 1 when the
 // configuration is not covered (caller runs the two separate kernels), 0 on success, < 0 on error.
 bool lb_sigma_fwd_fused_covers(const lb_plan* plan);
-int lb_launch_sigma_fwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* params, size_t n_points,
-                              int n_samples, float* sigma, float* enc, uint64_t* act, cudaStream_t st);
-int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* params,
-                              const float* enc, const uint64_t* act, const float* d_sigma, size_t n_points, int n_samples,
-                              float* grad_params, float* d_rays, cudaStream_t st);
+int lb_launch_sigma_fwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* params,
+                              size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act, cudaStream_t st);
+int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* x01,
+                              const float* params, const float* enc, const uint64_t* act, const float* d_sigma,
+                              size_t n_points, int n_samples, float* grad_params, float* d_rays, float* d_x01,
+                              cudaStream_t st);
 
 static inline lb_level_table lb_make_level_table(const lb_plan* p) {
     lb_level_table t;

@@ -1,11 +1,11 @@
 // R4: the fused sigma head = hash-grid encode (lb_encode.cu) + 32-64-1 MLP (lb_mlp.cu), forward and backward.
 //
 // Replaces tcnn.NetworkWithInputEncoding(3 -> 1) as used by DecoupledNeRF (reference
-// src/models/nerf_tcnn.py:35-38,63-72).  With (rays, z) and tables that fit the L2, each direction is ONE
-// warp-specialised kernel (lb_mlp_umma.cu: gather warps <-> tcgen05 MLP warps through a shared-memory ring); `enc`
-// [P,32] is then written once by the forward and read once by the backward.  Otherwise (x01 point source, level-group
-// passes, fp32 CUDA-core MLP) two launches per direction with `enc` as the hand-off, overwritten IN PLACE with
-// dL/d_enc by the MLP backward for the scatter kernel.
+// src/models/nerf_tcnn.py:35-38,63-72).  With tables that fit the L2, each direction is ONE warp-specialised kernel for
+// either point source -- (rays, z) of the fused render path or x01 [P,3] as tcnn.NetworkWithInputEncoding receives it
+// (lb_mlp_umma.cu: gather warps <-> tcgen05 MLP warps through a shared-memory ring); `enc` [P,32] is then written once by
+// the forward and read once by the backward.  Otherwise (level-group passes for tables beyond the L2) two launches per
+// direction with `enc` as the hand-off, overwritten IN PLACE with dL/d_enc by the MLP backward for the scatter kernel.
 #include "lb_common.cuh"
 
 extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
@@ -14,7 +14,7 @@ extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float*
     LB_REQUIRE(plan, "null pointer");
     LB_REQUIRE(n_rays == 0 || (params && sigma), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n_rays == 0 || (rays && z) || x01, "need (rays, z) or x01");
-    LB_REQUIRE(n_rays == 0 || enc || (rays && lb_sigma_fwd_fused_covers(plan)),
+    LB_REQUIRE(n_rays == 0 || enc || lb_sigma_fwd_fused_covers(plan),
                "enc [P,32] is required: it is the encode->MLP hand-off unless lb_sigma_fwd_enc_optional(plan)");
     LB_REQUIRE(plan->cfg.n_levels * LB_FEATS == LB_MLP_IN, "fused sigma head needs 16 levels x 2 features");
     LB_REQUIRE(n_rays >= 0 && n_samples >= 1, "bad sizes");
@@ -22,8 +22,8 @@ extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float*
     LB_REQUIRE(P < (size_t)1 << 32, "n_rays * n_samples must be below 2^32");
     if (P == 0) return LB_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (rays && (act || !enc)) {   // one kernel for both stages when the configuration allows it (lb_mlp_umma.cu)
-        const int frc = lb_launch_sigma_fwd_fused(plan, rays, z, params, P, n_samples, sigma, enc, act, st);
+    if (act || !enc) {   // one kernel for both stages, either point source, when the configuration allows it (lb_mlp_umma.cu)
+        const int frc = lb_launch_sigma_fwd_fused(plan, rays, z, rays ? nullptr : x01, params, P, n_samples, sigma, enc, act, st);
         if (frc <= 0) return frc;
     }
     int rc = lb_launch_encode_fwd(plan, rays, z, x01, params + LB_MLP_PARAMS, P, rays ? n_samples : 1, enc, st);
@@ -48,9 +48,9 @@ extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float*
     LB_REQUIRE(P < (size_t)1 << 32, "n_rays * n_samples must be below 2^32");
     if (P == 0) return LB_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (rays && !d_x01) {      // one kernel for both stages when the configuration allows it (lb_mlp_umma.cu)
-        const int frc = lb_launch_sigma_bwd_fused(plan, rays, z, params, enc_inout, act, d_sigma, P, n_samples, grad_params,
-                                                  d_rays, st);
+    {      // one kernel for both stages, either point source, when the configuration allows it (lb_mlp_umma.cu)
+        const int frc = lb_launch_sigma_bwd_fused(plan, rays, z, rays ? nullptr : x01, params, enc_inout, act, d_sigma, P,
+                                                  n_samples, grad_params, d_rays, d_x01, st);
         if (frc <= 0) return frc;
     }
     int rc = lb_launch_mlp_bwd(plan, params, enc_inout, d_sigma, act, P, grad_params, st);

@@ -5,14 +5,15 @@
 // cfg/nerf_config/default_nerf_hash.yaml:26-31).  Weight layout = tcnn's: W1 [64,32] then W2 [16,64]
 // row-major [out,in]; only W2 row 0 produces sigma, rows 1-15 are padding and receive zero gradient.
 //
-// Two implementations behind one launcher:
-//   * SIMT  (this file): fp32 CUDA-core kernels, one thread per point.
-//   * UMMA  (lb_mlp_umma.cu): tcgen05 tensor-core kernels; used whenever the caller supplies the `act` buffer.
-// LONER_B200_MLP=simt forces the SIMT kernels (used by the tests to cross-check the tensor-core path).
+// The shipped library has ONE implementation: the tcgen05 tensor-core kernels of lb_mlp_umma.cu (the caller supplies the
+// `act` ReLU-mask buffer).  The fp32 CUDA-core kernels in this file are a cross-check for the tests and exist only in a
+// build with -DLB_TEST_SWITCHES (`python -m loner_b200.build --test-switches`; lb_build_flags() & 1): there, act == NULL
+// or LONER_B200_MLP=simt selects them.
 #include <stdlib.h>
 
 #include "lb_common.cuh"
 
+#ifdef LB_TEST_SWITCHES
 namespace {
 
 constexpr int kThreads = 128;
@@ -155,7 +156,7 @@ int grid_for(int sm_count, size_t n_points, int blocks_per_sm) {
 
 }  // namespace
 
-// LONER_B200_MLP=simt forces the fp32 CUDA-core kernels (the tests use it to cross-check the tcgen05 path)
+// LONER_B200_MLP=simt forces the fp32 CUDA-core kernels (test builds only)
 static bool use_simt() {
     const char* e = getenv("LONER_B200_MLP");
     return e && strcmp(e, "simt") == 0;
@@ -178,3 +179,22 @@ int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, c
     mlp_bwd_simt_kernel<<<grid_for(plan->sm_count, n_points, 2), kThreads, smem, st>>>(mlp, enc_inout, d_sigma, n_points, grad_mlp);
     return lb_check_cuda(cudaGetLastError(), "mlp_bwd launch");
 }
+#else   // shipped build: tensor cores only
+int lb_launch_mlp_fwd(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
+                      uint64_t* act, cudaStream_t st) {
+    if (!act) {
+        lb_set_error("lb_sigma_fwd: the act [P] ReLU-mask buffer is required (the fp32 CUDA-core MLP is a test-only build option)");
+        return LB_ERR_UNSUPPORTED;
+    }
+    return lb_launch_mlp_fwd_umma(plan, mlp, enc, n_points, sigma, act, st);
+}
+
+int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
+                      const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st) {
+    if (!act) {
+        lb_set_error("lb_sigma_bwd: the act [P] ReLU-mask buffer is required (the fp32 CUDA-core MLP is a test-only build option)");
+        return LB_ERR_UNSUPPORTED;
+    }
+    return lb_launch_mlp_bwd_umma(plan, mlp, enc_inout, d_sigma, act, n_points, grad_mlp, st);
+}
+#endif

@@ -486,13 +486,14 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
-template <bool kInputGrad, int kNDense>
+template <bool kFromRays, bool kInputGrad, int kNDense>
 __global__ void __launch_bounds__(FusedShape<kInputGrad>::kThreads, 1)
 sigma_bwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
-                       const float* __restrict__ mlp, const float2* __restrict__ table, const float* __restrict__ enc,
-                       const float* __restrict__ d_sigma, const unsigned long long* __restrict__ act, size_t n_points,
-                       int n_samples, float* __restrict__ grad_mlp, float* __restrict__ grad_table,
-                       float* __restrict__ d_rays) {
+                       const float* __restrict__ x01, const float* __restrict__ mlp, const float2* __restrict__ table,
+                       const float* __restrict__ enc, const float* __restrict__ d_sigma,
+                       const unsigned long long* __restrict__ act, size_t n_points, int n_samples,
+                       float* __restrict__ grad_mlp, float* __restrict__ grad_table, float* __restrict__ d_rays,
+                       float* __restrict__ d_x01) {
     extern __shared__ __align__(128) uint8_t sm[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t bar_mma = smem_u32(sm + FusedSmem::bars);
@@ -647,7 +648,7 @@ sigma_bwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
             const bool valid = p < n_points;
             lb_enc::Point q = {0.5f, 0.5f, 0.5f};
             float zval = 0.0f;
-            if (valid) q = lb_enc::load_point<true>(rays, zv, nullptr, p, n_samples, &zval);
+            if (valid) q = lb_enc::load_point<kFromRays>(rays, zv, x01, p, n_samples, &zval);
             const uint32_t slot = kt % kRing;
             mbar_wait(bar_full + 8 * slot, (kt / kRing) & 1u);
             float de[LB_MLP_IN];
@@ -661,9 +662,8 @@ sigma_bwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_empty + 8 * slot);        // this unit's rows are in registers
-            lb_enc::encode_bwd_point<true, kInputGrad, kNDense, lb_enc::kAggLevelsFused, lb_enc::kAggMaxRunsFused>(
-                T, q, zval, de, valid, p, n_samples, table, grad_table,
-                                                                d_rays, nullptr, 0, T.n_levels);
+            lb_enc::encode_bwd_point<kFromRays, kInputGrad, kNDense, lb_enc::kAggLevelsFused, lb_enc::kAggMaxRunsFused>(
+                T, q, zval, de, valid, p, n_samples, table, grad_table, d_rays, d_x01, 0, T.n_levels);
         }
     }
     tc_fence_before();
@@ -671,20 +671,20 @@ sigma_bwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
     if (warp == 0) tmem_dealloc(tmem, kTmemCols);
 }
 
-template <bool kInputGrad, int kNDense>
-int launch_fused(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* params,
-                 const float* enc, const uint64_t* act, const float* d_sigma, size_t n_points, int n_samples,
-                 float* grad_params, float* d_rays, cudaStream_t st) {
-    auto kern = sigma_bwd_fused_kernel<kInputGrad, kNDense>;
+template <bool kFromRays, bool kInputGrad, int kNDense>
+int launch_fused(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* x01,
+                 const float* params, const float* enc, const uint64_t* act, const float* d_sigma, size_t n_points,
+                 int n_samples, float* grad_params, float* d_rays, float* d_x01, cudaStream_t st) {
+    auto kern = sigma_bwd_fused_kernel<kFromRays, kInputGrad, kNDense>;
     int rc = lb_check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FusedSmem::total),
                            "sigma_bwd_fused smem opt-in");
     if (rc) return rc;
     const size_t tiles = (n_points + kTile - 1) / kTile;
     const size_t cap = (size_t)plan->sm_count;
     kern<<<(int)(tiles < cap ? tiles : cap), FusedShape<kInputGrad>::kThreads, FusedSmem::total, st>>>(
-        T, rays, z, params, reinterpret_cast<const float2*>(params + LB_MLP_PARAMS), enc, d_sigma,
+        T, rays, z, x01, params, reinterpret_cast<const float2*>(params + LB_MLP_PARAMS), enc, d_sigma,
         reinterpret_cast<const unsigned long long*>(act), n_points, n_samples, grad_params,
-        grad_params ? grad_params + LB_MLP_PARAMS : nullptr, d_rays);
+        grad_params ? grad_params + LB_MLP_PARAMS : nullptr, d_rays, d_x01);
     return lb_check_cuda(cudaGetLastError(), "sigma_bwd_fused launch");
 }
 
@@ -712,11 +712,12 @@ struct FusedFwdSmem {
                               v = w2 + 64 * 4, bars = v + 32 * 4, tmem = bars + 8 * (2 + 2 * kFwdRing), total = tmem + 8;
 };
 
-template <int kNDense>
+template <bool kFromRays, int kNDense>
 __global__ void __launch_bounds__(kFusedFwdThreads, 1)
 sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
-                       const float* __restrict__ mlp, const float2* __restrict__ table, size_t n_points, int n_samples,
-                       float* __restrict__ sigma, float* __restrict__ enc, unsigned long long* __restrict__ act) {
+                       const float* __restrict__ x01, const float* __restrict__ mlp, const float2* __restrict__ table,
+                       size_t n_points, int n_samples, float* __restrict__ sigma, float* __restrict__ enc,
+                       unsigned long long* __restrict__ act) {
     extern __shared__ __align__(128) uint8_t sm[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t bar_mma = smem_u32(sm + FusedFwdSmem::bars);
@@ -844,7 +845,7 @@ sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
             const size_t p = fused_tile(kt) * (size_t)kTile + row;
             const bool valid = p < n_points;
             lb_enc::Point q = {0.5f, 0.5f, 0.5f};
-            if (valid) q = lb_enc::load_point<true>(rays, zv, nullptr, p, n_samples, nullptr);
+            if (valid) q = lb_enc::load_point<kFromRays>(rays, zv, x01, p, n_samples, nullptr);
             float out[16];
             lb_enc::encode_fwd_point<kNDense>(T, q, half, table, 0, 16, out);
             const uint32_t slot = kt % kFwdRing;
@@ -866,19 +867,29 @@ sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
     if (warp == 0) tmem_dealloc(tmem, kFusedFwdTmemCols);
 }
 
-template <int kNDense>
-int launch_fused_fwd(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* params,
-                     size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act, cudaStream_t st) {
-    auto kern = sigma_fwd_fused_kernel<kNDense>;
+template <bool kFromRays, int kNDense>
+int launch_fused_fwd_src(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* x01,
+                         const float* params, size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act,
+                         cudaStream_t st) {
+    auto kern = sigma_fwd_fused_kernel<kFromRays, kNDense>;
     int rc = lb_check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FusedFwdSmem::total),
                            "sigma_fwd_fused smem opt-in");
     if (rc) return rc;
     const size_t tiles = (n_points + kTile - 1) / kTile;
     const size_t cap = (size_t)plan->sm_count;
     kern<<<(int)(tiles < cap ? tiles : cap), kFusedFwdThreads, FusedFwdSmem::total, st>>>(
-        T, rays, z, params, reinterpret_cast<const float2*>(params + LB_MLP_PARAMS), n_points, n_samples, sigma, enc,
+        T, rays, z, x01, params, reinterpret_cast<const float2*>(params + LB_MLP_PARAMS), n_points, n_samples, sigma, enc,
         reinterpret_cast<unsigned long long*>(act));
     return lb_check_cuda(cudaGetLastError(), "sigma_fwd_fused launch");
+}
+
+// point source: (rays, z) -> x = o + d z inside the kernel, or x01 [P,3] as handed to tcnn.NetworkWithInputEncoding
+template <int kNDense>
+int launch_fused_fwd(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* x01,
+                     const float* params, size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act,
+                     cudaStream_t st) {
+    return rays ? launch_fused_fwd_src<true, kNDense>(plan, T, rays, z, nullptr, params, n_points, n_samples, sigma, enc, act, st)
+                : launch_fused_fwd_src<false, kNDense>(plan, T, nullptr, nullptr, x01, params, n_points, 1, sigma, enc, act, st);
 }
 
 int umma_grid(int sm_count, size_t n_points, int ctas_per_sm) {
@@ -891,13 +902,10 @@ int umma_grid(int sm_count, size_t n_points, int ctas_per_sm) {
 
 int lb_launch_mlp_fwd_umma(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
                            uint64_t* act, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_fwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                    (int)FwdSmem::total), "mlp_fwd_umma smem opt-in");
-        if (rc) return rc;
-        attr_set = true;
-    }
+    // per launch: the attribute is per device, and a process may drive several devices
+    int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_fwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                (int)FwdSmem::total), "mlp_fwd_umma smem opt-in");
+    if (rc) return rc;
     mlp_fwd_umma_kernel<<<umma_grid(plan->sm_count, n_points, kFwdCtasPerSm), kThreads, FwdSmem::total, st>>>(
         mlp, enc, n_points, sigma, reinterpret_cast<unsigned long long*>(act));
     return lb_check_cuda(cudaGetLastError(), "mlp_fwd_umma launch");
@@ -905,33 +913,36 @@ int lb_launch_mlp_fwd_umma(const lb_plan* plan, const float* mlp, const float* e
 
 int lb_launch_mlp_bwd_umma(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
                            const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                    (int)BwdSmem::total), "mlp_bwd_umma smem opt-in");
-        if (rc) return rc;
-        attr_set = true;
-    }
+    int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                (int)BwdSmem::total), "mlp_bwd_umma smem opt-in");
+    if (rc) return rc;
     mlp_bwd_umma_kernel<<<umma_grid(plan->sm_count, n_points, kBwdCtasPerSm), kThreads, BwdSmem::total, st>>>(
         mlp, enc_inout, d_sigma, reinterpret_cast<const unsigned long long*>(act), n_points, grad_mlp);
     return lb_check_cuda(cudaGetLastError(), "mlp_bwd_umma launch");
 }
 
-int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* params,
-                              const float* enc, const uint64_t* act, const float* d_sigma, size_t n_points, int n_samples,
-                              float* grad_params, float* d_rays, cudaStream_t st) {
+int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* x01,
+                              const float* params, const float* enc, const uint64_t* act, const float* d_sigma,
+                              size_t n_points, int n_samples, float* grad_params, float* d_rays, float* d_x01,
+                              cudaStream_t st) {
+#ifdef LB_TEST_SWITCHES       // test builds: LONER_B200_FUSED_BWD=0 runs the two-kernel path on configurations the fused kernel covers
     static int disabled = -1;
     if (disabled < 0) {
         const char* e = getenv("LONER_B200_FUSED_BWD");
         disabled = (e && e[0] == '0') ? 1 : 0;
     }
+#else
+    constexpr int disabled = 0;
+#endif
     const int nd = lb_encode_dense_prefix(plan);
-    if (disabled || !rays || !act || nd < 1 || !lb_encode_single_group(plan) || plan->cfg.n_levels != 16) return 1;
+    if (disabled || (!rays && !x01) || !act || nd < 1 || !lb_encode_single_group(plan) || plan->cfg.n_levels != 16) return 1;
     const lb_level_table T = lb_make_level_table(plan);
-#define LB_FUSED_CASE(ND)                                                                                                   \
-    case ND:                                                                                                                \
-        return d_rays ? launch_fused<true, ND>(plan, T, rays, z, params, enc, act, d_sigma, n_points, n_samples, grad_params, d_rays, st) \
-                      : launch_fused<false, ND>(plan, T, rays, z, params, enc, act, d_sigma, n_points, n_samples, grad_params, d_rays, st);
+    const bool in_grad = d_rays || d_x01;
+#define LB_FUSED_ARGS plan, T, rays, z, x01, params, enc, act, d_sigma, n_points, rays ? n_samples : 1, grad_params, d_rays, d_x01, st
+#define LB_FUSED_CASE(ND)                                                                                          \
+    case ND:                                                                                                       \
+        if (rays) return in_grad ? launch_fused<true, true, ND>(LB_FUSED_ARGS) : launch_fused<true, false, ND>(LB_FUSED_ARGS); \
+        return in_grad ? launch_fused<false, true, ND>(LB_FUSED_ARGS) : launch_fused<false, false, ND>(LB_FUSED_ARGS);
     switch (nd) {
         LB_FUSED_CASE(1)
         LB_FUSED_CASE(2)
@@ -940,27 +951,32 @@ int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const floa
         default: return 1;
     }
 #undef LB_FUSED_CASE
+#undef LB_FUSED_ARGS
 }
 
 bool lb_sigma_fwd_fused_covers(const lb_plan* plan) {
+#ifdef LB_TEST_SWITCHES
     static int disabled = -1;
     if (disabled < 0) {
         const char* e = getenv("LONER_B200_FUSED_FWD");
         disabled = (e && e[0] == '0') ? 1 : 0;
     }
+#else
+    constexpr int disabled = 0;
+#endif
     return !disabled && lb_encode_dense_prefix(plan) >= 1 && lb_encode_single_group(plan) && plan->cfg.n_levels == 16;
 }
 
 // returns 1 when the configuration is not covered (the caller then runs the two-kernel path)
-int lb_launch_sigma_fwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* params, size_t n_points,
-                              int n_samples, float* sigma, float* enc, uint64_t* act, cudaStream_t st) {
-    if (!rays || !lb_sigma_fwd_fused_covers(plan)) return 1;
+int lb_launch_sigma_fwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* params,
+                              size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act, cudaStream_t st) {
+    if ((!rays && !x01) || !lb_sigma_fwd_fused_covers(plan)) return 1;
     const lb_level_table T = lb_make_level_table(plan);
     switch (lb_encode_dense_prefix(plan)) {
-        case 1: return launch_fused_fwd<1>(plan, T, rays, z, params, n_points, n_samples, sigma, enc, act, st);
-        case 2: return launch_fused_fwd<2>(plan, T, rays, z, params, n_points, n_samples, sigma, enc, act, st);
-        case 3: return launch_fused_fwd<3>(plan, T, rays, z, params, n_points, n_samples, sigma, enc, act, st);
-        case 4: return launch_fused_fwd<4>(plan, T, rays, z, params, n_points, n_samples, sigma, enc, act, st);
+        case 1: return launch_fused_fwd<1>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, st);
+        case 2: return launch_fused_fwd<2>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, st);
+        case 3: return launch_fused_fwd<3>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, st);
+        case 4: return launch_fused_fwd<4>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, st);
         default: return 1;
     }
 }

@@ -70,6 +70,7 @@ build_rays_kernel(const float* __restrict__ directions, const float* __restrict_
     if (i >= m) return;
     const Pose p = load_pose(rot, origin);
     long long j = indices ? indices[i] : (long long)i;
+    j = j < 0 ? 0 : (j >= n ? (long long)n - 1 : j);       // never read out of bounds (the host wrapper validates)
     if (j < 0) j += n;                                   // torch-style negative index
     const float dx = __ldg(directions + j), dy = __ldg(directions + (size_t)n + j), dz = __ldg(directions + 2 * (size_t)n + j);
     const RayGeom g = ray_geometry(p, dx, dy, dz);
@@ -95,6 +96,8 @@ build_rays_bwd_kernel(const float* __restrict__ directions, const long long* __r
     for (int k = 0; k < 12; ++k) acc[k] = 0.0f;
     for (int i = blockIdx.x * kThreads + threadIdx.x; i < m; i += gridDim.x * kThreads) {
         long long j = indices ? indices[i] : (long long)i;
+        j = j < 0 ? 0 : (j >= n ? (long long)n - 1 : j);
+    j = j < 0 ? 0 : (j >= n ? (long long)n - 1 : j);       // never read out of bounds (the host wrapper validates)
         if (j < 0) j += n;
         const float dir[3] = {__ldg(directions + j), __ldg(directions + (size_t)n + j), __ldg(directions + 2 * (size_t)n + j)};
         const RayGeom g = ray_geometry(p, dir[0], dir[1], dir[2]);
@@ -157,6 +160,7 @@ build_camera_rays_kernel(const float* __restrict__ directions, const float* __re
     if (i >= m) return;
     const Pose p = load_pose(rot, origin);
     long long j = indices ? indices[i] : (long long)i;
+    j = j < 0 ? 0 : (j >= n ? (long long)n - 1 : j);       // never read out of bounds (the host wrapper validates)
     if (j < 0) j += n;
     const float* dir = directions + 3 * (size_t)j;
     const RayGeom g = ray_geometry(p, __ldg(dir), __ldg(dir + 1), __ldg(dir + 2));

@@ -321,7 +321,7 @@ composite_bwd_kernel(const float* __restrict__ sigma, const float* __restrict__ 
 __global__ void __launch_bounds__(kWarps * 32)
 composite_loss_kernel(const float* __restrict__ sigma, const float* __restrict__ zv, const float* __restrict__ rays,
                       const float* __restrict__ noise, const float* __restrict__ depth_gt, lb_loss_config cfg,
-                      const float* __restrict__ n_opaque_dev, int n_rays, int S, float* __restrict__ weights, float* __restrict__ depth,
+                      const float* __restrict__ norm_dev, int n_rays, int S, float* __restrict__ weights, float* __restrict__ depth,
                       float* __restrict__ opacity, float* __restrict__ variance, float* __restrict__ js_out,
                       float* __restrict__ eps_out, float* __restrict__ loss_parts, float* __restrict__ d_sigma,
                       float* __restrict__ d_rays) {
@@ -400,9 +400,13 @@ composite_loss_kernel(const float* __restrict__ sigma, const float* __restrict__
         const float inv_wg = 1.0f / (wg_sum + 1e-6f);
 
         // pass 4 (reverse): line-of-sight term, dL/dw and the chain to sigma, |d|, far
-        const float n_op = n_opaque_dev ? __ldg(n_opaque_dev) : cfg.n_opaque;
+        // global normalisers: {opaque-ray count, ray count} over all chunks and ranks, read from the device so that
+        // neither costs a host round trip (lb_count_opaque + one all-reduce)
+        const float n_op = norm_dev ? __ldg(norm_dev) : cfg.n_opaque;
+        const float n_all = norm_dev ? __ldg(norm_dev + 1) : 0.0f;
+        const float n_total = n_all > 0.0f ? n_all * (float)S : cfg.n_total_samples;
         const float inv_nop = (opaque && n_op > 0.0f) ? 1.0f / n_op : 0.0f;
-        const float c_los = cfg.los_lambda / cfg.n_total_samples;
+        const float c_los = cfg.los_lambda / n_total;
         const float derr = sc * D - g;
         const float gD = inv_nop * 2.0f * cfg.depthloss_lambda * sc * derr;     // dL/dD
         const float gA = inv_nop * sgn(A - 1.0f);                                 // dL/dA
@@ -461,6 +465,7 @@ __global__ void count_opaque_kernel(const float* __restrict__ rays, const float*
     }
     const unsigned m = __ballot_sync(0xffffffffu, op);
     if ((threadIdx.x & 31) == 0 && m) atomicAdd(count, (float)__popc(m));
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(count + 1, (float)n_rays);
 }
 
 }  // namespace
@@ -503,7 +508,7 @@ extern "C" int lb_composite_bwd(const float* sigma, const float* z, const float*
 }
 
 extern "C" int lb_composite_loss(const float* sigma, const float* z, const float* rays, const float* noise,
-                                 const float* depth_gt, const lb_loss_config* cfg, const float* n_opaque_dev,
+                                 const float* depth_gt, const lb_loss_config* cfg, const float* norm_dev,
                                  int n_rays, int n_samples,
                                  float* weights, float* depth, float* opacity, float* variance, float* js,
                                  float* eps, float* loss_parts, float* d_sigma, float* d_rays, void* stream) {
@@ -515,9 +520,9 @@ extern "C" int lb_composite_loss(const float* sigma, const float* z, const float
     if (n_rays == 0) return LB_OK;
     lb_loss_config c = *cfg;
     if (!(c.n_total_samples > 0.0f)) c.n_total_samples = (float)n_rays * (float)n_samples;
-    LB_REQUIRE(n_opaque_dev || c.n_opaque >= 0.0f, "n_opaque must be supplied (lb_count_opaque) and non-negative");
+    LB_REQUIRE(norm_dev || c.n_opaque >= 0.0f, "n_opaque must be supplied (lb_count_opaque) and non-negative");
     composite_loss_kernel<<<(n_rays + kWarps - 1) / kWarps, kWarps * 32, 0, (cudaStream_t)stream>>>(
-        sigma, z, rays, noise, depth_gt, c, n_opaque_dev, n_rays, n_samples, weights, depth, opacity, variance, js, eps,
+        sigma, z, rays, noise, depth_gt, c, norm_dev, n_rays, n_samples, weights, depth, opacity, variance, js, eps,
         loss_parts, d_sigma, d_rays);
     LB_LAUNCH_CHECK("lb_composite_loss");
     return LB_OK;

@@ -40,6 +40,16 @@ class BuildLidarRays(torch.autograd.Function):
         return d_rot, d_org, None, None, None, None, None, None, None
 
 
+def _consume(ctx):
+    """The saved encodings may be overwritten in place with dL/d_enc by the backward kernels (two-kernel path) and a
+    GradSink hands its buffer over exactly once: a second backward through the same node (retain_graph=True) would
+    silently return wrong gradients, so it raises instead -- run the forward again."""
+    if getattr(ctx, "_lb_consumed", False):
+        raise RuntimeError("loner_b200: backward through a sigma-field node a second time: its saved encodings were "
+                           "consumed by the first backward (retain_graph is not supported here; re-run the forward)")
+    ctx._lb_consumed = True
+
+
 class GradSink:
     """Shared by the SigmaFromRays nodes of one chunked forward pass whose outputs ALL feed the loss
     (Optimizer.compute_loss): the chunks' backward kernels accumulate into one parameter-gradient buffer and the
@@ -67,6 +77,7 @@ class SigmaFromRays(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, d_sigma):
+        _consume(ctx)
         params, rays, z, enc, act = ctx.saved_tensors
         need_p, need_r = ctx.need
         sink = ctx.sink
@@ -102,6 +113,7 @@ class SigmaFromPoints(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, d_sigma):
+        _consume(ctx)
         params, x01, enc, act = ctx.saved_tensors
         need_p, need_x = ctx.need
         gp = torch.zeros_like(params) if need_p else None
@@ -166,8 +178,8 @@ class RenderLoss(torch.autograd.Function):
         want_grad = sigma.requires_grad or rays.requires_grad
         out = ops.composite_loss(s_c, z_c, r_c, n_c, depth_gt.contiguous(), cfg, parts, want_grad=want_grad,
                                  n_opaque_dev=n_opaque_dev)
-        lam_d, lam_los, n_total = weights_lambda
-        n_op = n_opaque_dev[0]                      # device scalar: no host sync
+        lam_d, lam_los = weights_lambda
+        n_op, n_total = n_opaque_dev[0], n_opaque_dev[1] * z.shape[1]      # device scalars: no host sync
         loss = lam_d * parts[0] / n_op + lam_los * parts[1] / n_total + parts[2] / n_op
         ctx.save_for_backward(out["d_sigma"], out["d_rays"])
         ctx.need_rays = rays.requires_grad

@@ -270,21 +270,46 @@ class _ChunkedResults(dict):
 
 
 class RayDataParallel:
-    """Ray data-parallel context: rays shard over ranks, parameters are replicated, and
-    one NCCL all-reduce(SUM) per iteration carries {sigma-head gradient, pose gradients}; the global
-    opaque-ray count is a 4-byte all-reduce before the loss kernel.  world_size 1 is a no-op."""
+    """Ray data-parallel context: rays shard over ranks, parameters are replicated.  Per iteration:
+    one 8-byte all-reduce of the loss normalisers {opaque-ray count, ray count} before the loss kernel, the gradient
+    exchange inside FusedAdam.step (reduce-scatter -> Adam on this rank's 1/W of the flat parameter vector ->
+    all-gather of the updated parameters; pose 6-vectors: all-reduce), and the 4 MB occupancy gradient every 10th step.
+    world_size 1 is a no-op.
 
-    def __init__(self, group=None):
+    shard_batch=False (weak scaling): every rank brings its own ray batch.
+    shard_batch=True  (strong scaling / N-GPU == 1-GPU equivalence): every rank is handed the SAME global batch and
+    processes rows [rank * n / W, (rank + 1) * n / W) of every chunk; the chunk's random tensors are drawn for the whole
+    chunk from the (identically seeded) generator and sliced, so the union over ranks reproduces the 1-GPU step."""
+
+    def __init__(self, group=None, shard_batch=False):
         import torch.distributed as dist
         self.dist = dist
         self.group = group
         self.enabled = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
         self.world_size = dist.get_world_size(group) if self.enabled else 1
         self.rank = dist.get_rank(group) if self.enabled else 0
+        self.shard_batch = bool(shard_batch) and self.enabled
+        self.events = None              # bench.py: list of (name, start, end) CUDA events around the collectives
 
-    def all_reduce_(self, t):
+    def rows(self, n):
+        """Row range of this rank inside an n-row chunk (shard_batch)."""
+        per = (n + self.world_size - 1) // self.world_size
+        lo = min(self.rank * per, n)
+        return lo, min(lo + per, n)
+
+    def _timed(self, name, fn):
+        if self.events is None:
+            return fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        r = fn()
+        e1.record()
+        self.events.append((name, e0, e1))
+        return r
+
+    def all_reduce_(self, t, name="all_reduce"):
         if self.enabled:
-            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+            self._timed(name, lambda: self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group))
         return t
 
     def all_reduce_grads(self, params):
@@ -292,7 +317,15 @@ class RayDataParallel:
             return
         for p in params:
             if p.grad is not None:
-                self.dist.all_reduce(p.grad, op=self.dist.ReduceOp.SUM, group=self.group)
+                self.all_reduce_(p.grad, "all_reduce_grad")
+
+    def reduce_scatter(self, out, flat):
+        self._timed("reduce_scatter_grad", lambda: self.dist.reduce_scatter_tensor(out, flat, op=self.dist.ReduceOp.SUM, group=self.group))
+
+    def all_gather(self, flat, shard):
+        # NCCL gathers in place (shard is the rank's slice of flat); other backends (gloo, CPU tests) get a copy
+        src = shard if flat.is_cuda else shard.clone()
+        self._timed("all_gather_params", lambda: self.dist.all_gather_into_tensor(flat, src, group=self.group))
 
 
 class Optimizer:
@@ -386,32 +419,56 @@ class Optimizer:
             fixed_eps = L.depth_eps
         los_lambda = self._los_lambda()
         rays_d = rays.detach().contiguous()
-        # global normalisers: opaque-ray count and N*S over all ranks
-        n_op = self._dp.all_reduce_(ops.count_opaque(rays_d, depths))
-        n_total = float(n_rays * S * self._dp.world_size)
-        cfg = ops.make_loss_config(sel, self._scale_float, 0.0, n_total, L.JS_loss.min_js_score, L.JS_loss.max_js_score,
+        dp = self._dp
+        # global normalisers {opaque-ray count, ray count}, kept on the device: with a sharded global batch
+        # every rank counts the whole batch itself; with per-rank batches (whose sizes may differ once the world-cube
+        # filter has dropped rays) the two counts are summed over the ranks
+        norm = ops.count_opaque(rays_d, depths)
+        if not dp.shard_batch:
+            dp.all_reduce_(norm, "all_reduce_norm")
+        cfg = ops.make_loss_config(sel, self._scale_float, 0.0, float(n_rays * S), L.JS_loss.min_js_score, L.JS_loss.max_js_score,
                                    L.JS_loss.alpha, L.min_depth_eps, fixed_eps, los_lambda, L.depthloss_lambda)
         nerf = self._model.nerf_model
-        loss, outs = 0, []
+        loss, outs, kept = 0, [], []
         sink = GradSink() if n_rays > render.chunk else None       # every chunk's loss is summed below
         for i in range(0, n_rays, render.chunk):
             r_c, d_c = rays[i:i + render.chunk], depths[i:i + render.chunk]
-            z = self._ray_sampler.get_samples(r_c, S, render.perturb)
-            sigma = nerf.sigma_from_rays(r_c, z, sink)
+            rows = dp.rows(r_c.shape[0]) if dp.shard_batch else None
+            # `rows` only reaches the product's samplers (a duck-typed reference sampler keeps the 3-argument call)
+            z = self._ray_sampler.get_samples(r_c, S, render.perturb, **({} if rows is None else {"rows": rows}))
             noise = None
             if render.raw_noise_std > 0:
-                noise = torch.randn(z.shape, device=z.device)
+                noise = torch.randn((r_c.shape[0], S), device=z.device)
                 if render.raw_noise_std != 1.0:
                     noise = noise * render.raw_noise_std
+            if rows is not None:           # this rank's rows of the chunk (the draws above covered the whole chunk)
+                r_c, d_c = r_c[rows[0]:rows[1]], d_c[rows[0]:rows[1]]
+                noise = noise[rows[0]:rows[1]].contiguous() if noise is not None else None
+                kept.append((i + rows[0], i + rows[1]))
+                if r_c.shape[0] == 0:
+                    continue
+            sigma = nerf.sigma_from_rays(r_c, z, sink)
             l_c, w, depth, opac, var, js, eps = RenderLoss.apply(
-                sigma, z, r_c, noise, d_c, cfg, n_op, (L.depthloss_lambda, los_lambda, n_total))
+                sigma, z, r_c, noise, d_c, cfg, norm, (L.depthloss_lambda, los_lambda))
             loss = loss + l_c
             outs.append((z, w, depth, opac, var, js, eps))
+        if dp.shard_batch:                 # side-effect state below refers to this rank's rows only
+            idx = torch.cat([torch.arange(a, b, device=rays.device) for a, b in kept]) if kept else torch.zeros(0, dtype=torch.long, device=rays.device)
+            rays_d, depths = rays_d[idx].contiguous(), depths[idx].contiguous()
         # side effects the occupancy step and callers rely on (reference optimizer.py:730-736); the per-chunk pieces
         # are concatenated when a key is first read (the occupancy step reads them every 10th iteration only)
         self._results_lidar = _ChunkedResults(outs, {'samples_fine': 0, 'weights_fine': 1, 'depth_fine': 2, 'opacity_fine': 3,
                                                      'variance': 4, 'js_score': 5, 'depth_eps': 6}, rays=rays_d)
         self._lidar_depths_gt_cube = depths
+        if self._settings.debug.store_ray:
+            # reference optimizer.py:855-858: (loss, std_out, js_score_out) -- the std of the depth distribution about its
+            # weighted mean in metres (:737-741) and the CLAMPED js score (js_score_out aliases the tensor that :763-765
+            # clamp in place).  Debug path: the std is re-derived here with the reference's own torch expressions.
+            res = self._results_lidar
+            zm, w = res['samples_fine'] * self._scale_float, res['weights_fine']
+            mean = torch.sum(zm * w, axis=1) / (torch.sum(w, axis=1) + 1e-10)
+            var = torch.sum((zm - mean.unsqueeze(-1)) ** 2 * w, axis=1) / (torch.sum(w, axis=1) + 1e-10) + 1e-10
+            return loss, torch.sqrt(var).detach(), res['js_score'].detach()
         return loss
 
     def compute_loss_camera(self, camera_samples, lidar_samples, iteration_idx, override_enables=False, tracking=False):
@@ -478,6 +535,10 @@ class Optimizer:
         max_len = max(lengths)
         full = torch.zeros((len(keyframes), max_len), dtype=torch.int64, device=self._device)
         for k, n in enumerate(lengths):
+            if max_len - n > n:
+                # the reference pads with randperm(max_len - n), whose values index the scan: with a scan shorter than
+                # half the longest one it raises IndexError when the rays are built (optimizer.py:283-290)
+                raise IndexError(f"FIXED ray selection: scan {k} ({n} rays) is shorter than half the longest scan ({max_len})")
             full[k] = torch.cat((torch.randperm(n, device=self._device), torch.randperm(max_len - n, device=self._device)))
         return full, int(max_len // self._num_lidar_samples)
 
@@ -500,7 +561,13 @@ class Optimizer:
 
     def build_batch(self, keyframes, ignore_world_cube=False, fixed=None):
         """One iteration's ray batch: per keyframe index draw + ray construction (optimizer.py:363-424).
-        fixed = (full_indices, it_idx, num_iterations) selects the FIXED-strategy slice (optimizer.py:302-308)."""
+        fixed = (full_indices, it_idx, num_iterations) selects the FIXED-strategy slice (optimizer.py:302-308).
+
+        The reference drops, per keyframe, rays that leave the world cube within one metre of `near`
+        (ray_utils.py:321-322: a boolean-mask gather, i.e. a host sync per keyframe and sky set).  The world cube is
+        built to contain every ray (pose_utils.py:222-314), so the filter practically never fires: the rays of the whole
+        window are built unfiltered, ONE device flag says whether any ray is short, and only then is the mask applied
+        (to the concatenated batch, which keeps the reference's order).  One 1-byte read-back per iteration."""
         rays, depths = [], []
         # one batched pose -> (R, origin) evaluation for the whole window (autograd reaches every pose leaf)
         pose_tensors = [(kf._gt_pose if self._use_gt_poses else kf._pose).get_pose_tensor() for kf in keyframes]
@@ -513,11 +580,16 @@ class Optimizer:
                 lo, hi = max(int(nr * it_idx - 1), 0), min(int(nr * (it_idx + 1) - 1), int(n_it * nr))
                 idx = full[k, lo:hi]
             r, d = kf.build_lidar_rays(idx, self._ray_range, self._world_cube, self._use_gt_poses,
-                                       ignore_world_cube=ignore_world_cube, sky_indices=sky_idx,
-                                       rot_origin=(R[k], o[k]))
+                                       ignore_world_cube=True, sky_indices=sky_idx, rot_origin=(R[k], o[k]))
             rays.append(r)
             depths.append(d)
-        return torch.vstack(rays), torch.cat(depths)
+        rays, depths = torch.vstack(rays), torch.cat(depths)
+        if not ignore_world_cube:
+            s_host = self._world_cube.scale_host
+            valid = rays.detach()[:, 12] > (self._ray_range[0] / s_host + 1. / s_host)
+            if not bool(valid.all()):
+                rays, depths = rays[valid], depths[valid]
+        return rays, depths
 
     def iterate_optimizer(self, keyframe_window: List[KeyFrame], optimizer_settings: OptimizationSettings = None):
         """reference optimizer.py:143-190: pick the iteration schedule for this keyframe count and run it."""
@@ -531,7 +603,21 @@ class Optimizer:
                 break
         if schedule is None:
             raise LonerB200Error("keyframe_schedule has no entry for this keyframe")
+        log_dir = self._settings.get("log_directory")
+        if log_dir:
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
         result = self._do_iterate_optimizer(keyframe_window, schedule, optimizer_settings)
+        if log_dir:
+            # reference optimizer.py:178-188: one "num_its,elapsed_seconds" line per keyframe in timing.csv -- the file its
+            # own its/s figure is read from.  The elapsed time is DEVICE time between two CUDA events (the reference
+            # brackets asynchronous launches with time.time()); num_its counts the iterations actually run.
+            import os
+            t1.record()
+            t1.synchronize()
+            os.makedirs(log_dir, exist_ok=True)
+            with open(os.path.join(log_dir, "timing.csv"), "a+") as f:
+                f.write(f"{self._last_num_iterations},{t0.elapsed_time(t1) * 1e-3}\n")
         self._keyframe_count += 1
         return result
 
@@ -605,7 +691,7 @@ class Optimizer:
             self._model.freeze_sigma_head(True)
             self._model.freeze_rgb_head(False)
             params = self._model.get_rgb_parameters()
-            self._optimizer = FusedAdam([{'params': params, 'lr': train.lrate_rgb}])
+            self._optimizer = FusedAdam([{'params': params, 'lr': train.lrate_rgb}], data_parallel=self._dp)
             gamma = train.lrate_gamma
             full, n_it = self._camera_schedule(keyframe_window, len(cam))
             s.num_iterations = n_it
@@ -613,9 +699,8 @@ class Optimizer:
                 samples = self.build_camera_batch(keyframe_window, cam, full, it_idx, n_it)
                 loss = self.compute_loss_camera(samples, None, it_idx, tracking=False)
                 loss.backward()
-                self._dp.all_reduce_grads(params)
                 self._global_step += 1
-                self._optimizer.step()
+                self._optimizer.step()              # includes the gradient exchange when data-parallel
                 if gamma != 1.0:
                     for g in self._optimizer.param_groups:
                         g['lr'] *= gamma
@@ -636,6 +721,8 @@ class Optimizer:
         if optimizer_settings is not None:
             iteration_schedule = [None]
         train = self._model_config.train
+        self._last_num_iterations = 0
+        self.debug_rays = None
         for it_cfg in iteration_schedule:
             if optimizer_settings is None:
                 s = self._optimization_settings
@@ -665,20 +752,26 @@ class Optimizer:
                 groups.append({'params': self._model.get_sigma_parameters(), 'lr': train.lrate_sigma_mlp})
             if (tracking or optimize_poses) and poses:
                 groups.append({'params': poses, 'lr': train.lrate_pose})
-            self._optimizer = FusedAdam(groups)
+            self._optimizer = FusedAdam(groups, data_parallel=self._dp)
             gamma = train.lrate_gamma
-            all_params = [p for g in groups for p in g['params']]
             fixed_full = None
             if self._settings.rays_selection.strategy == 'FIXED':
                 fixed_full, s.num_iterations = self._fixed_schedule(active)
             for it_idx in range(s.num_iterations):
                 rays, depths = self.build_batch(active, fixed=None if fixed_full is None else (fixed_full, it_idx, s.num_iterations))
                 loss = self.compute_loss(None, (rays, depths), it_idx, tracking=tracking)
+                self._last_num_iterations += 1
+                if self._settings.debug.store_ray:
+                    # reference optimizer.py:426-433, 479-489: per-iteration (rays, depths, std, js) kept for inspection
+                    loss, std, js = loss
+                    acc = self.debug_rays or dict(rays=[], depths=[], std=[], js=[])
+                    for k, v in (("rays", rays.detach()), ("depths", depths), ("std", std), ("js", js)):
+                        acc[k].append(v)
+                    self.debug_rays = acc
                 if self._settings.debug.log_losses:
                     self.losses_log.append(float(loss.detach()))
                 loss.backward()
-                self._dp.all_reduce_grads(all_params)
-                self._optimizer.step()
+                self._optimizer.step()              # includes the gradient exchange when data-parallel
                 if gamma != 1.0:
                     for g in self._optimizer.param_groups:
                         g['lr'] *= gamma

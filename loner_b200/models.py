@@ -96,9 +96,14 @@ class UniformRaySampler:
     def __init__(self):
         pass
 
-    def get_samples(self, rays, N_samples, perturb):
+    def get_samples(self, rays, N_samples, perturb, rows=None):
+        """rows = (lo, hi): the random draw covers all of `rays` (same generator consumption as a single-GPU run),
+        the depths are produced for rays[lo:hi] only (RayDataParallel.shard_batch)."""
         r = rays.detach().contiguous()
         u = torch.rand((r.shape[0], N_samples), device=r.device) if perturb > 0 else None
+        if rows is not None:
+            r = r[rows[0]:rows[1]].contiguous()
+            u = u[rows[0]:rows[1]].contiguous() if u is not None else None
         return ops.sample_uniform(r, u, N_samples, perturb)
 
 
@@ -111,11 +116,16 @@ class OccGridRaySampler:
     def update_occ_grid(self, occ_gamma):
         self._occ_gamma = occ_gamma
 
-    def get_samples(self, rays, N_samples, perturb, debug=False):
+    def get_samples(self, rays, N_samples, perturb, debug=False, rows=None):
+        """rows = (lo, hi): see UniformRaySampler.get_samples."""
         r = rays.detach().contiguous()
         s2 = N_samples // 2
         u1 = torch.rand((r.shape[0], s2), device=r.device) if perturb > 0 else None   # ray_sampling.py:71-72
         u2 = torch.rand(r.shape[0], s2, device=r.device)                                # rendering_tcnn.py:49
+        if rows is not None:
+            r = r[rows[0]:rows[1]].contiguous()
+            u1 = u1[rows[0]:rows[1]].contiguous() if u1 is not None else None
+            u2 = u2[rows[0]:rows[1]].contiguous()
         return ops.sample_occ(r, self._occ_gamma.detach().contiguous(), u1, u2, N_samples, perturb, debug=debug)
 
 

@@ -35,11 +35,13 @@ class Plan:
     (reference cfg/nerf_config/default_nerf_hash.yaml:14-31)."""
 
     def __init__(self, n_levels=16, n_features_per_level=2, log2_hashmap_size=18, base_resolution=16,
-                 per_level_scale=2.0, mlp_width=64, mlp_hidden_layers=1):
+                 per_level_scale=2.0, mlp_width=64, mlp_hidden_layers=1, l2_bytes=None):
         self.cfg = GridConfig(n_levels, n_features_per_level, log2_hashmap_size, base_resolution,
                               per_level_scale, mlp_width, mlp_hidden_layers)
         self._h = C.c_void_p()
         _lib.call("lb_plan_create", C.byref(self.cfg), C.byref(self._h))
+        if l2_bytes is not None:       # level-group budget override (tests force group passes on small tables)
+            _lib.call("lb_plan_set_l2_bytes", self._h, int(l2_bytes))
         a, b = C.c_int64(), C.c_int64()
         _lib.call("lb_plan_param_counts", self._h, C.byref(a), C.byref(b))
         self.n_mlp_params, self.n_table_params = a.value, b.value
@@ -173,10 +175,13 @@ def sigma_fwd(plan, params, rays=None, z=None, x01=None, save_enc=True, tensor_c
     else:
         n, s = x01.shape[0], 1
         shape = (n,)
+    if not tensor_cores and not _lib.test_switches():
+        raise LonerB200Error("sigma_fwd(tensor_cores=False): the fp32 CUDA-core MLP exists only in a test build "
+                             "(python -m loner_b200.build --test-switches)")
     sigma = torch.empty(shape, device=params.device, dtype=torch.float32)
     # the encodings are the encode -> MLP hand-off of the two-kernel path; the fused gather + MLP kernel needs
     # neither buffer when nothing is kept for lb_sigma_bwd
-    inference = (not save_enc) and rays is not None and tensor_cores and plan.enc_optional
+    inference = (not save_enc) and tensor_cores and plan.enc_optional
     enc = None if inference else torch.empty(n * s, plan.n_enc, device=params.device, dtype=torch.float32)
     act = torch.empty(n * s, device=params.device, dtype=torch.int64) if (tensor_cores and not inference) else None
     _lib.call("lb_sigma_fwd", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
@@ -223,7 +228,8 @@ def composite_bwd(sigma, z, rays, noise, g_w, g_depth, g_opacity, g_variance, d_
 
 
 def count_opaque(rays, depth_gt):
-    c = torch.zeros(1, device=rays.device, dtype=torch.float32)
+    """-> device float[2] = {opaque rays, rays} of this batch: the global loss normalisers once summed over ranks."""
+    c = torch.zeros(2, device=rays.device, dtype=torch.float32)
     _lib.call("lb_count_opaque", _p(rays, name="rays"), _p(depth_gt, name="depth_gt"), rays.shape[0], _p(c), _stream())
     return c
 
@@ -236,8 +242,11 @@ def make_loss_config(kind, scale_factor, n_opaque, n_total_samples, min_js_score
 
 
 def composite_loss(sigma, z, rays, noise, depth_gt, cfg, loss_parts, want_grad=True, n_opaque_dev=None):
-    """Fused compositing + loss (+ analytic gradient). loss_parts [4] is accumulated into.
+    """Fused compositing + loss (+ analytic gradient). loss_parts [4] is accumulated into.  n_opaque_dev = device
+    float[2] {opaque-ray count, ray count} from count_opaque (global normalisers), or None to use cfg's.
     Returns dict(weights, depth, opacity, variance, js, eps, d_sigma, d_rays)."""
+    if n_opaque_dev is not None and n_opaque_dev.numel() != 2:
+        raise LonerB200Error("composite_loss: the normaliser tensor must hold {n_opaque, n_rays} (ops.count_opaque)")
     n, s = z.shape
     dev = z.device
     f = lambda *shape: torch.empty(*shape, device=dev, dtype=torch.float32)

@@ -5,6 +5,13 @@
 every phase, src/mapping/optimizer.py:255-265) but runs one lb_adam_step kernel per CUDA parameter
 (p, g, m, v streamed once).  Tiny CPU/GPU tensors that are not 16-byte-aligned fp32 CUDA buffers
 (the pose 6-vectors) are stepped with the same formula in torch.
+
+Ray data parallelism (`data_parallel=` a loner_b200.mapping.RayDataParallel): the gradient exchange is
+part of the step.  A flat parameter vector whose length divides by 4 * world_size is handled ZeRO-1 style:
+    reduce-scatter(grad) -> Adam on this rank's 1/W slice (moments exist for the slice only) -> all-gather(params)
+which moves the same bytes over NVLink as an all-reduce but cuts the optimiser's HBM traffic and moment memory by W
+(T = 2^22: 2.95 GB of Adam traffic and 844 MB of moments per step and rank otherwise).  Everything else (pose 6-vectors)
+is all-reduced and stepped in full on every rank.  The update of an element is the same arithmetic in either layout.
 """
 import math
 
@@ -14,34 +21,65 @@ from . import ops
 
 
 class FusedAdam(torch.optim.Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, data_parallel=None):
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+        self._dp = data_parallel if (data_parallel is not None and data_parallel.enabled) else None
+
+    @staticmethod
+    def _fast(p, g):
+        return p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous() \
+            and p.data_ptr() % 16 == 0 and g.data_ptr() % 16 == 0 and p.numel() >= 1024
+
+    @staticmethod
+    def _update(p, g, m, v, step, lr, b1, b2, eps, grad_scale):
+        """One Adam update of the flat views p, g, m, v (same length), in place on p, m, v."""
+        if FusedAdam._fast(p, g):
+            ops.adam_step(p, g, m, v, step, lr, b1, b2, eps, grad_scale=grad_scale)
+            return
+        if grad_scale != 1.0:
+            g = g * grad_scale
+        m.mul_(b1).add_(g, alpha=1 - b1)
+        v.mul_(b2).addcmul_(g, g, value=1 - b2)
+        bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step
+        denom = (v.sqrt() / math.sqrt(bc2)).add_(eps)
+        p.addcdiv_(m, denom, value=-lr / bc1)
 
     @torch.no_grad()
     def step(self, closure=None, grad_scale=1.0):
+        dp = self._dp
         for group in self.param_groups:
             b1, b2 = group["betas"]
             for p in group["params"]:
                 if p.grad is None:
                     continue
                 st = self.state[p]
+                g = p.grad
+                n = p.numel()
+                sharded = dp is not None and n >= 4096 and n % (4 * dp.world_size) == 0 and p.is_contiguous() and g.is_contiguous()
                 if not st:
                     st["step"] = 0
-                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
-                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                    if sharded:
+                        k = n // dp.world_size
+                        st["exp_avg"] = torch.zeros(k, device=p.device, dtype=p.dtype)
+                        st["exp_avg_sq"] = torch.zeros(k, device=p.device, dtype=p.dtype)
+                        st["grad_shard"] = torch.empty(k, device=p.device, dtype=p.dtype)
+                    else:
+                        st["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                        st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
                 st["step"] += 1
-                g = p.grad
-                if p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous() \
-                        and p.data_ptr() % 16 == 0 and g.data_ptr() % 16 == 0 and p.numel() >= 1024:
-                    ops.adam_step(p.data.view(-1), g.view(-1), st["exp_avg"].view(-1), st["exp_avg_sq"].view(-1),
-                                  st["step"], group["lr"], b1, b2, group["eps"], grad_scale=grad_scale)
+                args = (st["step"], group["lr"], b1, b2, group["eps"], grad_scale)
+                if sharded:
+                    k = n // dp.world_size
+                    flat = p.data.view(-1)
+                    mine = flat[dp.rank * k:(dp.rank + 1) * k]
+                    dp.reduce_scatter(st["grad_shard"], g.view(-1))
+                    self._update(mine, st["grad_shard"], st["exp_avg"], st["exp_avg_sq"], *args)
+                    dp.all_gather(flat, mine)
+                    continue
+                if dp is not None:
+                    dp.all_reduce_(g, "all_reduce_grad")
+                if self._fast(p, g):
+                    self._update(p.data.view(-1), g.view(-1), st["exp_avg"].view(-1), st["exp_avg_sq"].view(-1), *args)
                 else:
-                    if grad_scale != 1.0:
-                        g = g * grad_scale
-                    m, v = st["exp_avg"], st["exp_avg_sq"]
-                    m.mul_(b1).add_(g, alpha=1 - b1)
-                    v.mul_(b2).addcmul_(g, g, value=1 - b2)
-                    bc1, bc2 = 1 - b1 ** st["step"], 1 - b2 ** st["step"]
-                    denom = (v.sqrt() / math.sqrt(bc2)).add_(group["eps"])
-                    p.addcdiv_(m, denom, value=-group["lr"] / bc1)
+                    self._update(p, g, st["exp_avg"], st["exp_avg_sq"], *args)
         return None

@@ -1,0 +1,42 @@
+"""On-hardware N-GPU == 1-GPU equivalence.  Needs >= 2 GPUs: skipped on a
+single-GPU box (run with `gpurun --gpus 2 -- python -m pytest tests/test_dp_nccl_gpu.py`)."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("world", [2])
+def test_sharded_batch_step_equals_single_gpu_step(world):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "dp_equivalence_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("DP_EQUIVALENCE ")][-1]
+    rep = json.loads(line[len("DP_EQUIVALENCE "):])
+    print(rep)
+    assert rep["z_equal"] and rep["params_identical_across_ranks"]
+    assert rep["depth_equal"] < 1e-6
+    assert rep["loss_vs_single"] < 1e-5
+    assert rep["grad_vs_single"] < 1e-5
+    assert rep["rays_grad_vs_single"] < 1e-5
+    assert rep["params_after_adam_vs_single"] < 1e-4
+    assert rep["occ_after_update_vs_single"] < 1e-5
+    # and the reference's own run of this batch (oracle tolerance 1e-3)
+    assert rep["loss_vs_reference"] < 1e-4
+    assert rep["mlp_grad_vs_reference"] < 1e-3
+    assert rep["table_grad_vs_reference"] < 1e-3

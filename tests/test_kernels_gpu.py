@@ -131,9 +131,16 @@ def test_encode_bwd_skips_zero_rows(dev, ops, O):
     assert rel_err(gt2, tr.grad) < 1e-4
 
 
+def _need_test_build(tc):
+    from loner_b200 import _lib
+    if not tc and not _lib.test_switches():
+        pytest.skip("fp32 CUDA-core MLP cross-check: test build only (python -m loner_b200.build --test-switches)")
+
+
 @pytest.mark.parametrize("tc", [True, False], ids=["tcgen05", "simt"])
 @pytest.mark.parametrize("name", ALL_CASES)
 def test_sigma_fwd_bwd_golden(name, tc, dev, ops, O):
+    _need_test_build(tc)
     g = load_golden(name)
     p = golden_params(g)
     plan = ops.Plan(log2_hashmap_size=g["log2_T"])
@@ -227,7 +234,8 @@ def test_mlp_tensor_cores_match_fp32(P, dev, ops, O):
     ref = O.sigma_mlp(O.hash_encode(xr, pr[3072:], log2T), pr[:3072])
     ref.backward(ds)
     out = {}
-    for tc in (True, False):
+    from loner_b200 import _lib
+    for tc in ((True, False) if _lib.test_switches() else (True,)):
         sigma, saved = ops.sigma_fwd(plan, p.to(dev), x01=x.to(dev), tensor_cores=tc)
         gp = torch.zeros_like(p, device=dev)
         dx = ops.sigma_bwd(plan, p.to(dev), saved, ds.to(dev), x01=x.to(dev), grad_params=gp, need_dx=True)
@@ -238,7 +246,8 @@ def test_mlp_tensor_cores_match_fp32(P, dev, ops, O):
         assert (gp[2112:3072] == 0).all()
         assert rel_err(gp[3072:], pr.grad[3072:]) < 1e-4, tc
         assert rel_err(dx, xr.grad) < 1e-3, tc
-    assert rel_err(out[True][0], out[False][0]) < 2e-5
+    if False in out:
+        assert rel_err(out[True][0], out[False][0]) < 2e-5
 
 
 # ------------------------------------------------------------------------------------------ compositing
@@ -287,8 +296,8 @@ def test_composite_loss_golden(name, dev, ops, O):
     rays, z, sig, noise, dgt = (g[k].to(dev) for k in ("rays", "z", "sigma", "noise", "depths"))
     n_op = ops.count_opaque(rays, dgt)
     far = g["rays"][:, -1]
-    assert n_op.item() == float(((g["depths"] > 0) & ~(g["depths"] > far)).sum())
-    cfg = ops.make_loss_config(g["loss_selection"], float(g["scale"]), n_op.item(), z.numel(), min_js_score=g["min_js"])
+    assert n_op.tolist() == [float(((g["depths"] > 0) & ~(g["depths"] > far)).sum()), float(rays.shape[0])]
+    cfg = ops.make_loss_config(g["loss_selection"], float(g["scale"]), n_op[0].item(), z.numel(), min_js_score=g["min_js"])
     parts = torch.zeros(4, device=dev)
     out = ops.composite_loss(sig, z, rays, noise, dgt, cfg, parts)
     pc = parts.cpu()
@@ -465,9 +474,7 @@ def test_level_group_passes_match_single_pass(monkeypatch):
     torch.manual_seed(11)
     N, S, T = 96, 64, 15
     plan1 = ops.Plan(log2_hashmap_size=T)
-    monkeypatch.setenv("LONER_B200_L2_BYTES", str(700 * 1024))     # ~385 KB budget: groups of 2 hashed levels
-    planN = ops.Plan(log2_hashmap_size=T)
-    monkeypatch.delenv("LONER_B200_L2_BYTES")
+    planN = ops.Plan(log2_hashmap_size=T, l2_bytes=700 * 1024)     # ~385 KB budget: groups of 2 hashed levels
     params = torch.cat([(torch.rand(3072) - 0.5) * 0.5, (torch.rand(plan1.n_table_params) - 0.5) * 0.4]).to(dev)
     rays = torch.zeros(N, 13, device=dev)
     rays[:, 0:3] = (torch.rand(N, 3, device=dev) - 0.5) * 0.2
