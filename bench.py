@@ -411,7 +411,8 @@ def run_ours(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))    # a lost collective dies fast
     _lib.load()
     W = WORKLOAD
     if W.get("eval"):
@@ -518,7 +519,14 @@ def run_ours(args):
     e2e_ms = ms2.item()
     if world > 1:
         dist.barrier()
-    launches = count_launches(lambda: step(args.warmup + 2 * args.steps + 1)) if rank == 0 else None     # not a multiple of 10: no occupancy update
+    # one more step under the CUPTI profiler for the real launch counts; every rank runs it (it contains collectives)
+    i_prof = args.warmup + 2 * args.steps
+    i_prof += 1 if i_prof % n_acc == 0 else 0                 # not a multiple of 10: no occupancy update
+    if rank == 0:
+        launches = count_launches(lambda: step(i_prof))
+    else:
+        launches = None
+        step(i_prof)
     if world > 1:
         dist.barrier()
     if rank != 0:

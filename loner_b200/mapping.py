@@ -312,6 +312,12 @@ class RayDataParallel:
             self._timed(name, lambda: self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group))
         return t
 
+    def all_reduce_async(self, t):
+        """Starts an all-reduce(SUM) on NCCL's own stream; returns the work handle (None when not data-parallel)."""
+        if not self.enabled:
+            return None
+        return self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group, async_op=True)
+
     def all_reduce_grads(self, params):
         if not self.enabled:
             return
@@ -424,8 +430,9 @@ class Optimizer:
         # every rank counts the whole batch itself; with per-rank batches (whose sizes may differ once the world-cube
         # filter has dropped rays) the two counts are summed over the ranks
         norm = ops.count_opaque(rays_d, depths)
-        if not dp.shard_batch:
-            dp.all_reduce_(norm, "all_reduce_norm")
+        # 8 bytes, latency-bound: issued asynchronously here and waited for right before the first loss kernel, so the
+        # sampler and the field forward of the first chunk hide it
+        norm_work = dp.all_reduce_async(norm) if not dp.shard_batch else None
         cfg = ops.make_loss_config(sel, self._scale_float, 0.0, float(n_rays * S), L.JS_loss.min_js_score, L.JS_loss.max_js_score,
                                    L.JS_loss.alpha, L.min_depth_eps, fixed_eps, los_lambda, L.depthloss_lambda)
         nerf = self._model.nerf_model
@@ -448,6 +455,9 @@ class Optimizer:
                 if r_c.shape[0] == 0:
                     continue
             sigma = nerf.sigma_from_rays(r_c, z, sink)
+            if norm_work is not None:
+                norm_work.wait()              # the current stream waits for the collective; the host does not
+                norm_work = None
             l_c, w, depth, opac, var, js, eps = RenderLoss.apply(
                 sigma, z, r_c, noise, d_c, cfg, norm, (L.depthloss_lambda, los_lambda))
             loss = loss + l_c
