@@ -202,6 +202,9 @@ def inference(model, xyz_, dir_, sigma_only=False, netchunk=32768, detach_sigma=
     return out if meshing else out.view(n_rays, n_samples, -1)
 
 
+_EVAL_COLOUR_BLOCK_POINTS = 1 << 23       # sample points per block of the colour head in inference (render_rays)
+
+
 def render_rays(rays, ray_sampler, nerf_model, ray_range, scale_factor, N_samples=64, retraw=False, perturb=0,
                 white_bkgd=False, raw_noise_std=0., netchunk=32768, num_colors=3, sigma_only=False, DEBUG=True,
                 detach_sigma=True, return_variance=False, render_strategy='default'):
@@ -217,8 +220,19 @@ def render_rays(rays, ray_sampler, nerf_model, ray_range, scale_factor, N_sample
         raw = nerf_model.sigma_from_rays(rays, z_vals).unsqueeze(-1)
     else:
         # camera rays (rendering_tcnn.py:387-392): colour + sigma per sample point through DecoupledNeRF.forward
-        xyz = rays[:, None, 0:3] + rays[:, None, 3:6] * z_vals.unsqueeze(2)
-        raw = inference(nerf_model, xyz, rays[:, 6:9], sigma_only=False, netchunk=0, detach_sigma=detach_sigma)
+        block = _EVAL_COLOUR_BLOCK_POINTS // max(1, N_samples)
+        if torch.is_grad_enabled() or rays.shape[0] <= block:
+            xyz = rays[:, None, 0:3] + rays[:, None, 3:6] * z_vals.unsqueeze(2)
+            raw = inference(nerf_model, xyz, rays[:, 6:9], sigma_only=False, netchunk=0, detach_sigma=detach_sigma)
+        else:
+            # inference (eval renders: 16384 rays x 2048 samples per chunk): the per-point intermediates of the colour
+            # head (positions, both encodings, their concatenation: ~450 B per point) are produced for blocks of rays
+            # instead of the whole chunk -- same numbers, 15 GB of temporaries per chunk become < 4 GB
+            raw = torch.empty(rays.shape[0], N_samples, num_colors + 1, device=rays.device, dtype=torch.float32)
+            for b0 in range(0, rays.shape[0], block):
+                r_b, z_b = rays[b0:b0 + block], z_vals[b0:b0 + block]
+                xyz = r_b[:, None, 0:3] + r_b[:, None, 3:6] * z_b.unsqueeze(2)
+                raw[b0:b0 + block] = inference(nerf_model, xyz, r_b[:, 6:9], sigma_only=False, netchunk=0, detach_sigma=detach_sigma)
     if render_strategy == 'default':
         rgb, depth, weights, opacity, variance = raw2outputs(
             raw, z_vals, None, raw_noise_std, white_bkgd, sigma_only=sigma_only, num_colors=num_colors,
