@@ -57,19 +57,23 @@ int  lb_check_cuda(cudaError_t e, const char* what);
 // internal launchers (lb_encode.cu, lb_mlp.cu) used by the fused entry points in lb_field.cu
 int lb_launch_encode_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* table,
                          size_t n_points, int n_samples, float* enc, cudaStream_t st);
+// level_major: d_enc holds planes [n_levels][n_points] (float2) instead of rows [n_points][32] (lb_encode.cu)
 int lb_launch_encode_bwd(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* table,
                          const float* d_enc, size_t n_points, int n_samples, float* grad_table, float* d_rays,
-                         float* d_x01, cudaStream_t st);
+                         float* d_x01, cudaStream_t st, bool level_major);
+int lb_launch_encode_fwd_lm(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* table,
+                            size_t n_points, int n_samples, float* planes, cudaStream_t st);
 // act [P] uint64 = ReLU bit masks (hand-off forward -> backward of the tensor-core path); NULL selects the
 // fp32 CUDA-core kernels
+// level_major: enc is stored as planes [16][n_points] (float2), the hand-off layout of multi-group plans
 int lb_launch_mlp_fwd(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
-                      uint64_t* act, cudaStream_t st);
+                      uint64_t* act, cudaStream_t st, bool level_major = false);
 int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
-                      const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st);
+                      const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st, bool level_major = false);
 int lb_launch_mlp_fwd_umma(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
-                           uint64_t* act, cudaStream_t st);
+                           uint64_t* act, cudaStream_t st, bool level_major = false);
 int lb_launch_mlp_bwd_umma(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
-                           const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st);
+                           const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st, bool level_major = false);
 
 // lb_encode.cu: leading dense levels of a "dense prefix + power-of-two hashed rest" plan (else -1); whether all levels
 // fit one L2-resident group

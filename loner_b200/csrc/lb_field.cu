@@ -26,6 +26,13 @@ extern "C" int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float*
         const int frc = lb_launch_sigma_fwd_fused(plan, rays, z, rays ? nullptr : x01, params, P, n_samples, sigma, enc, act, st);
         if (frc <= 0) return frc;
     }
+    // two-kernel path.  Tables beyond the L2 with the tensor-core MLP: `enc` is the level-major hand-off (planes
+    // [16][P] float2, same size) written by single-level-group passes (lb_encode.cu); otherwise row-major [P,32].
+    if (act && !lb_encode_single_group(plan)) {
+        int rc = lb_launch_encode_fwd_lm(plan, rays, z, x01, params + LB_MLP_PARAMS, P, rays ? n_samples : 1, enc, st);
+        if (rc) return rc;
+        return lb_launch_mlp_fwd(plan, params, enc, P, sigma, act, st, true);
+    }
     int rc = lb_launch_encode_fwd(plan, rays, z, x01, params + LB_MLP_PARAMS, P, rays ? n_samples : 1, enc, st);
     if (rc) return rc;
     return lb_launch_mlp_fwd(plan, params, enc, P, sigma, act, st);
@@ -53,8 +60,9 @@ extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float*
                                                   n_samples, grad_params, d_rays, d_x01, st);
         if (frc <= 0) return frc;
     }
-    int rc = lb_launch_mlp_bwd(plan, params, enc_inout, d_sigma, act, P, grad_params, st);
+    const bool lm = act && !lb_encode_single_group(plan);      // the layout lb_sigma_fwd left in `enc` (see there)
+    int rc = lb_launch_mlp_bwd(plan, params, enc_inout, d_sigma, act, P, grad_params, st, lm);
     if (rc) return rc;
     return lb_launch_encode_bwd(plan, rays, z, x01, params + LB_MLP_PARAMS, enc_inout, P, rays ? n_samples : 1,
-                                grad_params ? grad_params + LB_MLP_PARAMS : nullptr, d_rays, d_x01, st);
+                                grad_params ? grad_params + LB_MLP_PARAMS : nullptr, d_rays, d_x01, st, lm);
 }

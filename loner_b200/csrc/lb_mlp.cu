@@ -163,15 +163,17 @@ static bool use_simt() {
 }
 
 int lb_launch_mlp_fwd(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
-                      uint64_t* act, cudaStream_t st) {
-    if (act && !use_simt()) return lb_launch_mlp_fwd_umma(plan, mlp, enc, n_points, sigma, act, st);
+                      uint64_t* act, cudaStream_t st, bool level_major) {
+    if (act && (!use_simt() || level_major)) return lb_launch_mlp_fwd_umma(plan, mlp, enc, n_points, sigma, act, st, level_major);
+    if (level_major) { lb_set_error("the fp32 CUDA-core MLP reads row-major encodings only"); return LB_ERR_UNSUPPORTED; }
     mlp_fwd_simt_kernel<<<grid_for(plan->sm_count, n_points, 8), kThreads, 0, st>>>(mlp, enc, n_points, sigma);
     return lb_check_cuda(cudaGetLastError(), "mlp_fwd launch");
 }
 
 int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
-                      const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st) {
-    if (act && !use_simt()) return lb_launch_mlp_bwd_umma(plan, mlp, enc_inout, d_sigma, act, n_points, grad_mlp, st);
+                      const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st, bool level_major) {
+    if (act && (!use_simt() || level_major)) return lb_launch_mlp_bwd_umma(plan, mlp, enc_inout, d_sigma, act, n_points, grad_mlp, st, level_major);
+    if (level_major) { lb_set_error("the fp32 CUDA-core MLP reads row-major encodings only"); return LB_ERR_UNSUPPORTED; }
     const size_t smem = (size_t)(LB_MLP_W * LB_MLP_IN + LB_MLP_W + (2 * LB_MLP_W + LB_MLP_IN) * kLd) * sizeof(float);
     int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_bwd_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                            "mlp_bwd smem opt-in");
@@ -181,20 +183,20 @@ int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, c
 }
 #else   // shipped build: tensor cores only
 int lb_launch_mlp_fwd(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
-                      uint64_t* act, cudaStream_t st) {
+                      uint64_t* act, cudaStream_t st, bool level_major) {
     if (!act) {
         lb_set_error("lb_sigma_fwd: the act [P] ReLU-mask buffer is required (the fp32 CUDA-core MLP is a test-only build option)");
         return LB_ERR_UNSUPPORTED;
     }
-    return lb_launch_mlp_fwd_umma(plan, mlp, enc, n_points, sigma, act, st);
+    return lb_launch_mlp_fwd_umma(plan, mlp, enc, n_points, sigma, act, st, level_major);
 }
 
 int lb_launch_mlp_bwd(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
-                      const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st) {
+                      const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st, bool level_major) {
     if (!act) {
         lb_set_error("lb_sigma_bwd: the act [P] ReLU-mask buffer is required (the fp32 CUDA-core MLP is a test-only build option)");
         return LB_ERR_UNSUPPORTED;
     }
-    return lb_launch_mlp_bwd_umma(plan, mlp, enc_inout, d_sigma, act, n_points, grad_mlp, st);
+    return lb_launch_mlp_bwd_umma(plan, mlp, enc_inout, d_sigma, act, n_points, grad_mlp, st, level_major);
 }
 #endif

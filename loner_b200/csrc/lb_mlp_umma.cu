@@ -64,6 +64,24 @@ __device__ __forceinline__ void load_tile(const float* __restrict__ src, size_t 
     }
 }
 
+// the same register tile from level-major planes planes[l][p] (float2): float4 q of a row = levels 2q and 2q + 1
+__device__ __forceinline__ void load_tile_lm(const float* __restrict__ src, size_t tile, size_t n_points, TileRegs& t) {
+    const float2* planes = reinterpret_cast<const float2*>(src);
+    const size_t first = tile * (size_t)kTile;
+    const int q = threadIdx.x & 7;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const size_t p = first + i * 16 + (threadIdx.x >> 3);
+        if (p < n_points) {
+            const float2 a = __ldg(planes + (size_t)(2 * q) * n_points + p);
+            const float2 b = __ldg(planes + (size_t)(2 * q + 1) * n_points + p);
+            t.f[i] = make_float4(a.x, a.y, b.x, b.y);
+        } else {
+            t.f[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+}
+
 // converts the register tile (optionally scaled per row by s_scale[row]) into two or three bf16 piece tiles
 template <bool kThree>
 __device__ __forceinline__ void convert_tile(const TileRegs& t, const float* s_scale, uint8_t* p1, uint8_t* p2,
@@ -177,9 +195,20 @@ __device__ __forceinline__ void stage_tile(const float* __restrict__ enc, size_t
     }
 }
 
+// level-major source: thread t copies the 16 float2 of point `first + t` (one per plane) into row t; a warp reads 256
+// contiguous bytes of each plane
+__device__ __forceinline__ void stage_tile_lm(const float* __restrict__ enc, size_t tile, size_t n_points, uint32_t dst) {
+    const float2* planes = reinterpret_cast<const float2*>(enc);
+    const size_t p = tile * (size_t)kTile + threadIdx.x;
+    const bool ok = p < n_points;
+#pragma unroll
+    for (int l = 0; l < 16; ++l)
+        cp_async8(dst + threadIdx.x * kRowStride + l * 8, ok ? (const void*)(planes + (size_t)l * n_points + p) : (const void*)enc, ok ? 8u : 0u);
+}
+
 __global__ void __launch_bounds__(kThreads, kFwdCtasPerSm)
 mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc, size_t n_points,
-                    float* __restrict__ sigma, unsigned long long* __restrict__ act) {
+                    float* __restrict__ sigma, unsigned long long* __restrict__ act, int level_major) {
     extern __shared__ __align__(128) uint8_t sm[];
     const int tid = threadIdx.x, warp = tid >> 5;
     float* w2s = reinterpret_cast<float*>(sm + FwdSmem::w2);
@@ -190,7 +219,10 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
 
     const size_t n_tiles = (n_points + kTile - 1) / kTile;
     size_t tile = blockIdx.x;
-    if (tile < n_tiles) stage_tile(enc, tile, n_points, stage0);
+    if (tile < n_tiles) {
+        if (level_major) stage_tile_lm(enc, tile, n_points, stage0);
+        else stage_tile(enc, tile, n_points, stage0);
+    }
     cp_async_commit();
 
     if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kFwdTmemCols);
@@ -222,7 +254,10 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
     for (; tile < n_tiles; tile += gridDim.x, buf ^= 1u) {
         // the other staging tile was read (by its row owners) before the second barrier of the previous iteration
         const size_t next = tile + gridDim.x;
-        if (next < n_tiles) stage_tile(enc, next, n_points, stage0 + (buf ^ 1u) * kStage);
+        if (next < n_tiles) {
+            if (level_major) stage_tile_lm(enc, next, n_points, stage0 + (buf ^ 1u) * kStage);
+            else stage_tile(enc, next, n_points, stage0 + (buf ^ 1u) * kStage);
+        }
         cp_async_commit();
         cp_async_wait<1>();
         __syncthreads();                                               // every thread's copies of this tile have landed
@@ -306,7 +341,8 @@ mlp_fwd_umma_kernel(const float* __restrict__ mlp, const float* __restrict__ enc
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, kBwdCtasPerSm)
 mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, const float* __restrict__ d_sigma,
-                    const unsigned long long* __restrict__ act, size_t n_points, float* __restrict__ grad_mlp) {
+                    const unsigned long long* __restrict__ act, size_t n_points, float* __restrict__ grad_mlp,
+                    int level_major) {
     extern __shared__ __align__(128) uint8_t sm[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     float* ds_s = reinterpret_cast<float*>(sm + BwdSmem::ds);
@@ -340,7 +376,8 @@ mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, cons
         st.ds = 0.0f;
         st.bits = 0ull;
         if (t < n_tiles) {
-            load_tile(enc, t, n_points, st.regs);
+            if (level_major) load_tile_lm(enc, t, n_points, st.regs);
+            else load_tile(enc, t, n_points, st.regs);
             const size_t p = t * (size_t)kTile + tid;
             if (p < n_points) { st.ds = __ldg(d_sigma + p); st.bits = __ldg(act + p); }
         }
@@ -413,7 +450,15 @@ mlp_bwd_umma_kernel(const float* __restrict__ mlp, float* __restrict__ enc, cons
         }
         tc_fence_before();
         __syncthreads();
-        {   // coalesced write-back (in place over the encodings of this tile)
+        if (level_major) {   // write-back into the planes: thread t stores the float2 of point first + t, plane by plane
+            float2* planes = reinterpret_cast<float2*>(enc);
+            const size_t p = tile * (size_t)kTile + tid;
+            if (p < n_points) {
+#pragma unroll
+                for (int l = 0; l < 16; ++l)
+                    __stcs(planes + (size_t)l * n_points + p, *reinterpret_cast<const float2*>(sm + BwdSmem::out + tid * kOutStride + l * 8));
+            }
+        } else {   // coalesced write-back (in place over the encodings of this tile)
             float4* base = reinterpret_cast<float4*>(enc) + tile * (size_t)(kTile * 8);
             const size_t first_p = tile * (size_t)kTile;
 #pragma unroll
@@ -901,23 +946,23 @@ int umma_grid(int sm_count, size_t n_points, int ctas_per_sm) {
 }  // namespace
 
 int lb_launch_mlp_fwd_umma(const lb_plan* plan, const float* mlp, const float* enc, size_t n_points, float* sigma,
-                           uint64_t* act, cudaStream_t st) {
+                           uint64_t* act, cudaStream_t st, bool level_major) {
     // per launch: the attribute is per device, and a process may drive several devices
     int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_fwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)FwdSmem::total), "mlp_fwd_umma smem opt-in");
     if (rc) return rc;
     mlp_fwd_umma_kernel<<<umma_grid(plan->sm_count, n_points, kFwdCtasPerSm), kThreads, FwdSmem::total, st>>>(
-        mlp, enc, n_points, sigma, reinterpret_cast<unsigned long long*>(act));
+        mlp, enc, n_points, sigma, reinterpret_cast<unsigned long long*>(act), level_major ? 1 : 0);
     return lb_check_cuda(cudaGetLastError(), "mlp_fwd_umma launch");
 }
 
 int lb_launch_mlp_bwd_umma(const lb_plan* plan, const float* mlp, float* enc_inout, const float* d_sigma,
-                           const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st) {
+                           const uint64_t* act, size_t n_points, float* grad_mlp, cudaStream_t st, bool level_major) {
     int rc = lb_check_cuda(cudaFuncSetAttribute(mlp_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)BwdSmem::total), "mlp_bwd_umma smem opt-in");
     if (rc) return rc;
     mlp_bwd_umma_kernel<<<umma_grid(plan->sm_count, n_points, kBwdCtasPerSm), kThreads, BwdSmem::total, st>>>(
-        mlp, enc_inout, d_sigma, reinterpret_cast<const unsigned long long*>(act), n_points, grad_mlp);
+        mlp, enc_inout, d_sigma, reinterpret_cast<const unsigned long long*>(act), n_points, grad_mlp, level_major ? 1 : 0);
     return lb_check_cuda(cudaGetLastError(), "mlp_bwd_umma launch");
 }
 
