@@ -102,6 +102,15 @@ LB_API int  lb_plan_level(const lb_plan* plan, int level, float* scale, uint32_t
                    uint32_t* offset, uint32_t* size, int32_t* is_dense);
 
 /* ---- R0: ray construction ---------------------------------------------------------------- */
+/* Pose 6-vectors [n_poses, 6] = [t, axis-angle] -> rot [n_poses, 9] (row-major R) and origin [n_poses, 3] =
+ * (t + shift) / scale: Pose.get_transformation_matrix / tensor_to_transform (src/common/pose.py:148-152,
+ * src/common/pose_utils.py:354-368: pytorch3d axis_angle_to_matrix) + the origin lines of build_lidar_rays
+ * (src/common/ray_utils.py:293-296).  _bwd: d_pose6 [n_poses, 6] = chain rule through the same formulas (overwritten). */
+LB_API int lb_pose_to_rot_origin(const float* pose6, const float* shift, float scale, int n_poses, float* rot,
+                          float* origin, void* stream);
+LB_API int lb_pose_to_rot_origin_bwd(const float* pose6, float scale, int n_poses, const float* d_rot,
+                              const float* d_origin, float* d_pose6, void* stream);
+
 /* LidarRayDirections.build_lidar_rays (src/common/ray_utils.py:269-322) incl. get_far_val (ray_utils.py:31-60)
  * and the index selection of src/mapping/optimizer.py:389-400, as called by KeyFrame.build_lidar_rays
  * (src/mapping/keyframe.py:75-105).  directions [3,n]; distances [n] in metres (NULL: every depth is

@@ -176,7 +176,96 @@ build_camera_rays_kernel(const float* __restrict__ directions, const float* __re
         for (int c = 0; c < n_colors; ++c) intensities[(size_t)i * n_colors + c] = __ldg(image + (size_t)j * n_colors + c);
 }
 
+// ------------------------------------------------------------------------------------------
+// pose 6-vector [t, axis-angle] -> (R [3,3] row-major, ray origin o = (t + shift) / scale), forward and backward, one
+// thread per keyframe.  Same arithmetic as reference pose_utils.py:354-368 (pytorch3d axis_angle_to_matrix: axis-angle ->
+// quaternion -> matrix, sin(x/2)/x replaced by its Taylor series below 1e-6) and ray_utils.py:293-296; the backward is
+// the chain rule through exactly those formulas, so it equals what autograd produces for them.  In PyTorch this chain
+// is ~40 tiny launches forward and ~250 backward per iteration of pose refinement; here it is two.
+// ------------------------------------------------------------------------------------------
+struct Quat {
+    float th, sn, r, i, j, k, ts;     // angle, sin(th/2)/th, quaternion (r, i, j, k), 2 / |q|^2
+};
+
+__device__ __forceinline__ Quat pose_quat(const float* a) {
+    Quat q;
+    q.th = sqrtf(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]);
+    const float h = 0.5f * q.th;
+    q.sn = (fabsf(q.th) < 1e-6f) ? 0.5f - q.th * q.th / 48.0f : sinf(h) / q.th;
+    q.r = cosf(h);
+    q.i = a[0] * q.sn; q.j = a[1] * q.sn; q.k = a[2] * q.sn;
+    q.ts = 2.0f / (q.r * q.r + q.i * q.i + q.j * q.j + q.k * q.k);
+    return q;
+}
+
+__global__ void pose_to_rot_origin_kernel(const float* __restrict__ pose6, const float* __restrict__ shift, float scale,
+                                          int K, float* __restrict__ rot, float* __restrict__ origin) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= K) return;
+    const float* p = pose6 + 6 * n;
+    const Quat q = pose_quat(p + 3);
+    const float r = q.r, i = q.i, j = q.j, k = q.k, ts = q.ts;
+    float* R = rot + 9 * n;
+    R[0] = 1.0f - ts * (j * j + k * k); R[1] = ts * (i * j - k * r);        R[2] = ts * (i * k + j * r);
+    R[3] = ts * (i * j + k * r);        R[4] = 1.0f - ts * (i * i + k * k); R[5] = ts * (j * k - i * r);
+    R[6] = ts * (i * k - j * r);        R[7] = ts * (j * k + i * r);        R[8] = 1.0f - ts * (i * i + j * j);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) origin[3 * n + c] = __fdiv_rn(__fadd_rn(p[c], __ldg(shift + c)), scale);
+}
+
+__global__ void pose_to_rot_origin_bwd_kernel(const float* __restrict__ pose6, float scale, int K,
+                                              const float* __restrict__ d_rot, const float* __restrict__ d_origin,
+                                              float* __restrict__ d_pose6) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= K) return;
+    const float* a = pose6 + 6 * n + 3;
+    const Quat q = pose_quat(a);
+    const float r = q.r, i = q.i, j = q.j, k = q.k, ts = q.ts;
+    const float* G = d_rot + 9 * n;
+    // R = I + ts * M(q):  dL/dts = <G, M>,  dL/dq = ts * dM^T G  (+ dL/dts * dts/dq, dts/dq = -ts^2 q)
+    const float m0 = -(j * j + k * k), m1 = i * j - k * r, m2 = i * k + j * r, m3 = i * j + k * r, m4 = -(i * i + k * k),
+                m5 = j * k - i * r, m6 = i * k - j * r, m7 = j * k + i * r, m8 = -(i * i + j * j);
+    const float dts = G[0] * m0 + G[1] * m1 + G[2] * m2 + G[3] * m3 + G[4] * m4 + G[5] * m5 + G[6] * m6 + G[7] * m7 + G[8] * m8;
+    float dr = ts * (-G[1] * k + G[2] * j + G[3] * k - G[5] * i - G[6] * j + G[7] * i);
+    float di = ts * (G[1] * j + G[2] * k + G[3] * j - 2.0f * G[4] * i - G[5] * r + G[6] * k + G[7] * r - 2.0f * G[8] * i);
+    float dj = ts * (-2.0f * G[0] * j + G[1] * i + G[2] * r + G[3] * i + G[5] * k - G[6] * r + G[7] * k - 2.0f * G[8] * j);
+    float dk = ts * (-2.0f * G[0] * k - G[1] * r + G[2] * i + G[3] * r - 2.0f * G[4] * k + G[5] * j + G[6] * i + G[7] * j);
+    const float tt = -ts * ts * dts;
+    dr += tt * r; di += tt * i; dj += tt * j; dk += tt * k;
+    // q = (cos(th/2), a * sn(th)):  d a_c = sn * d(ijk)_c + [ (a . d(ijk)) * sn'(th) - dr * sin(th/2) / 2 ] * a_c / th
+    const float h = 0.5f * q.th;
+    const float dsn = (fabsf(q.th) < 1e-6f) ? -q.th / 24.0f : (0.5f * cosf(h) * q.th - sinf(h)) / (q.th * q.th);
+    const float radial = (a[0] * di + a[1] * dj + a[2] * dk) * dsn - 0.5f * sinf(h) * dr;
+    const float inv_th = q.th > 0.0f ? 1.0f / q.th : 0.0f;        // d|a|/da at a = 0: the subgradient 0, like torch.norm
+    float* out = d_pose6 + 6 * n;
+    out[3] = q.sn * di + radial * a[0] * inv_th;
+    out[4] = q.sn * dj + radial * a[1] * inv_th;
+    out[5] = q.sn * dk + radial * a[2] * inv_th;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) out[c] = d_origin[3 * n + c] / scale;
+}
+
 }  // namespace
+
+extern "C" int lb_pose_to_rot_origin(const float* pose6, const float* shift, float scale, int n_poses, float* rot,
+                                     float* origin, void* stream) {
+    LB_REQUIRE(n_poses == 0 || (pose6 && shift && rot && origin), "null pointer");
+    LB_REQUIRE(n_poses >= 0 && scale > 0.0f, "bad sizes");
+    if (n_poses == 0) return LB_OK;
+    pose_to_rot_origin_kernel<<<(n_poses + 63) / 64, 64, 0, (cudaStream_t)stream>>>(pose6, shift, scale, n_poses, rot, origin);
+    LB_LAUNCH_CHECK("lb_pose_to_rot_origin");
+    return LB_OK;
+}
+
+extern "C" int lb_pose_to_rot_origin_bwd(const float* pose6, float scale, int n_poses, const float* d_rot,
+                                         const float* d_origin, float* d_pose6, void* stream) {
+    LB_REQUIRE(n_poses == 0 || (pose6 && d_rot && d_origin && d_pose6), "null pointer");
+    LB_REQUIRE(n_poses >= 0 && scale > 0.0f, "bad sizes");
+    if (n_poses == 0) return LB_OK;
+    pose_to_rot_origin_bwd_kernel<<<(n_poses + 63) / 64, 64, 0, (cudaStream_t)stream>>>(pose6, scale, n_poses, d_rot, d_origin, d_pose6);
+    LB_LAUNCH_CHECK("lb_pose_to_rot_origin_bwd");
+    return LB_OK;
+}
 
 extern "C" int lb_build_lidar_rays(const float* directions, const float* distances, const int64_t* indices, int n,
                                    int m, const float* rot, const float* origin, float near, float far_max,

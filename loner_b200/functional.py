@@ -40,6 +40,49 @@ class BuildLidarRays(torch.autograd.Function):
         return d_rot, d_org, None, None, None, None, None, None, None
 
 
+class BuildWindowRays(torch.autograd.Function):
+    """R0 for a whole keyframe window in one autograd node: pose 6-vectors [K,6] -> (R, origin) per keyframe
+    (lb_pose_to_rot_origin) -> one lb_build_lidar_rays launch per job, each writing its slice of ONE [N,13] batch.
+    A job = (keyframe k, directions [3,n], distances [n] or None, indices [m], const_depth, differentiable); sky rays are
+    jobs with a constant depth that do not reach the pose (reference keyframe.py:96-98 builds them from the detached
+    pose).  Backward: per differentiable job lb_build_lidar_rays_bwd accumulates dL/dR, dL/do into row k, then
+    lb_pose_to_rot_origin_bwd.  The same chain through PyTorch ops (pose_to_rot_origin + a BuildLidarRays node and two
+    selects per keyframe) is ~40 launches forward and ~250 backward for an 8-keyframe window."""
+
+    @staticmethod
+    def forward(ctx, pose_stack, shift, scale, jobs, near, far_max, inv_scale):
+        poses = pose_stack.detach().contiguous().float()
+        rot, org = ops.pose_to_rot_origin(poses, shift, scale)
+        total = sum(j[3].shape[0] for j in jobs)
+        rays = torch.empty(total, 13, device=poses.device, dtype=torch.float32)
+        depths = torch.empty(total, device=poses.device, dtype=torch.float32)
+        off = 0
+        for (k, directions, distances, indices, const_depth, _) in jobs:
+            m = indices.shape[0]
+            ops.build_lidar_rays(directions, distances, indices, rot[k], org[k], near, far_max, inv_scale, const_depth,
+                                 out_rays=rays[off:off + m], out_depths=depths[off:off + m])
+            off += m
+        ctx.jobs, ctx.far_max, ctx.scale = jobs, far_max, scale
+        ctx.save_for_backward(poses, rot, org)
+        ctx.mark_non_differentiable(depths)
+        return rays, depths
+
+    @staticmethod
+    def backward(ctx, d_rays, _d_depths):
+        poses, rot, org = ctx.saved_tensors
+        K = poses.shape[0]
+        d_rot = torch.zeros(K, 9, device=poses.device, dtype=torch.float32)
+        d_org = torch.zeros(K, 3, device=poses.device, dtype=torch.float32)
+        d_rays = d_rays.contiguous()
+        off = 0
+        for (k, directions, _distances, indices, _const_depth, differentiable) in ctx.jobs:
+            m = indices.shape[0]
+            if differentiable:
+                ops.build_lidar_rays_bwd(directions, indices, rot[k], org[k], ctx.far_max, d_rays[off:off + m], d_rot[k], d_org[k])
+            off += m
+        return ops.pose_to_rot_origin_bwd(poses, ctx.scale, d_rot, d_org), None, None, None, None, None, None
+
+
 def _consume(ctx):
     """The saved encodings may be overwritten in place with dL/d_enc by the backward kernels (two-kernel path) and a
     GradSink hands its buffer over exactly once: a second backward through the same node (retain_graph=True) would

@@ -19,7 +19,7 @@ import torch.nn as nn
 
 from . import ops
 from ._lib import LonerB200Error
-from .functional import BuildLidarRays, GradSink, RenderLoss
+from .functional import BuildLidarRays, BuildWindowRays, GradSink, RenderLoss
 from .models import Model, OccupancyGridModel, OccGridRaySampler, UniformRaySampler
 from .optim import FusedAdam
 
@@ -552,23 +552,6 @@ class Optimizer:
             full[k] = torch.cat((torch.randperm(n, device=self._device), torch.randperm(max_len - n, device=self._device)))
         return full, int(max_len // self._num_lidar_samples)
 
-    def _window_rot_origin(self, pose_tensors):
-        """(R [K,3,3], origin [K,3]) of the window's poses.  While no pose is being optimised (map-only phases,
-        reference defaults.yaml:80-84) the result is reused until a pose tensor is replaced or modified in place
-        (tensor identity + version counter): the ~25 tiny launches of the axis-angle chain are per-iteration
-        latency, not work.  With a trainable pose the chain runs every iteration so autograd reaches the leaves."""
-        if any(t.requires_grad for t in pose_tensors):
-            self._rot_origin_cache = None
-            return pose_to_rot_origin(torch.stack(pose_tensors), self._world_cube)
-        key = tuple((id(t), t._version) for t in pose_tensors)
-        cache = getattr(self, "_rot_origin_cache", None)
-        if cache is None or cache[0] != key:
-            with torch.no_grad():
-                R, o = pose_to_rot_origin(torch.stack(pose_tensors), self._world_cube)
-            cache = (key, list(pose_tensors), R, o)       # holds the tensors: their ids cannot be recycled
-            self._rot_origin_cache = cache
-        return cache[2], cache[3]
-
     def build_batch(self, keyframes, ignore_world_cube=False, fixed=None):
         """One iteration's ray batch: per keyframe index draw + ray construction (optimizer.py:363-424).
         fixed = (full_indices, it_idx, num_iterations) selects the FIXED-strategy slice (optimizer.py:302-308).
@@ -578,10 +561,13 @@ class Optimizer:
         built to contain every ray (pose_utils.py:222-314), so the filter practically never fires: the rays of the whole
         window are built unfiltered, ONE device flag says whether any ray is short, and only then is the mask applied
         (to the concatenated batch, which keeps the reference's order).  One 1-byte read-back per iteration."""
-        rays, depths = [], []
-        # one batched pose -> (R, origin) evaluation for the whole window (autograd reaches every pose leaf)
+        # ONE autograd node for the window: fused pose -> (R, origin) kernel, then one ray-build launch per keyframe (and
+        # sky set) writing its slice of the batch; gradients reach every trainable pose leaf through the stack
         pose_tensors = [(kf._gt_pose if self._use_gt_poses else kf._pose).get_pose_tensor() for kf in keyframes]
-        R, o = self._window_rot_origin(pose_tensors)
+        pose_stack = torch.stack(pose_tensors)
+        s_host = self._world_cube.scale_host
+        r0, r1 = self._ray_range
+        jobs = []
         for k, kf in enumerate(keyframes):
             idx, sky_idx = self._select_rays(kf)
             if fixed is not None:
@@ -589,11 +575,16 @@ class Optimizer:
                 nr = self._num_lidar_samples
                 lo, hi = max(int(nr * it_idx - 1), 0), min(int(nr * (it_idx + 1) - 1), int(n_it * nr))
                 idx = full[k, lo:hi]
-            r, d = kf.build_lidar_rays(idx, self._ray_range, self._world_cube, self._use_gt_poses,
-                                       ignore_world_cube=True, sky_indices=sky_idx, rot_origin=(R[k], o[k]))
-            rays.append(r)
-            depths.append(d)
-        rays, depths = torch.vstack(rays), torch.cat(depths)
+            scan = kf.get_lidar_scan()
+            if not hasattr(kf, "_dirs_f32"):          # fp32 contiguous copies of the scan, made once per keyframe
+                kf._dirs_f32 = scan.ray_directions.float().contiguous()
+                kf._dist_f32 = scan.distances.float().contiguous()
+                kf._sky_f32 = None if scan.sky_rays is None else scan.sky_rays.float().contiguous()
+            jobs.append((k, kf._dirs_f32, kf._dist_f32, idx, 0.0, True))
+            if sky_idx is not None:                   # keyframe.py:96-98: depth ray_range[1] + 1, detached pose
+                jobs.append((k, kf._sky_f32, None, sky_idx, (r1 + 1.0) / s_host, False))
+        shift = self._world_cube.shift.float().contiguous()
+        rays, depths = BuildWindowRays.apply(pose_stack, shift, s_host, jobs, r0 / s_host, r1 / s_host, 1.0 / s_host)
         if not ignore_world_cube:
             s_host = self._world_cube.scale_host
             valid = rays.detach()[:, 12] > (self._ray_range[0] / s_host + 1. / s_host)

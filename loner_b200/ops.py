@@ -81,6 +81,23 @@ class Plan:
 _T_STEPS = {}
 
 
+def pose_to_rot_origin(pose6, shift, scale):
+    """pose 6-vectors [K,6] -> (rot [K,9] row-major, origin [K,3] = (t + shift) / scale)."""
+    K = pose6.shape[0]
+    rot = torch.empty(K, 9, device=pose6.device, dtype=torch.float32)
+    org = torch.empty(K, 3, device=pose6.device, dtype=torch.float32)
+    _lib.call("lb_pose_to_rot_origin", _p(pose6, name="pose6"), _p(shift, name="shift"), float(scale), K, _p(rot), _p(org), _stream())
+    return rot, org
+
+
+def pose_to_rot_origin_bwd(pose6, scale, d_rot, d_origin):
+    K = pose6.shape[0]
+    d_pose = torch.empty(K, 6, device=pose6.device, dtype=torch.float32)
+    _lib.call("lb_pose_to_rot_origin_bwd", _p(pose6, name="pose6"), float(scale), K, _p(d_rot, name="d_rot"),
+              _p(d_origin, name="d_origin"), _p(d_pose), _stream())
+    return d_pose
+
+
 def build_lidar_rays(directions, distances, indices, rot, origin, near, far_max, inv_scale, const_depth=0.0,
                      out_rays=None, out_depths=None):
     """R0 forward.  directions [3,n]; distances [n] or None (constant depth); indices [m] int64 or None.

@@ -45,12 +45,54 @@ class FusedAdam(torch.optim.Optimizer):
         p.addcdiv_(m, denom, value=-lr / bc1)
 
     @torch.no_grad()
+    def _step_small(self, group, params, grad_scale):
+        """All small tensors of a group (pose 6-vectors) in a handful of multi-tensor launches: one flat all-reduce of
+        their gradients when data-parallel, then the Adam formula through torch._foreach_* (one launch per operation for
+        ALL tensors instead of ~10 launches per tensor)."""
+        dp = self._dp
+        b1, b2 = group["betas"]
+        grads = [p.grad for p in params]
+        if dp is not None:
+            flat = torch.cat([g.reshape(-1) for g in grads])
+            dp.all_reduce_(flat, "all_reduce_grad")
+            grads = [t.view_as(g) for t, g in zip(flat.split([g.numel() for g in grads]), grads)]
+        if grad_scale != 1.0:
+            grads = torch._foreach_mul(grads, grad_scale)
+        ms, vs, step = [], [], None
+        for p in params:
+            st = self.state[p]
+            if not st:
+                st["step"] = 0
+                st["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+            st["step"] += 1
+            ms.append(st["exp_avg"]); vs.append(st["exp_avg_sq"])
+        steps = {self.state[p]["step"] for p in params}
+        if len(steps) != 1:                       # tensors joined the group at different times: per-tensor formula
+            for p, g, m, v in zip(params, grads, ms, vs):
+                self._update(p, g, m, v, self.state[p]["step"], group["lr"], b1, b2, group["eps"], 1.0)
+            return
+        step = steps.pop()
+        torch._foreach_mul_(ms, b1)
+        torch._foreach_add_(ms, grads, alpha=1 - b1)
+        torch._foreach_mul_(vs, b2)
+        torch._foreach_addcmul_(vs, grads, grads, value=1 - b2)
+        bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step
+        denom = torch._foreach_sqrt(vs)
+        torch._foreach_div_(denom, math.sqrt(bc2))
+        torch._foreach_add_(denom, group["eps"])
+        torch._foreach_addcdiv_(list(params), ms, denom, value=-group["lr"] / bc1)
+
+    @torch.no_grad()
     def step(self, closure=None, grad_scale=1.0):
         dp = self._dp
         for group in self.param_groups:
             b1, b2 = group["betas"]
+            small = [p for p in group["params"] if p.grad is not None and p.numel() < 1024]
+            if small:
+                self._step_small(group, small, grad_scale)
             for p in group["params"]:
-                if p.grad is None:
+                if p.grad is None or p.numel() < 1024:
                     continue
                 st = self.state[p]
                 g = p.grad
