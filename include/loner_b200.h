@@ -172,6 +172,22 @@ LB_API int lb_sigma_fwd_enc_optional(const lb_plan* plan);
 LB_API int lb_sigma_fwd(const lb_plan* plan, const float* rays, const float* z, const float* x01,
                  const float* params, int n_rays, int n_samples, float* sigma, float* enc,
                  uint64_t* act, void* stream);
+/* lb_sigma_fwd for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc): sigma-head INFERENCE (nothing is kept for a backward) with the encode -> MLP hand-off
+ * and the ReLU masks in a fixed scratch array inside the library instead of caller-owned enc / act buffers.
+ * NO COUNTERPART IN THE REFERENCE.
+ *   - limit: P = n_rays * n_samples (or n_rays points with x01) <= LB_NOALLOC_MAX_POINTS; more is rejected with
+ *     LB_ERR_BAD_ARGUMENT and a message naming the limit.  The scratch (136 B per point = 8.5 MiB) is a file-scope
+ *     __device__ array: every GPU that loads the library holds it until the process exits.
+ *   - calls no cudaMalloc / cudaFree / allocating library routine.  The first call on a device looks up the array's
+ *     device address (cudaGetSymbolAddress); make that call before starting a stream capture.
+ *   - all calls on a device share the array, which keeps the previous call's contents (nothing needs clearing: a call
+ *     writes every element it reads).  Calls that OVERLAP on the GPU race on it: keep them on one stream or order them
+ *     with events.
+ * Same arguments and results as lb_sigma_fwd without enc / act; same kernels, so sigma is bit-identical to it. */
+#define LB_NOALLOC_MAX_POINTS 65536
+LB_API int lb_sigma_fwd_noalloc(const lb_plan* plan, const float* rays, const float* z, const float* x01,
+                         const float* params, int n_rays, int n_samples, float* sigma, void* stream);
 /* Backward of the above: d_sigma [P] -> grad_params += (MLP grads, table scatter-add; NULL to skip);
  * d_rays [N,13] += (origin/direction gradients through the grid input) when non-NULL
  * (or d_x01 [P,3] when the point source is x01).  enc_inout = enc as written by lb_sigma_fwd; it is

@@ -66,3 +66,94 @@ extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float*
     return lb_launch_encode_bwd(plan, rays, z, x01, params + LB_MLP_PARAMS, enc_inout, P, rays ? n_samples : 1,
                                 grad_params ? grad_params + LB_MLP_PARAMS : nullptr, d_rays, d_x01, st, lm);
 }
+
+// ------------------------------------------------------------------------------------------
+// lb_sigma_fwd_noalloc: sigma-head inference for callers that cannot allocate device memory (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.
+//
+// lb_sigma_fwd needs two scratch buffers from its caller whenever the plan is not covered by the one-kernel path
+// (tables beyond the L2: T >= 2^20): `enc` (the encode -> MLP hand-off, 128 B per point) and `act` (ReLU masks, 8 B per
+// point).  Here both live in ONE file-scope device array of fixed size, LB_NOALLOC_MAX_POINTS points = 8.5 MiB, which
+// every GPU that loads the library holds until the process exits.  The caller passes inputs and the sigma output only.
+//
+//   * g_sigma_scratch is a device symbol: in host code its name is a host-side stand-in, NOT a device address, so the
+//     launchers are given the pointer cudaGetSymbolAddress returns -- looked up once per device, with that device
+//     current, and cached per device ordinal.
+//   * nothing in the array has to start at zero: every element a call reads (planes / rows and masks of points
+//     < P) is written earlier in the same call; tile tails beyond P are zero-filled by the MLP kernel's own staging.
+//     The array keeps the previous call's contents otherwise.
+//   * every call on a device shares the array: two calls that overlap on the GPU (different streams, or graphs
+//     replayed concurrently) RACE on it.  Serialise them (one stream, or events between streams).
+//   * no cudaMalloc / cudaFree / allocating library routine is called here or below (the launchers only launch).
+// ------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace {
+
+constexpr size_t kScratchEncBytes = (size_t)LB_NOALLOC_MAX_POINTS * LB_MLP_IN * sizeof(float);     // 8 MiB
+constexpr size_t kScratchActBytes = (size_t)LB_NOALLOC_MAX_POINTS * sizeof(uint64_t);               // 0.5 MiB
+static __device__ __align__(256) unsigned char g_sigma_scratch[kScratchEncBytes + kScratchActBytes];
+
+constexpr int kMaxDevices = 64;
+unsigned char* g_scratch_ptr[kMaxDevices] = {};      // device address of g_sigma_scratch, per device ordinal
+std::mutex g_scratch_mutex;
+
+// device address of the scratch array on the CURRENT device (set up on first use per device); nullptr on error
+int scratch_for_current_device(unsigned char** out) {
+    int dev = -1;
+    int rc = lb_check_cuda(cudaGetDevice(&dev), "lb_sigma_fwd_noalloc: cudaGetDevice");
+    if (rc) return rc;
+    if (dev < 0 || dev >= kMaxDevices) {
+        lb_set_error("lb_sigma_fwd_noalloc: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+        return LB_ERR_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (!g_scratch_ptr[dev]) {
+        void* p = nullptr;
+        rc = lb_check_cuda(cudaGetSymbolAddress(&p, g_sigma_scratch), "lb_sigma_fwd_noalloc: cudaGetSymbolAddress(scratch)");
+        if (rc) return rc;
+        if (!p) {
+            lb_set_error("lb_sigma_fwd_noalloc: cudaGetSymbolAddress returned a null device address");
+            return LB_ERR_CUDA;
+        }
+        g_scratch_ptr[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = g_scratch_ptr[dev];
+    return LB_OK;
+}
+
+}  // namespace
+
+extern "C" int lb_sigma_fwd_noalloc(const lb_plan* plan, const float* rays, const float* z, const float* x01,
+                                    const float* params, int n_rays, int n_samples, float* sigma, void* stream) {
+    LB_REQUIRE(plan, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (params && sigma), "null pointer");
+    LB_REQUIRE(n_rays == 0 || (rays && z) || x01, "need (rays, z) or x01");
+    LB_REQUIRE(plan->cfg.n_levels * LB_FEATS == LB_MLP_IN, "fused sigma head needs 16 levels x 2 features");
+    LB_REQUIRE(n_rays >= 0 && n_samples >= 1, "bad sizes");
+    const size_t P = (size_t)n_rays * (size_t)(rays ? n_samples : 1);
+    if (P > (size_t)LB_NOALLOC_MAX_POINTS) {
+        lb_set_error("lb_sigma_fwd_noalloc: %zu sample points exceed the built-in scratch of LB_NOALLOC_MAX_POINTS = %d "
+                     "points; split the batch or call lb_sigma_fwd with caller-owned enc / act buffers",
+                     P, (int)LB_NOALLOC_MAX_POINTS);
+        return LB_ERR_BAD_ARGUMENT;
+    }
+    if (P == 0) return LB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ns = rays ? n_samples : 1;
+    // plans the one-kernel path covers need no hand-off at all in inference: gather + MLP in one launch, nothing saved
+    {
+        const int frc = lb_launch_sigma_fwd_fused(plan, rays, z, rays ? nullptr : x01, params, P, ns, sigma, nullptr, nullptr, st);
+        if (frc <= 0) return frc;
+    }
+    unsigned char* scratch = nullptr;
+    int rc = scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    float* enc = reinterpret_cast<float*>(scratch);
+    uint64_t* act = reinterpret_cast<uint64_t*>(scratch + kScratchEncBytes);
+    // two-kernel path through the level-major hand-off (planes [16][P] float2), exactly as lb_sigma_fwd runs it
+    rc = lb_launch_encode_fwd_lm(plan, rays, z, x01, params + LB_MLP_PARAMS, P, ns, enc, st);
+    if (rc) return rc;
+    return lb_launch_mlp_fwd(plan, params, enc, P, sigma, act, st, true);
+}

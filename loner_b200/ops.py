@@ -206,6 +206,24 @@ def sigma_fwd(plan, params, rays=None, z=None, x01=None, save_enc=True, tensor_c
     return sigma, ((enc, act) if save_enc else None)
 
 
+NOALLOC_MAX_POINTS = 65536       # LB_NOALLOC_MAX_POINTS (include/loner_b200.h)
+
+
+def sigma_fwd_noalloc(plan, params, sigma_out, rays=None, z=None, x01=None):
+    """lb_sigma_fwd_noalloc: sigma-head inference into the caller's `sigma_out` with the library's built-in scratch
+    (at most NOALLOC_MAX_POINTS sample points).  Allocates nothing, neither here nor in the library; calls that overlap
+    on the GPU race on the shared scratch (see include/loner_b200.h).  No counterpart in the reference."""
+    if rays is not None:
+        n, s = z.shape
+    else:
+        n, s = x01.shape[0], 1
+    if sigma_out.numel() != n * s:
+        raise LonerB200Error(f"sigma_out must hold {n * s} values, got {sigma_out.numel()}")
+    _lib.call("lb_sigma_fwd_noalloc", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
+              _p(params, name="params"), n, s, _p(sigma_out, name="sigma_out"), _stream())
+    return sigma_out
+
+
 def sigma_bwd(plan, params, saved, d_sigma, rays=None, z=None, x01=None, grad_params=None, d_rays=None, need_dx=False):
     """Accumulates into grad_params / d_rays (caller zero-fills); returns d_x01 when asked.
     `saved` = (enc, act) from sigma_fwd; enc is consumed (overwritten in place with dL/d_enc)."""
