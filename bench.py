@@ -68,7 +68,6 @@ def parse_args():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS),
                     help="c2 = BASELINE configs[1] (default, the headline); c3 / c4 / c5 = configs[2] / [3] / [4]")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--graph", type=int, default=-1, help="capture the step in CUDA graphs (1/0; default: on for strong scaling)")
     return ap.parse_args()
 
 
@@ -505,12 +504,25 @@ def run_ours(args):
         pool.append((r.detach().cpu().pin_memory(), d.detach().cpu().pin_memory()))
     barrier()
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
-    last = None
+    # D2H of EVERY step's loss into pinned memory, read by the host one step behind (after that step's event): the host
+    # sees each loss inside the timed region without draining the launch queue the way a blocking .cpu() per step does
+    loss_host = torch.zeros(args.steps, dtype=torch.float32).pin_memory()
+    done = [torch.cuda.Event() for _ in range(args.steps)]
+    losses = []
     t0.record()
     for i in range(args.steps):
-        last = float(step(args.warmup + args.steps + i, pool[i % len(pool)]).detach().cpu())   # D2H of the loss each step
+        l = step(args.warmup + args.steps + i, pool[i % len(pool)])
+        loss_host[i:i + 1].copy_(l.detach().reshape(1), non_blocking=True)
+        done[i].record()
+        if i > 0:
+            done[i - 1].synchronize()
+            losses.append(float(loss_host[i - 1]))
+    done[-1].synchronize()
+    losses.append(float(loss_host[args.steps - 1]))
     t1.record()
     barrier()
+    last = losses[-1]
+    assert len(losses) == args.steps and all(x == x for x in losses), "a step's loss was not read back / is NaN"
     ms2 = torch.tensor([t0.elapsed_time(t1)], device=dev)
     last_t = torch.tensor([last], device=dev)
     if world > 1:
@@ -580,7 +592,8 @@ def run_ours(args):
             "config": config_dict(world, args.scaling),
             "roofline": roofline,
             "e2e": {"value": n_rays * (1 if strong else world) * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
-                    "h2d_bytes_per_step": n_rays * 14 * 4, "d2h_bytes_per_step": 4, "last_loss": last_t.item()},
+                    "h2d_bytes_per_step": n_rays * 14 * 4, "d2h_bytes_per_step": 4, "last_loss": last_t.item(),
+                    "readback": "every step's loss is copied to pinned host memory and read by the host one step behind (event per step)"},
             "gpu_launches": per_step_ours * args.steps if per_step_ours else abi_calls,
             "launches_per_step": launches, "c_abi_calls": abi_calls, "clocks": clk}
     if coll:

@@ -117,10 +117,15 @@ LB_API int lb_pose_to_rot_origin_bwd(const float* pose6, float scale, int n_pose
  * const_depth, the sky-ray case of keyframe.py:96-98); indices [m] int64 (NULL: identity, m <= n);
  * rot [9] = row-major R of the lidar pose, origin [3] = (t + shift) / scale (device pointers, computed by the
  * host from the pose 6-vector); near = r0/scale, far_max = r1/scale, inv_scale = 1/scale.
- * Outputs rays [m,13] = [o, d, -d, 0, 0, near, min(far_max, cube exit)], depths [m] in cube units. */
+ * Outputs rays [m,13] = [o, d, -d, 0, 0, near, min(far_max, cube exit)], depths [m] in cube units.
+ * mask_span (cube units; 0 = off): the reference DROPS rays with far <= near + 1/scale (ray_utils.py:321-322, a
+ * boolean-mask gather: host sync + data-dependent shape).  With mask_span = 1/scale such a ray stays in the batch and
+ * its depth is set to NaN -- the "masked ray" convention of lb_count_opaque / lb_composite_loss / lb_occ_grad: no loss
+ * term, no gradient, not counted in either normaliser, i.e. the arithmetic of the batch without the ray. */
 LB_API int lb_build_lidar_rays(const float* directions, const float* distances, const int64_t* indices, int n,
                         int m, const float* rot, const float* origin, float near, float far_max,
-                        float inv_scale, float const_depth, float* rays, float* depths, void* stream);
+                        float inv_scale, float const_depth, float mask_span, float* rays, float* depths,
+                        void* stream);
 /* its backward: d_rays [m,13] -> d_rot [9] += , d_origin [3] +=  (the pose chain rule R(axis-angle), o(t)
  * of src/common/pose_utils.py:354-368 stays with the host's autograd). */
 LB_API int lb_build_lidar_rays_bwd(const float* directions, const int64_t* indices, int n, int m,
@@ -229,7 +234,8 @@ LB_API int lb_composite_loss(const float* sigma, const float* z, const float* ra
                       float* weights, float* depth, float* opacity, float* variance, float* js,
                       float* eps, float* loss_parts, float* d_sigma, float* d_rays, void* stream);
 /* count of opaque rays (depth_gt > 0 and depth_gt <= far; optimizer.py:724-727): count[0] += opaque rays,
- * count[1] += n_rays (device float[2]: the norm_dev of lb_composite_loss) */
+ * count[1] += rays that are not masked (depth_gt != NaN; all n_rays when nothing is masked) -- device float[2]: the
+ * norm_dev of lb_composite_loss */
 LB_API int lb_count_opaque(const float* rays, const float* depth_gt, int n_rays, float* count, void* stream);
 
 /* ---- O1/O2: optimiser step and occupancy update ------------------------------------------ */

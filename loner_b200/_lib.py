@@ -46,7 +46,7 @@ SIGNATURES = {
                            C.POINTER(C.c_uint32), C.POINTER(C.c_int32)]),
     "lb_pose_to_rot_origin": (_I, [_P, _P, _F, _I, _P, _P, _P]),
     "lb_pose_to_rot_origin_bwd": (_I, [_P, _F, _I, _P, _P, _P, _P]),
-    "lb_build_lidar_rays": (_I, [_P, _P, _P, _I, _I, _P, _P, _F, _F, _F, _F, _P, _P, _P]),
+    "lb_build_lidar_rays": (_I, [_P, _P, _P, _I, _I, _P, _P, _F, _F, _F, _F, _F, _P, _P, _P]),
     "lb_voxel_splat_max": (_I, [_P, _P, _P, _P, _I, _I, _P, _I, _P, _I, _P, _I, _P, _P]),
     "lb_build_camera_rays": (_I, [_P, _P, _P, _P, _I, _P, _I, _I, _P, _P, _F, _P, _P, _P]),
     "lb_build_lidar_rays_bwd": (_I, [_P, _P, _I, _I, _P, _P, _F, _P, _P, _P, _P]),

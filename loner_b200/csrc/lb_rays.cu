@@ -65,13 +65,13 @@ __global__ void __launch_bounds__(kThreads)
 build_rays_kernel(const float* __restrict__ directions, const float* __restrict__ distances,
                   const long long* __restrict__ indices, int n, int m, const float* __restrict__ rot,
                   const float* __restrict__ origin, float near, float far_max, float inv_scale, float const_depth,
-                  float* __restrict__ rays, float* __restrict__ depths) {
+                  float mask_span, float* __restrict__ rays, float* __restrict__ depths) {
     const int i = blockIdx.x * kThreads + threadIdx.x;
     if (i >= m) return;
     const Pose p = load_pose(rot, origin);
     long long j = indices ? indices[i] : (long long)i;
-    j = j < 0 ? 0 : (j >= n ? (long long)n - 1 : j);       // never read out of bounds (the host wrapper validates)
     if (j < 0) j += n;                                   // torch-style negative index
+    j = j < 0 ? 0 : (j >= n ? (long long)n - 1 : j);       // never read out of bounds
     const float dx = __ldg(directions + j), dy = __ldg(directions + (size_t)n + j), dz = __ldg(directions + 2 * (size_t)n + j);
     const RayGeom g = ray_geometry(p, dx, dy, dz);
     float* r = rays + (size_t)i * LB_RAY_STRIDE;
@@ -80,8 +80,14 @@ build_rays_kernel(const float* __restrict__ directions, const float* __restrict_
     r[6] = -g.d[0]; r[7] = -g.d[1]; r[8] = -g.d[2];
     r[9] = 0.0f; r[10] = 0.0f;
     r[11] = near;
-    r[12] = fminf(far_max, g.exit_t);
-    depths[i] = distances ? __ldg(distances + j) * inv_scale : const_depth;
+    const float far = fminf(far_max, g.exit_t);
+    r[12] = far;
+    // The reference DROPS rays that leave the world cube within one metre of `near` (ray_utils.py:321-322: a
+    // boolean-mask gather, i.e. a host sync and a data-dependent batch shape).  With mask_span > 0 such a ray stays in
+    // the batch and is MASKED instead: depth = NaN, which lb_count_opaque / lb_composite_loss / lb_occ_grad read as
+    // "this ray does not exist" (no loss term, no gradient, not counted in the normalisers).
+    const float depth = distances ? __ldg(distances + j) * inv_scale : const_depth;
+    depths[i] = (mask_span > 0.0f && !(far > near + mask_span)) ? __int_as_float(0x7fc00000) : depth;
 }
 
 // d_rot [9] += sum_i g_u (x) dir_i,  d_origin [3] += sum_i (g_o + far term)
@@ -269,13 +275,14 @@ extern "C" int lb_pose_to_rot_origin_bwd(const float* pose6, float scale, int n_
 
 extern "C" int lb_build_lidar_rays(const float* directions, const float* distances, const int64_t* indices, int n,
                                    int m, const float* rot, const float* origin, float near, float far_max,
-                                   float inv_scale, float const_depth, float* rays, float* depths, void* stream) {
+                                   float inv_scale, float const_depth, float mask_span, float* rays, float* depths,
+                                   void* stream) {
     LB_REQUIRE(m == 0 || (directions && rot && origin && rays && depths), "null pointer");   // an empty batch may pass NULL buffers
     LB_REQUIRE(n > 0 && m >= 0, "bad sizes");
     if (m == 0) return LB_OK;
     build_rays_kernel<<<(m + kThreads - 1) / kThreads, kThreads, 0, (cudaStream_t)stream>>>(
         directions, distances, reinterpret_cast<const long long*>(indices), n, m, rot, origin, near, far_max, inv_scale,
-        const_depth, rays, depths);
+        const_depth, mask_span, rays, depths);
     LB_LAUNCH_CHECK("lb_build_lidar_rays");
     return LB_OK;
 }

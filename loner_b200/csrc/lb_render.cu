@@ -346,7 +346,12 @@ composite_loss_kernel(const float* __restrict__ sigma, const float* __restrict__
         __syncwarp();
         const float A = s.A;
         const float D = s.wz + (1.0f - A) * ray.far;
-        const float dg = __ldg(depth_gt + r);
+        // depth_gt = NaN marks a MASKED ray (lb_build_lidar_rays, mask_span): it is rendered like any other ray (the outputs
+        // below are defined) but contributes no loss term and no gradient, and lb_count_opaque leaves it out of both
+        // normalisers -- the arithmetic of a batch from which the reference had dropped the ray
+        const float dg_in = __ldg(depth_gt + r);
+        const bool masked = dg_in != dg_in;
+        const float dg = masked ? 0.0f : dg_in;
         const float g = dg * sc;
         const bool opaque = (dg > 0.0f) && !(dg > ray.far);        // optimizer.py:724-727
 
@@ -406,7 +411,7 @@ composite_loss_kernel(const float* __restrict__ sigma, const float* __restrict__
         const float n_all = norm_dev ? __ldg(norm_dev + 1) : 0.0f;
         const float n_total = n_all > 0.0f ? n_all * (float)S : cfg.n_total_samples;
         const float inv_nop = (opaque && n_op > 0.0f) ? 1.0f / n_op : 0.0f;
-        const float c_los = cfg.los_lambda / n_total;
+        const float c_los = masked ? 0.0f : cfg.los_lambda / n_total;
         const float derr = sc * D - g;
         const float gD = inv_nop * 2.0f * cfg.depthloss_lambda * sc * derr;     // dL/dD
         const float gA = inv_nop * sgn(A - 1.0f);                                 // dL/dA
@@ -437,7 +442,7 @@ composite_loss_kernel(const float* __restrict__ sigma, const float* __restrict__
                 dr[12] = gD * (1.0f - A);
             }
             part[0] = opaque ? derr * derr : 0.0f;
-            part[1] = los;
+            part[1] = masked ? 0.0f : los;
             part[2] = opaque ? fabsf(A - 1.0f) : 0.0f;
             part[3] = opaque ? 1.0f : 0.0f;
         }
@@ -458,14 +463,18 @@ composite_loss_kernel(const float* __restrict__ sigma, const float* __restrict__
 __global__ void count_opaque_kernel(const float* __restrict__ rays, const float* __restrict__ depth_gt, int n_rays,
                                     float* __restrict__ count) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    bool op = false;
+    bool op = false, alive = false;
     if (i < n_rays) {
         const float dg = __ldg(depth_gt + i);
+        alive = dg == dg;
         op = (dg > 0.0f) && !(dg > __ldg(rays + (size_t)i * LB_RAY_STRIDE + 12));
     }
     const unsigned m = __ballot_sync(0xffffffffu, op);
-    if ((threadIdx.x & 31) == 0 && m) atomicAdd(count, (float)__popc(m));
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(count + 1, (float)n_rays);
+    const unsigned a = __ballot_sync(0xffffffffu, alive);
+    if ((threadIdx.x & 31) == 0) {
+        if (m) atomicAdd(count, (float)__popc(m));
+        if (a) atomicAdd(count + 1, (float)__popc(a));       // rays of the batch that are not masked (depth_gt = NaN)
+    }
 }
 
 }  // namespace

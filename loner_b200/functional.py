@@ -50,7 +50,7 @@ class BuildWindowRays(torch.autograd.Function):
     selects per keyframe) is ~40 launches forward and ~250 backward for an 8-keyframe window."""
 
     @staticmethod
-    def forward(ctx, pose_stack, shift, scale, jobs, near, far_max, inv_scale):
+    def forward(ctx, pose_stack, shift, scale, jobs, near, far_max, inv_scale, mask_span=0.0):
         poses = pose_stack.detach().contiguous().float()
         rot, org = ops.pose_to_rot_origin(poses, shift, scale)
         total = sum(j[3].shape[0] for j in jobs)
@@ -60,7 +60,7 @@ class BuildWindowRays(torch.autograd.Function):
         for (k, directions, distances, indices, const_depth, _) in jobs:
             m = indices.shape[0]
             ops.build_lidar_rays(directions, distances, indices, rot[k], org[k], near, far_max, inv_scale, const_depth,
-                                 out_rays=rays[off:off + m], out_depths=depths[off:off + m])
+                                 out_rays=rays[off:off + m], out_depths=depths[off:off + m], mask_span=mask_span)
             off += m
         ctx.jobs, ctx.far_max, ctx.scale = jobs, far_max, scale
         ctx.save_for_backward(poses, rot, org)
@@ -80,7 +80,7 @@ class BuildWindowRays(torch.autograd.Function):
             if differentiable:
                 ops.build_lidar_rays_bwd(directions, indices, rot[k], org[k], ctx.far_max, d_rays[off:off + m], d_rot[k], d_org[k])
             off += m
-        return ops.pose_to_rot_origin_bwd(poses, ctx.scale, d_rot, d_org), None, None, None, None, None, None
+        return ops.pose_to_rot_origin_bwd(poses, ctx.scale, d_rot, d_org), None, None, None, None, None, None, None
 
 
 def _consume(ctx):

@@ -557,10 +557,14 @@ class Optimizer:
         fixed = (full_indices, it_idx, num_iterations) selects the FIXED-strategy slice (optimizer.py:302-308).
 
         The reference drops, per keyframe, rays that leave the world cube within one metre of `near`
-        (ray_utils.py:321-322: a boolean-mask gather, i.e. a host sync per keyframe and sky set).  The world cube is
-        built to contain every ray (pose_utils.py:222-314), so the filter practically never fires: the rays of the whole
-        window are built unfiltered, ONE device flag says whether any ray is short, and only then is the mask applied
-        (to the concatenated batch, which keeps the reference's order).  One 1-byte read-back per iteration."""
+        (ray_utils.py:321-322: a boolean-mask gather, i.e. a host sync per keyframe and sky set, and a batch whose shape
+        depends on the data).  Here the batch keeps its shape and such a ray is MASKED on the device instead: its depth is
+        NaN, which the loss kernel, the normaliser count and the occupancy update read as "this ray does not exist"
+        (include/loner_b200.h, lb_build_lidar_rays mask_span).  Loss, gradients and the occupancy update are those of
+        the reference's filtered batch; `_results_lidar` keeps a (rendered, unused) row for a masked ray.  No host sync
+        is left in the iteration: the world cube is built to contain every ray (pose_utils.py:222-314), so the filter
+        practically never fires, and a sync per iteration would put this function's ~30 launches on the GPU's critical
+        path (0.3 ms of a 9.8 ms step).  ignore_world_cube=True switches the masking off (reference flag)."""
         # ONE autograd node for the window: fused pose -> (R, origin) kernel, then one ray-build launch per keyframe (and
         # sky set) writing its slice of the batch; gradients reach every trainable pose leaf through the stack
         pose_tensors = [(kf._gt_pose if self._use_gt_poses else kf._pose).get_pose_tensor() for kf in keyframes]
@@ -584,13 +588,8 @@ class Optimizer:
             if sky_idx is not None:                   # keyframe.py:96-98: depth ray_range[1] + 1, detached pose
                 jobs.append((k, kf._sky_f32, None, sky_idx, (r1 + 1.0) / s_host, False))
         shift = self._world_cube.shift.float().contiguous()
-        rays, depths = BuildWindowRays.apply(pose_stack, shift, s_host, jobs, r0 / s_host, r1 / s_host, 1.0 / s_host)
-        if not ignore_world_cube:
-            s_host = self._world_cube.scale_host
-            valid = rays.detach()[:, 12] > (self._ray_range[0] / s_host + 1. / s_host)
-            if not bool(valid.all()):
-                rays, depths = rays[valid], depths[valid]
-        return rays, depths
+        return BuildWindowRays.apply(pose_stack, shift, s_host, jobs, r0 / s_host, r1 / s_host, 1.0 / s_host,
+                                     0.0 if ignore_world_cube else 1.0 / s_host)
 
     def iterate_optimizer(self, keyframe_window: List[KeyFrame], optimizer_settings: OptimizationSettings = None):
         """reference optimizer.py:143-190: pick the iteration schedule for this keyframe count and run it."""

@@ -99,9 +99,10 @@ def pose_to_rot_origin_bwd(pose6, scale, d_rot, d_origin):
 
 
 def build_lidar_rays(directions, distances, indices, rot, origin, near, far_max, inv_scale, const_depth=0.0,
-                     out_rays=None, out_depths=None):
+                     out_rays=None, out_depths=None, mask_span=0.0):
     """R0 forward.  directions [3,n]; distances [n] or None (constant depth); indices [m] int64 or None.
-    Writes into out_rays [m,13] / out_depths [m] when given (slices of a batch buffer)."""
+    Writes into out_rays [m,13] / out_depths [m] when given (slices of a batch buffer).  mask_span > 0: rays with
+    far <= near + mask_span (the ones the reference drops) get depth NaN = masked (see include/loner_b200.h)."""
     n = directions.shape[1]
     m = n if indices is None else indices.shape[0]
     dev = directions.device
@@ -109,7 +110,8 @@ def build_lidar_rays(directions, distances, indices, rot, origin, near, far_max,
     depths = out_depths if out_depths is not None else torch.empty(m, device=dev, dtype=torch.float32)
     _lib.call("lb_build_lidar_rays", _p(directions, name="directions"), _p(distances, name="distances"),
               _p(indices, torch.int64, name="indices"), n, m, _p(rot, name="rot"), _p(origin, name="origin"),
-              float(near), float(far_max), float(inv_scale), float(const_depth), _p(rays), _p(depths), _stream())
+              float(near), float(far_max), float(inv_scale), float(const_depth), float(mask_span), _p(rays), _p(depths),
+              _stream())
     return rays, depths
 
 

@@ -491,3 +491,117 @@ def test_window_rays_follow_pose_updates():
     window[1].get_lidar_pose().set_fixed(False)                          # trainable pose: the batch carries the graph
     r3, _ = opt.build_batch(window, ignore_world_cube=True)
     assert r3.requires_grad
+
+
+def test_masked_rays_equal_the_reference_filtered_batch():
+    """Rays the reference DROPS before compute_loss (ray_utils.py:321-322) stay in the product's batch with depth NaN.
+    The step on the masked batch must be the step on the filtered batch: loss, parameter gradients, occupancy update,
+    and zero gradient on the masked rows.  Checker: the oracle on the batch with those rays removed."""
+    from oracle import loner_oracle as O
+    g = load_golden("c1_ogm_l1js")
+    opt, M = make_optimizer(g)
+    n = g["rays"].shape[0]
+    drop = torch.zeros(n, dtype=torch.bool)
+    drop[[0, 5, 6, 100, n - 65, n - 1]] = True            # lidar rays and sky rays (the last 64 rows)
+    keep = ~drop
+    depths = g["depths"].clone()
+    depths[drop] = float("nan")
+    rays = g["rays"].to(DEV).requires_grad_(True)
+    with replay_random([g["u1"], g["u2"]], [g["noise"]]):
+        loss = opt.compute_loss(None, (rays, depths.to(DEV)), 0)
+    loss.backward()
+    gp = opt._model.nerf_model._model_sigma.params.grad
+    p_ref = golden_params(g).requires_grad_(True)
+    r_ref = g["rays"][keep].clone().requires_grad_(True)
+    cfg = dict(loss_selection=g["loss_selection"], min_js_score=g["min_js"])
+    ref = O.mapping_forward(r_ref, g["depths"][keep], p_ref, g["occ"], g["u1"][keep], g["u2"][keep], g["noise"][keep],
+                            g["scale"], g["n_samples"], log2_hashmap_size=g["log2_T"], cfg=cfg, sampler="OGM")
+    ref["loss"].backward()
+    assert torch.isfinite(loss) and abs(loss.item() - ref["loss"].item()) < 1e-4 * abs(ref["loss"].item())
+    assert torch.isfinite(gp).all() and rel_err(gp, p_ref.grad) < 1e-3
+    assert torch.isfinite(rays.grad).all()
+    assert (rays.grad[drop.to(DEV)] == 0).all()
+    assert rel_err(rays.grad[keep.to(DEV)], r_ref.grad) < 1e-3
+    res = opt._results_lidar
+    assert torch.isfinite(res["depth_fine"]).all() and torch.isfinite(res["depth_eps"]).all()
+    assert abs(opt._depth_eps - float(ref["eps"].mean())) < 0.02 * float(ref["eps"].mean())      # mean incl. eps_min rows of masked rays
+    occ0 = opt._occupancy_grid.detach().clone()
+    opt._step_occupancy_grid()
+    occ_ref = O.occ_update(g["occ"], ref["xyz"].detach(), ref["z"] * g["scale"], (g["depths"][keep] * g["scale"]).reshape(-1, 1))
+    assert torch.isfinite(opt._occupancy_grid).all()
+    assert rel_err(opt._occupancy_grid.detach() - occ0, occ_ref - g["occ"]) < 1e-3
+
+
+def test_build_batch_masks_the_rays_the_reference_drops():
+    """A world cube so small that many rays leave it within one metre of `near`: Optimizer.build_batch keeps the batch
+    shape and marks exactly the rays that KeyFrame.build_lidar_rays (reference semantics: boolean-mask gather) drops."""
+    from loner_b200 import mapping as M, synth
+    kfs, _, _ = synth.make_keyframes(2, ray_range=(1.0, 30.0), seed=6)
+    scale, shift = torch.tensor(4.0), torch.tensor([2.5, 0.0, 0.5]) - kfs[0].pose[:3]      # sensor 2.5 m off-centre in an 8 m cube
+    s = M.default_settings(n_samples_train=64, log2_hashmap_size=14, ray_range=(1.0, 30.0), lidar=700, sky=0, voxel_size=32)
+    opt = M.Optimizer(s, None, M.WorldCube(scale, shift), DEV)
+    window = [M.KeyFrame(M.LidarScanData(k.directions, k.distances, None), k.pose, device=DEV) for k in kfs]
+    for kf in window:
+        kf.is_anchored = True
+    draws, orig = [], opt._select_rays
+    opt._select_rays = lambda kf: draws.append(orig(kf)) or draws[-1]
+    rays, depths = opt.build_batch(window)
+    assert rays.shape == (1400, 13) and depths.shape == (1400,)
+    masked = depths.isnan()
+    want = ~(rays[:, 12] > rays[:, 11] + 1.0 / 4.0)
+    assert torch.equal(masked, want) and 50 < int(masked.sum()) < 1350
+    kept_r, kept_d = [], []
+    for kf, (idx, _) in zip(window, draws):
+        r, d = kf.build_lidar_rays(idx, opt._ray_range, opt._world_cube)          # drops (host sync), like the reference
+        kept_r.append(r); kept_d.append(d)
+    assert (rays[~masked] - torch.vstack(kept_r)).abs().max().item() < 1e-6
+    assert torch.equal(depths[~masked], torch.cat(kept_d))
+    rays2, depths2 = opt.build_batch(window, ignore_world_cube=True)
+    assert not depths2.isnan().any()
+    # negative (torch-style) indices wrap, out-of-range ones are clamped instead of read out of bounds
+    kf = window[0]
+    n = len(kf.get_lidar_scan())
+    a, _ = kf.build_lidar_rays(torch.tensor([-1, -n, 3], device=DEV), opt._ray_range, opt._world_cube, ignore_world_cube=True)
+    b, _ = kf.build_lidar_rays(torch.tensor([n - 1, 0, 3], device=DEV), opt._ray_range, opt._world_cube, ignore_world_cube=True)
+    assert torch.equal(a, b)
+    loss = opt.compute_loss(None, (rays, depths), 0)
+    loss.backward()
+    assert torch.isfinite(loss)
+
+
+def test_store_ray_return_and_timing_csv(tmp_path):
+    """debug.store_ray: compute_loss returns (loss, std, js) like reference optimizer.py:855-858 (std of the depth
+    distribution about its weighted mean, the clamped JS score), iterate_optimizer keeps the per-iteration rays; a
+    log_directory makes iterate_optimizer append the reference's "num_its,elapsed" line to timing.csv (:178-188)."""
+    from oracle import loner_oracle as O
+    g = load_golden("c1_ogm_l1js")
+    opt, M = make_optimizer(g)
+    opt._settings["debug"]["store_ray"] = True
+    with replay_random([g["u1"], g["u2"]], [g["noise"]]):
+        out = opt.compute_loss(None, (g["rays"].to(DEV), g["depths"].to(DEV)), 0)
+    assert isinstance(out, tuple) and len(out) == 3
+    loss, std, js = out
+    assert abs(loss.item() - g["loss"].item()) < 1e-4 * abs(g["loss"].item())
+    ref = O.mapping_forward(g["rays"], g["depths"], golden_params(g), g["occ"], g["u1"], g["u2"], g["noise"], g["scale"],
+                            g["n_samples"], log2_hashmap_size=g["log2_T"],
+                            cfg=dict(loss_selection=g["loss_selection"], min_js_score=g["min_js"]), sampler="OGM")
+    assert std.shape == js.shape == (g["rays"].shape[0],) and not std.requires_grad
+    assert rel_err(std, ref["std"].reshape(-1)) < 1e-3
+    assert rel_err(js, ref["js"].reshape(-1)) < 1e-3
+    # timing.csv + stored rays through the schedule loop
+    from loner_b200 import synth
+    kfs, scale, shift = synth.make_keyframes(1, ray_range=(1.0, 30.0), seed=3)
+    s = M.default_settings(n_samples_train=64, log2_hashmap_size=14, ray_range=(1.0, 30.0), lidar=128, sky=0, voxel_size=32,
+                           num_iterations=4)
+    s["debug"]["store_ray"] = True
+    s["log_directory"] = str(tmp_path / "logs")
+    opt2 = M.Optimizer(s, None, M.WorldCube(scale, shift), DEV)
+    kf = M.KeyFrame(M.LidarScanData(kfs[0].directions, kfs[0].distances, None), kfs[0].pose, device=DEV)
+    opt2.iterate_optimizer([kf])
+    opt2.iterate_optimizer([kf])
+    lines = (tmp_path / "logs" / "timing.csv").read_text().strip().splitlines()
+    assert len(lines) == 2
+    for ln in lines:
+        n_its, elapsed = ln.split(",")
+        assert int(n_its) == 4 and 0.0 < float(elapsed) < 60.0
+    assert len(opt2.debug_rays["rays"]) == 4 and opt2.debug_rays["std"][0].shape == (128,)
