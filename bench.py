@@ -369,16 +369,17 @@ def run_eval(args, dev, world, rank, dist):
     S = W["n_samples"]
     pts = W["chunk"] * S
     n_l, t_l = ktimes["lb_sigma_fwd"]
-    l2 = load_json("r02_l2_ceiling.json").get("patterns", {})
+    l2 = load_json("r02_l2_ceiling.json").get("ncu_tex_sectors_g_per_s", {})
     sect = load_json("r02_traffic.json").get("lb_sigma_fwd_inference", {})
     roof = {"bound": "l2", "kernel": "lb_sigma_fwd (inference: no encodings written)", "unit": "GB/s",
             "avg_launch_ms": t_l / n_l, "points_per_launch": pts,
             "hbm_view": {"achieved": (ALGO_BYTES["lb_sigma_fwd"] - 128) * pts / (t_l / n_l * 1e-3) / 1e9, "peak": peak, "peak_source": peak_src,
                          "algorithmic_bytes_per_point": ALGO_BYTES["lb_sigma_fwd"] - 128},
             "kernels_ms_per_step": {k: round(v[1] / args.steps, 3) for k, v in sorted(ktimes.items())}}
-    if l2 and sect.get("lts_sectors_per_point"):
-        ach = sect["lts_sectors_per_point"] * pts * 32 / (t_l / n_l * 1e-3) / 1e9
-        roof.update(achieved=ach, peak=l2["ld8"]["sector_gbs"], frac=ach / l2["ld8"]["sector_gbs"], traffic=sect.get("dram_bytes"))
+    if l2 and sect.get("tex_sectors_per_point"):
+        ach = sect["tex_sectors_per_point"] * pts * 32 / (t_l / n_l * 1e-3) / 1e9
+        pk = l2[sect["ceiling"]] * 32.0
+        roof.update(achieved=ach, peak=pk, frac=ach / pk, tex_sectors_per_point=sect["tex_sectors_per_point"], traffic=sect.get("dram_bytes"))
     else:
         roof.update(achieved=roof["hbm_view"]["achieved"], peak=peak, frac=roof["hbm_view"]["achieved"] / peak, traffic=None, bound="hbm")
     line = {"metric": "eval render rays/sec (depth + variance images)", "value": n_total * args.steps / (ms.item() * 1e-3), "unit": UNIT,
@@ -551,13 +552,15 @@ def run_ours(args):
     n_chunks = max(1, (n_rays + W["chunk"] - 1) // W["chunk"])
     per_launch_points = rays_local * W["n_samples"] / n_chunks
     dom = max((k for k in ktimes if k in ALGO_BYTES), key=lambda k: ktimes[k][1])
-    # L2 request-rate roofline (profiles/README.md, round 2): both fused kernels are bound by 32-byte sector requests to the
-    # L2-resident tables, not by DRAM.  peak = measured ceiling of randomly addressed 8-byte gathers (forward) /
-    # red.global.add.v2.f32 (backward) into a 57 MB table (profiles/l2_ceiling.cu -> r02_l2_ceiling.json), in the unit ncu
-    # counts (lts__t_sectors_op_read / _op_red; a reduction counts 1.5 per 32-byte sector touched); achieved = sectors
-    # per point of the kernel (ncu capture, r02_traffic.json) x points per launch / CUDA-event time.  The SURVEY 8(d)
-    # algorithmic-byte figure against the HBM copy peak is kept next to it as `hbm_view`.
-    l2 = load_json("r02_l2_ceiling.json").get("patterns", {})
+    # L2 request-rate roofline (profiles/README.md, round 2): both fused kernels are bound by the 32-byte sector requests
+    # the SMs send to the L2-resident tables, not by DRAM.  One unit on both sides, the ncu counter
+    # lts__t_sectors_srcunit_tex: achieved = sectors per point of the kernel (dense steady-state capture,
+    # profiles/r02_traffic.json) x points per launch x 32 B / CUDA-event time; peak = the same counter per second for the
+    # microbenchmark pattern with the kernel's request mix (profiles/l2_ceiling.cu -> r02_l2_ceiling.json: random 8-byte
+    # gathers + 14 % streaming stores for the forward, red.global.add.v2.f32 + 8 % streaming loads for the backward, into
+    # a 57 MB table, 'of measured').  The SURVEY 8(d) algorithmic-byte figure against the HBM copy peak stays next to it
+    # as `hbm_view`.
+    ceil = load_json("r02_l2_ceiling.json").get("ncu_tex_sectors_g_per_s", {})
     traffic = load_json("r02_traffic.json")
 
     def views(k):
@@ -567,20 +570,20 @@ def run_ours(args):
         v = {"avg_launch_ms": t_l / n_l, "hbm_view": {"achieved": hbm, "peak": peak, "frac": hbm / peak, "peak_source": peak_src,
                                                        "algorithmic_bytes_per_point": ALGO_BYTES[k]}}
         tr = traffic.get(k, {})
-        pat = "ld8" if k == "lb_sigma_fwd" else "red8"
-        if l2 and tr.get("lts_sectors_per_point") and W["log2_hashmap_size"] <= 19:
-            ceil = l2[pat]["sector_gbs"] * (1.5 if pat == "red8" else 1.0)
-            ach = tr["lts_sectors_per_point"] * per_launch_points * 32 / sec / 1e9
-            v.update(bound="l2", achieved=ach, peak=ceil, frac=ach / ceil, lts_sectors_per_point=tr["lts_sectors_per_point"],
-                     traffic=tr.get("dram_bytes") if abs(per_launch_points - 16384 * 512) < 1 else None)
-        else:
+        if ceil and tr.get("tex_sectors_per_point") and W["log2_hashmap_size"] <= 19 and not W["pose_grad"]:
+            pk = ceil[tr["ceiling"]] * 32.0
+            ach = tr["tex_sectors_per_point"] * per_launch_points * 32 / sec / 1e9
+            v.update(bound="l2", achieved=ach, peak=pk, frac=ach / pk, tex_sectors_per_point=tr["tex_sectors_per_point"],
+                     ceiling_pattern=tr["ceiling"], traffic=tr.get("dram_bytes") if abs(per_launch_points - 16384 * 512) < 1 else None)
+        else:      # other table sizes / the dL/dx backward: no sector capture committed, HBM view only
             v.update(bound="hbm", achieved=hbm, peak=peak, frac=hbm / peak, traffic=None)
         return v
 
     roofline = {"kernel": dom, "unit": "GB/s", **views(dom), "points_per_launch": per_launch_points,
-                "peak_note": "bound l2: GB/s = 32-byte L2 sector requests per second x 32; peak = measured random-access ceiling into a "
-                             "57 MB L2-resident table (profiles/r02_l2_ceiling.json, 'of measured'); hbm_view = SURVEY 8(d) algorithmic bytes "
-                             "/ MEASURED_PEAKS.json copy bandwidth",
+                "peak_note": "bound l2: GB/s = 32-byte sectors the SMs send to L2 per second x 32 (ncu lts__t_sectors_srcunit_tex); peak = the same "
+                             "counter for the microbenchmark pattern with this kernel's request mix into a 57 MB L2-resident table "
+                             "(profiles/r02_l2_ceiling.json, 'of measured'); traffic = DRAM bytes per launch; hbm_view = SURVEY 8(d) algorithmic "
+                             "bytes / MEASURED_PEAKS.json copy bandwidth",
                 "kernels_ms_per_step": {k: round(v[1] / args.steps, 4) for k, v in sorted(ktimes.items())}}
     for k in ALGO_BYTES:
         if k in ktimes and k != dom:

@@ -29,10 +29,17 @@
         }                                                                                              \
     } while (0)
 
-enum Pattern { LD8 = 0, LD8PAIR, LD16, LD8MIX, RED8, RED8PAIR, RED16, RED8MIX, N_PATTERNS };
-static const char* kNames[N_PATTERNS] = {"ld8", "ld8pair", "ld16", "ld8mix", "red8", "red8pair", "red16", "red8mix"};
-// sectors touched per warp instruction
-static const double kSectors[N_PATTERNS] = {32, 16, 32, 24, 32, 16, 32, 24};
+enum Pattern { LD8 = 0, LD8PAIR, LD16, LD8MIX, RED8, RED8PAIR, RED16, RED8MIX, FWDMIX, BWDMIX, N_PATTERNS };
+static const char* kNames[N_PATTERNS] = {"ld8", "ld8pair", "ld16", "ld8mix", "red8", "red8pair", "red16", "red8mix",
+                                         "fwdmix", "bwdmix"};
+// sectors the SMs send to L2 per warp instruction of the random-access part (the unit of lts__t_sectors_srcunit_tex)
+static const double kSectors[N_PATTERNS] = {32, 16, 32, 24, 32, 16, 32, 24, 24, 24};
+// composite patterns (round 2): the request mix of the two fused sigma kernels, per iteration of 8 random accesses
+//   fwdmix  8 x ld8mix (192 sectors per warp) + 4 coalesced streaming 8-byte stores per lane (32 sectors): 14 % writes,
+//           sigma_fwd_fused_kernel's ratio (354 M table-read sectors : 69 M sectors of saved encodings per launch)
+//   bwdmix  8 x red8mix (192 sectors) + 2 coalesced streaming 8-byte loads per lane (16 sectors): 8 % reads,
+//           sigma_bwd_fused_kernel's ratio (444 M reduction sectors : ~40 M sectors of encodings / masks / d_sigma)
+static const double kExtraSectors[N_PATTERNS] = {0, 0, 0, 0, 0, 0, 0, 0, 32, 16};
 
 __device__ __forceinline__ uint32_t lcg(uint32_t& s) {
     s = s * 1664525u + 1013904223u;
@@ -64,24 +71,39 @@ __device__ __forceinline__ uint32_t pick(uint32_t& s, uint32_t n_entries, int la
     const uint32_t r = lcg(s);
     const uint32_t base = __umulhi(r, n_entries >> 1) << 1;
     if (kPattern == LD8PAIR || kPattern == RED8PAIR) return base + (lane & 1);
+    // (LD8MIX, RED8MIX, FWDMIX, BWDMIX share the mixed pairing below)
     // mix: even-x cells (r bit 0 clear) are adjacent entries, odd-x cells two unrelated entries
     if (r & 1u) return (lane & 1) ? __umulhi(r * 2654435761u, n_entries) : base;
     return base + (lane & 1);
 }
 
 template <int kPattern, int kUnroll>
-__global__ void __launch_bounds__(256) l2_kernel(float2* table, uint32_t n_entries, int iters, float* sink) {
+__global__ void __launch_bounds__(256) l2_kernel(float2* table, uint32_t n_entries, int iters, float* sink, float2* stream,
+                                                 size_t stream_entries) {
     const int lane = threadIdx.x & 31;
     const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x;
     // pair patterns: lanes 2k and 2k+1 share a stream
-    const bool paired = kPattern == LD8PAIR || kPattern == RED8PAIR || kPattern == LD8MIX || kPattern == RED8MIX;
+    const bool paired = kPattern == LD8PAIR || kPattern == RED8PAIR || kPattern == LD8MIX || kPattern == RED8MIX ||
+                        kPattern == FWDMIX || kPattern == BWDMIX;
+    const size_t n_threads = (size_t)gridDim.x * blockDim.x;
     uint32_t s = (paired ? (gtid >> 1) : gtid) * 2654435761u + 12345u;
     float acc = 0.0f;
     for (int it = 0; it < iters; ++it) {
         uint32_t idx[kUnroll];
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) idx[u] = pick<kPattern>(s, n_entries, lane);
-        if (kPattern == LD8 || kPattern == LD8PAIR || kPattern == LD8MIX) {
+        if (kPattern == FWDMIX) {            // streaming stores of use-once data next to the gathers
+#pragma unroll
+            for (int w = 0; w < 4; ++w) __stcs(stream + ((size_t)(it * 4 + w) * n_threads + gtid) % stream_entries, make_float2(acc, 1.0f));
+        }
+        if (kPattern == BWDMIX) {            // streaming loads of use-once data next to the reductions
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+                const float2 t = __ldcs(stream + ((size_t)(it * 2 + w) * n_threads + gtid) % stream_entries);
+                acc += t.x;
+            }
+        }
+        if (kPattern == LD8 || kPattern == LD8PAIR || kPattern == LD8MIX || kPattern == FWDMIX) {
             float2 v[kUnroll];
 #pragma unroll
             for (int u = 0; u < kUnroll; ++u) v[u] = ldg8(table + idx[u]);
@@ -105,17 +127,18 @@ __global__ void __launch_bounds__(256) l2_kernel(float2* table, uint32_t n_entri
 }
 
 template <int kPattern>
-static double run(float2* table, uint32_t n_entries, float* sink, int blocks, int iters, double* ms_out) {
+static double run(float2* table, uint32_t n_entries, float* sink, int blocks, int iters, double* ms_out, float2* stream,
+                  size_t stream_entries) {
     constexpr int kUnroll = 8;
     cudaEvent_t e0, e1;
     CHECK(cudaEventCreate(&e0));
     CHECK(cudaEventCreate(&e1));
-    for (int w = 0; w < 3; ++w) l2_kernel<kPattern, kUnroll><<<blocks, 256>>>(table, n_entries, iters / 4 + 1, sink);
+    for (int w = 0; w < 3; ++w) l2_kernel<kPattern, kUnroll><<<blocks, 256>>>(table, n_entries, iters / 4 + 1, sink, stream, stream_entries);
     CHECK(cudaDeviceSynchronize());
     float best = 1e30f;
     for (int rep = 0; rep < 5; ++rep) {
         CHECK(cudaEventRecord(e0));
-        l2_kernel<kPattern, kUnroll><<<blocks, 256>>>(table, n_entries, iters, sink);
+        l2_kernel<kPattern, kUnroll><<<blocks, 256>>>(table, n_entries, iters, sink, stream, stream_entries);
         CHECK(cudaEventRecord(e1));
         CHECK(cudaEventSynchronize(e1));
         float ms;
@@ -139,23 +162,29 @@ int main(int argc, char** argv) {
     CHECK(cudaMalloc(&table, (size_t)n_entries * 8));
     CHECK(cudaMemset(table, 0, (size_t)n_entries * 8));
     CHECK(cudaMalloc(&sink, 4));
+    const size_t stream_entries = (size_t)1 << 27;            // 1 GiB of float2: use-once streams never hit the L2
+    float2* stream;
+    CHECK(cudaMalloc(&stream, stream_entries * 8));
+    CHECK(cudaMemset(stream, 0, stream_entries * 8));
     const int blocks = prop.multiProcessorCount * 8;          // 2048 threads per SM
     const int iters = 400;                                    // 148*8*8 warps x 400 x 8 = 30 M warp instr = 0.97 G lane accesses
     printf("device %s, %d SMs, L2 %d MB, table %.1f MB (%u entries), %d blocks x 256 threads, %d accesses in flight per thread\n",
            prop.name, prop.multiProcessorCount, prop.l2CacheSize >> 20, n_entries * 8 / 1e6, n_entries, blocks, 8);
     double wips[N_PATTERNS], ms[N_PATTERNS];
-    wips[LD8] = run<LD8>(table, n_entries, sink, blocks, iters, &ms[LD8]);
-    wips[LD8PAIR] = run<LD8PAIR>(table, n_entries, sink, blocks, iters, &ms[LD8PAIR]);
-    wips[LD16] = run<LD16>(table, n_entries, sink, blocks, iters, &ms[LD16]);
-    wips[LD8MIX] = run<LD8MIX>(table, n_entries, sink, blocks, iters, &ms[LD8MIX]);
-    wips[RED8] = run<RED8>(table, n_entries, sink, blocks, iters, &ms[RED8]);
-    wips[RED8PAIR] = run<RED8PAIR>(table, n_entries, sink, blocks, iters, &ms[RED8PAIR]);
-    wips[RED16] = run<RED16>(table, n_entries, sink, blocks, iters, &ms[RED16]);
-    wips[RED8MIX] = run<RED8MIX>(table, n_entries, sink, blocks, iters, &ms[RED8MIX]);
+    wips[LD8] = run<LD8>(table, n_entries, sink, blocks, iters, &ms[LD8], stream, stream_entries);
+    wips[LD8PAIR] = run<LD8PAIR>(table, n_entries, sink, blocks, iters, &ms[LD8PAIR], stream, stream_entries);
+    wips[LD16] = run<LD16>(table, n_entries, sink, blocks, iters, &ms[LD16], stream, stream_entries);
+    wips[LD8MIX] = run<LD8MIX>(table, n_entries, sink, blocks, iters, &ms[LD8MIX], stream, stream_entries);
+    wips[RED8] = run<RED8>(table, n_entries, sink, blocks, iters, &ms[RED8], stream, stream_entries);
+    wips[RED8PAIR] = run<RED8PAIR>(table, n_entries, sink, blocks, iters, &ms[RED8PAIR], stream, stream_entries);
+    wips[RED16] = run<RED16>(table, n_entries, sink, blocks, iters, &ms[RED16], stream, stream_entries);
+    wips[RED8MIX] = run<RED8MIX>(table, n_entries, sink, blocks, iters, &ms[RED8MIX], stream, stream_entries);
+    wips[FWDMIX] = run<FWDMIX>(table, n_entries, sink, blocks, iters, &ms[FWDMIX], stream, stream_entries);
+    wips[BWDMIX] = run<BWDMIX>(table, n_entries, sink, blocks, iters, &ms[BWDMIX], stream, stream_entries);
     FILE* jf = json_path ? fopen(json_path, "w") : nullptr;
     if (jf) fprintf(jf, "{\"device\": \"%s\", \"table_mb\": %.1f, \"threads_per_sm\": 2048, \"in_flight_per_thread\": 8, \"patterns\": {", prop.name, n_entries * 8 / 1e6);
     for (int p = 0; p < N_PATTERNS; ++p) {
-        const double sect = wips[p] * kSectors[p];
+        const double sect = wips[p] * (kSectors[p] + kExtraSectors[p] / 8.0);       // the extra stream accesses come once per 8 random ones
         printf("%-9s %8.3f ms  %7.2f G warp-instr/s  %7.1f G sectors/s  %8.1f GB/s of sectors  %7.1f G lane-accesses/s\n",
                kNames[p], ms[p], wips[p] / 1e9, sect / 1e9, sect * 32 / 1e9, wips[p] * 32 / 1e9);
         if (jf) fprintf(jf, "%s\"%s\": {\"ms\": %.4f, \"g_warp_instr_per_s\": %.3f, \"g_sectors_per_s\": %.2f, \"sector_gbs\": %.1f, \"g_lane_accesses_per_s\": %.2f}",
