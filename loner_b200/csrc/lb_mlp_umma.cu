@@ -736,7 +736,7 @@ int launch_fused(const lb_plan* plan, const lb_level_table& T, const float* rays
 // ------------------------------------------------------------------------------------------
 // fused forward: hash-grid gather + MLP in one launch.
 //
-// 24 gather warps (the 2-lanes-per-point walk of lb_encode.cu, 16 points per warp-unit) write their rows into a
+// 28 gather warps (the 2-lanes-per-point walk of lb_encode.cu, 16 points per warp-unit) write their rows into a
 // 2-tile shared-memory ring (and to `enc` for the backward when it is non-NULL); 4 MLP warps take each full tile
 // through the tf32 / TMEM-operand pipeline of mlp_fwd_umma_kernel.  The hand-off never leaves the SM, so the MLP's
 // re-read of the encodings (128 B per point) and its launch disappear behind the gather, which stays bound by L2
@@ -749,7 +749,13 @@ int launch_fused(const lb_plan* plan, const lb_level_table& T, const float* rays
 #define LB_FWD_RING 2
 #endif
 constexpr int kFwdRing = LB_FWD_RING;
-constexpr int kGatherWarps = 24;
+// Gather warps of the fused forward: 28 + the 4 MLP warps = 1024 threads, the CTA maximum, at 64 registers (same spills
+// as 24 warps at 72).  The gathers are latency-bound requests into an L1TEX that is 84 % busy: more warps in flight,
+// measured A-B-A-B inside the bench step: lb_sigma_fwd 3.159 -> 3.108 ms, 0.908 -> 0.922 of the L2 gather ceiling.
+#ifndef LB_GATHER_WARPS
+#define LB_GATHER_WARPS 28
+#endif
+constexpr int kGatherWarps = LB_GATHER_WARPS;
 constexpr int kFusedFwdThreads = kProducerThreads + 32 * kGatherWarps;
 constexpr uint32_t kFusedFwdTmemCols = 256;        // H0 64 | H1 64 | A0 hi 32 lo 32 | A1 hi 32 lo 32
 struct FusedFwdSmem {
