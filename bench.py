@@ -68,6 +68,8 @@ def parse_args():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS),
                     help="c2 = BASELINE configs[1] (default, the headline); c3 / c4 / c5 = configs[2] / [3] / [4]")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="N > 1: synchronous parameter all-gather (A/B against the default, which overlaps it with the next step)")
     return ap.parse_args()
 
 
@@ -305,10 +307,25 @@ def run_eval(args, dev, world, rank, dist):
     mine = rays[rank * per:(rank + 1) * per].contiguous()      # contiguous image tiles per rank, no collective
     host = mine.cpu().pin_memory()
 
+    TILE = 8 * W["chunk"]          # rays per Model.forward call: an image-sized tile (131072 rays = 8 chunks)
+
     def render(r, camera=False, strategy="default"):
+        """The whole ray set as image tiles through Model.forward(testing=True); only the images are kept (depth,
+        variance, opacity, colour): the per-sample results of a tile (weights, raw: 34 KB per ray with colour) are
+        dropped before the next tile, as a frame renderer does (analysis/renderer.py:181-215 keeps images only)."""
+        n = r.shape[0]
+        out = {"depth_fine": torch.empty(n, device=dev), "variance": torch.empty(n, device=dev),
+               "opacity_fine": torch.empty(n, device=dev)}
+        if camera:
+            out["rgb_fine"] = torch.empty(n, 3, device=dev)
         with torch.no_grad():
-            return opt._model(r, opt._ray_sampler, opt._scale_factor, testing=True, camera=camera, return_variance=True,
-                              render_strategy=strategy)
+            for t0 in range(0, n, TILE):
+                res = opt._model(r[t0:t0 + TILE], opt._ray_sampler, opt._scale_factor, testing=True, camera=camera,
+                                 return_variance=True, render_strategy=strategy)
+                for k in out:
+                    out[k][t0:t0 + TILE] = res[k].reshape(out[k][t0:t0 + TILE].shape)
+                del res
+        return out
 
     def barrier():
         if world > 1:
@@ -386,7 +403,7 @@ def run_eval(args, dev, world, rank, dist):
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms.item() / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": W["name"], "rays": n_total, "n_samples": S, "log2_hashmap_size": W["log2_hashmap_size"],
-                       "chunk": W["chunk"], "rays_per_gpu": mine.shape[0], "parallelism": f"ray-tiles{world}", "render_strategy": "default",
+                       "chunk": W["chunk"], "tile_rays": TILE, "rays_per_gpu": mine.shape[0], "parallelism": f"ray-tiles{world}", "render_strategy": "default",
                        "l2": "inputs_exceed_l2"},
             "samples_per_s": n_total * S * args.steps / (ms.item() * 1e-3),
             "roofline": roof, "other_renders_ms": extra, "peak_mem_gib": peak_mem,
@@ -443,7 +460,9 @@ def run_ours(args):
     pose_params = [kf.get_lidar_pose().get_pose_tensor() for kf in window if not kf.is_anchored]
     if pose_params:
         groups.append({"params": pose_params, "lr": settings.model_config.train.lrate_pose})
-    adam = M.FusedAdam(groups, data_parallel=dp)
+    # the parameter all-gather of step i overlaps the ray build / sampler of step i+1 (what Optimizer.iterate_optimizer
+    # does); compute_loss waits for it before the first field evaluation
+    adam = M.FusedAdam(groups, data_parallel=dp, overlap_param_gather=not args.no_overlap)
     n_acc = settings.model_config.model.occ_model.N_iters_acc
     n_rays = W["keyframes"] * W["rays_per_keyframe"]
 
@@ -475,12 +494,12 @@ def run_ours(args):
         clocks.start()
     _lib.reset_counters()
     _lib.TIMING["on"] = True
-    dp.events = [] if world > 1 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
     for i in range(args.steps):
         step(args.warmup + i)
+    dp.wait_params()                # the last step's parameter all-gather belongs to the timed region
     e1.record()
     barrier()
     _lib.TIMING["on"] = False
@@ -490,13 +509,19 @@ def run_ours(args):
     ms_total = ms.item()
     abi_calls = sum(_lib.LAUNCHES.values())
     ktimes = _lib.kernel_times()
-    coll = {}
-    if dp.events:
+    clk = clocks.stop() if rank == 0 else None
+    # collective durations: a separate short pass with every collective synchronous and bracketed by CUDA events (the
+    # timed region above overlaps the parameter all-gather with the next step, which events on this stream cannot see)
+    coll, coll_steps = {}, min(args.steps, 10)
+    if world > 1:
+        dp.events = []
+        for i in range(coll_steps):
+            step(args.warmup + i + 1)
+        barrier()
         for name, a, b in dp.events:
             n, t = coll.get(name, (0, 0.0))
             coll[name] = (n + 1, t + a.elapsed_time(b))
-    dp.events = None
-    clk = clocks.stop() if rank == 0 else None
+        dp.events = None
 
     # ---- e2e: same step through the public API with HOST ray buffers --------------------------
     pool = []
@@ -518,6 +543,8 @@ def run_ours(args):
         if i > 0:
             done[i - 1].synchronize()
             losses.append(float(loss_host[i - 1]))
+    dp.wait_params()
+    done[-1].record()
     done[-1].synchronize()
     losses.append(float(loss_host[args.steps - 1]))
     t1.record()
@@ -600,7 +627,10 @@ def run_ours(args):
             "gpu_launches": per_step_ours * args.steps if per_step_ours else abi_calls,
             "launches_per_step": launches, "c_abi_calls": abi_calls, "clocks": clk}
     if coll:
-        line["collectives_ms_per_step"] = {k: round(v[1] / args.steps, 4) for k, v in sorted(coll.items())}
+        line["collectives_ms_per_step"] = {k: round(v[1] / coll_steps, 4) for k, v in sorted(coll.items())}
+        line["collectives_note"] = (f"separate pass of {coll_steps} steps with synchronous collectives; in the timed region the parameter "
+                                    "all-gather " + ("is synchronous too (--no-overlap)" if args.no_overlap else
+                                                     "overlaps the next step's ray build and sampler"))
     if not args.no_cpu_baseline and world == 1:
         r = cpu_reference_steps(10, 2, args.cpu_sample_rays)
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}

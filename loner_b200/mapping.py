@@ -290,6 +290,7 @@ class RayDataParallel:
         self.rank = dist.get_rank(group) if self.enabled else 0
         self.shard_batch = bool(shard_batch) and self.enabled
         self.events = None              # bench.py: list of (name, start, end) CUDA events around the collectives
+        self._param_work = []           # all-gathers of updated parameters still in flight (FusedAdam overlap)
 
     def rows(self, n):
         """Row range of this rank inside an n-row chunk (shard_batch)."""
@@ -328,10 +329,22 @@ class RayDataParallel:
     def reduce_scatter(self, out, flat):
         self._timed("reduce_scatter_grad", lambda: self.dist.reduce_scatter_tensor(out, flat, op=self.dist.ReduceOp.SUM, group=self.group))
 
-    def all_gather(self, flat, shard):
+    def all_gather(self, flat, shard, overlap=False):
+        """overlap=True: the gather runs on NCCL's stream while the caller's stream goes on (next iteration's ray build,
+        normaliser count, sampler); whoever reads the parameters next must call wait_params() first.  While collectives
+        are being timed (self.events) every gather is synchronous so that its duration can be bracketed."""
         # NCCL gathers in place (shard is the rank's slice of flat); other backends (gloo, CPU tests) get a copy
         src = shard if flat.is_cuda else shard.clone()
+        if overlap and self.events is None and flat.is_cuda:
+            self._param_work.append(self.dist.all_gather_into_tensor(flat, src, group=self.group, async_op=True))
+            return
         self._timed("all_gather_params", lambda: self.dist.all_gather_into_tensor(flat, src, group=self.group))
+
+    def wait_params(self):
+        """Makes the current stream wait for parameter all-gathers still in flight (no host wait)."""
+        for w in self._param_work:
+            w.wait()
+        self._param_work.clear()
 
 
 class Optimizer:
@@ -454,6 +467,7 @@ class Optimizer:
                 kept.append((i + rows[0], i + rows[1]))
                 if r_c.shape[0] == 0:
                     continue
+            dp.wait_params()                  # an overlapped all-gather of the last Adam step ends here at the latest
             sigma = nerf.sigma_from_rays(r_c, z, sink)
             if norm_work is not None:
                 norm_work.wait()              # the current stream waits for the collective; the host does not
@@ -486,6 +500,7 @@ class Optimizer:
         (rays [N,13], intensities [N,num_colors]); sigma is evaluated under no_grad (detach_sigma)."""
         camera_rays, camera_intensities = camera_samples[0], camera_samples[1]
         camera_rays = camera_rays.reshape(-1, camera_rays.shape[-1])
+        self._dp.wait_params()
         self._results_camera = self._model(camera_rays, self._ray_sampler, self._scale_factor, camera=True,
                                            return_variance=True)
         self._camera_color_samples_fine = self._results_camera['rgb_fine'].reshape(-1, 1)
@@ -691,7 +706,8 @@ class Optimizer:
             self._model.freeze_sigma_head(True)
             self._model.freeze_rgb_head(False)
             params = self._model.get_rgb_parameters()
-            self._optimizer = FusedAdam([{'params': params, 'lr': train.lrate_rgb}], data_parallel=self._dp)
+            self._optimizer = FusedAdam([{'params': params, 'lr': train.lrate_rgb}], data_parallel=self._dp,
+                                        overlap_param_gather=True)
             gamma = train.lrate_gamma
             full, n_it = self._camera_schedule(keyframe_window, len(cam))
             s.num_iterations = n_it
@@ -710,6 +726,7 @@ class Optimizer:
             if gamma != 1.0:
                 for g in self._optimizer.param_groups:
                     g['lr'] *= gamma
+            self._dp.wait_params()
         return None if loss is None else float(loss.detach())
 
     def _do_iterate_optimizer(self, keyframe_window, iteration_schedule, optimizer_settings=None):
@@ -752,7 +769,9 @@ class Optimizer:
                 groups.append({'params': self._model.get_sigma_parameters(), 'lr': train.lrate_sigma_mlp})
             if (tracking or optimize_poses) and poses:
                 groups.append({'params': poses, 'lr': train.lrate_pose})
-            self._optimizer = FusedAdam(groups, data_parallel=self._dp)
+            # the parameter all-gather of a step overlaps the next iteration's ray build / sampler; compute_loss waits for
+            # it before the first field evaluation, and the loop's end below before anybody else can read the parameters
+            self._optimizer = FusedAdam(groups, data_parallel=self._dp, overlap_param_gather=True)
             gamma = train.lrate_gamma
             fixed_full = None
             if self._settings.rays_selection.strategy == 'FIXED':
@@ -780,6 +799,7 @@ class Optimizer:
                         self._global_step % self._model_config.model.occ_model.N_iters_acc == 0:
                     self._step_occupancy_grid()
                 self._global_step += 1
+            self._dp.wait_params()
         return None
 
     def check_finite(self, keyframe_window):

@@ -21,9 +21,13 @@ from . import ops
 
 
 class FusedAdam(torch.optim.Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, data_parallel=None):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, data_parallel=None, overlap_param_gather=False):
+        """overlap_param_gather: the all-gather of the updated parameters is left in flight when step() returns; the
+        caller must run data_parallel.wait_params() before the parameters are read again (Optimizer.compute_loss does).
+        Off by default: step() then returns with complete parameters on the current stream."""
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
         self._dp = data_parallel if (data_parallel is not None and data_parallel.enabled) else None
+        self._overlap = bool(overlap_param_gather)
 
     @staticmethod
     def _fast(p, g):
@@ -86,6 +90,8 @@ class FusedAdam(torch.optim.Optimizer):
     @torch.no_grad()
     def step(self, closure=None, grad_scale=1.0):
         dp = self._dp
+        if dp is not None:
+            dp.wait_params()           # a gather still in flight writes the slices this step is about to update
         for group in self.param_groups:
             b1, b2 = group["betas"]
             small = [p for p in group["params"] if p.grad is not None and p.numel() < 1024]
@@ -116,7 +122,7 @@ class FusedAdam(torch.optim.Optimizer):
                     mine = flat[dp.rank * k:(dp.rank + 1) * k]
                     dp.reduce_scatter(st["grad_shard"], g.view(-1))
                     self._update(mine, st["grad_shard"], st["exp_avg"], st["exp_avg_sq"], *args)
-                    dp.all_gather(flat, mine)
+                    dp.all_gather(flat, mine, overlap=self._overlap)
                     continue
                 if dp is not None:
                     dp.all_reduce_(g, "all_reduce_grad")

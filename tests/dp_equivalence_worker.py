@@ -41,6 +41,30 @@ def run(dev, dp, g, state, M, R, params0):
     return out
 
 
+def train(dev, dp, g, state, M, R, params0, overlap, n_steps=4):
+    """n_steps of compute_loss -> backward -> sharded Adam on the same batch; with `overlap` the parameter all-gather of
+    each step is left in flight and compute_loss's wait_params() is what orders it before the next field evaluation."""
+    s = M.default_settings(n_samples_train=g["n_samples"], log2_hashmap_size=g["log2_T"], ray_range=tuple(g["ray_range"]),
+                           voxel_size=g["voxel"], loss_selection=g["states"][state]["loss_selection"], strategy="OGM", chunk=g["chunk"])
+    opt = M.Optimizer(s, None, M.WorldCube(g["scale"], g["shift"]), dev, data_parallel=dp)
+    p = opt._model.nerf_model._model_sigma.params
+    with torch.no_grad():
+        p.copy_(params0.to(dev))
+        opt._occupancy_grid.copy_(g["occ"].to(dev))
+    adam = M.FusedAdam([{"params": [p], "lr": 0.01}], data_parallel=dp, overlap_param_gather=overlap)
+    rays, depths = g["rays"].to(dev), g["depths"].to(dev)
+    losses = []
+    for i in range(n_steps):
+        with R.Patch(g["rng_base_stream"] + i):
+            loss = opt.compute_loss(None, (rays, depths), i)
+        loss.backward()
+        adam.step()
+        adam.zero_grad(set_to_none=True)
+        losses.append(loss.detach().clone())
+    dp.wait_params()
+    return p.detach().clone(), torch.stack(losses)
+
+
 def main():
     from conftest import load_golden, c2_shape_params
     from loner_b200 import mapping as M
@@ -67,6 +91,7 @@ def main():
     class Off(M.RayDataParallel):
         def __init__(self):
             self.enabled, self.world_size, self.rank, self.shard_batch, self.events, self.group = False, 1, 0, False, None, None
+            self._param_work = []
     single = run(dev, Off(), g, state, M, R, params0)
     lo, hi = dp.rows(g["chunk"])
     rows = torch.cat([torch.arange(c + lo, min(c + hi, g["rays"].shape[0])) for c in range(0, g["rays"].shape[0], g["chunk"])]).to(dev)
@@ -85,6 +110,15 @@ def main():
     lst = [torch.zeros_like(chk) for _ in range(world)]
     dist.all_gather(lst, chk)
     report["params_identical_across_ranks"] = bool(all(torch.equal(lst[0], t) for t in lst))
+    # overlapped parameter all-gather (what Optimizer.iterate_optimizer runs) against the synchronous one: a gather that
+    # a field evaluation did not wait for would leave the other ranks' slices one step stale and bend the loss curve.
+    # Not bit-equal by construction: the table gradients are fp32 atomics, their order differs from run to run.
+    p_sync, l_sync = train(dev, dp, g, state, M, R, params0, overlap=False)
+    p_over, l_over = train(dev, dp, g, state, M, R, params0, overlap=True)
+    p0 = params0.to(dev)
+    report["overlap_losses"] = ((l_sync - l_over).abs() / l_sync.abs()).max().item()
+    report["overlap_loss_curve"] = [round(x, 6) for x in l_over.tolist()]
+    report["overlap_params_mean"] = ((p_sync - p_over).abs().mean() / (p_sync - p0).abs().mean()).item()
     if rank == 0:
         print("DP_EQUIVALENCE " + json.dumps(report))
     dist.barrier()

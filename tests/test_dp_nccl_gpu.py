@@ -40,3 +40,8 @@ def test_sharded_batch_step_equals_single_gpu_step(world):
     assert rep["loss_vs_reference"] < 1e-4
     assert rep["mlp_grad_vs_reference"] < 1e-3
     assert rep["table_grad_vs_reference"] < 1e-3
+    # overlapped parameter all-gather == synchronous one over 4 training steps (stale slices would bend the loss curve)
+    c = rep["overlap_loss_curve"]
+    assert abs(c[0] - c[-1]) > 1e-3 * abs(c[0]), "the 4 steps must move the loss, else the check below sees nothing"
+    assert rep["overlap_losses"] < 1e-4
+    assert rep["overlap_params_mean"] < 1e-2
