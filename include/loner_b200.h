@@ -203,6 +203,22 @@ LB_API int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float* z, 
                  const float* params, float* enc_inout, const uint64_t* act, const float* d_sigma,
                  int n_rays, int n_samples, float* grad_params, float* d_rays, float* d_x01, void* stream);
 
+/* Forward-mode input derivative for pose refinement (the lidar pose is a leaf of the reference's graph,
+ * src/mapping/optimizer.py:701-712,849: autograd carries dL/dsigma through tcnn's input gradient to the ray origins and
+ * directions built in src/common/ray_utils.py:300-322).  lb_sigma_fwd_jvp = lb_sigma_fwd on the one-kernel path plus
+ * dsigma_dx [P,3] = d sigma / d x01 of every sample point, formed inside the same kernel from the corner values the
+ * gather already holds (no second table gather in the backward).  The backward is then lb_sigma_bwd with d_rays = d_x01 =
+ * NULL plus, for the (rays, z) source, lb_rays_grad_from_jvp: d_rays[:,0:3] += sum_s d_sigma g / 2,
+ * d_rays[:,3:6] += sum_s d_sigma z g / 2 (with x01 the caller forms d_x01 = d_sigma * dsigma_dx itself).
+ * Covered plans only (lb_sigma_fwd_jvp_supported() = 1: tables within the L2 budget); others get LB_ERR_UNSUPPORTED and
+ * use the d_rays / d_x01 outputs of lb_sigma_bwd.  enc / act may be NULL when no parameter gradient will be asked. */
+LB_API int lb_sigma_fwd_jvp_supported(const lb_plan* plan);
+LB_API int lb_sigma_fwd_jvp(const lb_plan* plan, const float* rays, const float* z, const float* x01,
+                     const float* params, int n_rays, int n_samples, float* sigma, float* enc,
+                     uint64_t* act, float* dsigma_dx, void* stream);
+LB_API int lb_rays_grad_from_jvp(const float* z, const float* dsigma_dx, const float* d_sigma, int n_rays, int n_samples,
+                          float* d_rays, void* stream);
+
 /* ---- R5/R6: compositing ------------------------------------------------------------------ */
 /* raw2outputs, sigma-only (src/models/rendering_tcnn.py:219-295).  noise [N,S] already scaled by
  * raw_noise_std (NULL: none).  Outputs: weights [N,S], depth/opacity/variance [N] (variance may be NULL).

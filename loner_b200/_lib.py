@@ -57,6 +57,9 @@ SIGNATURES = {
     "lb_sigma_fwd_enc_optional": (_I, [_P]),
     "lb_sigma_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "lb_sigma_fwd_noalloc": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P]),
+    "lb_sigma_fwd_jvp_supported": (_I, [_P]),
+    "lb_sigma_fwd_jvp": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _P]),
+    "lb_rays_grad_from_jvp": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "lb_sigma_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
     "lb_composite_fwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P]),
     "lb_composite_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P]),

@@ -84,6 +84,10 @@ bool lb_encode_single_group(const lb_plan* plan);
 bool lb_sigma_fwd_fused_covers(const lb_plan* plan);
 int lb_launch_sigma_fwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* params,
                               size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act, cudaStream_t st);
+// forward + d sigma / d x01 [P,3] (forward-mode input derivative); same return convention
+int lb_launch_sigma_fwd_jvp_fused(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* params,
+                                  size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act, float* dsigma_dx,
+                                  cudaStream_t st);
 int lb_launch_sigma_bwd_fused(const lb_plan* plan, const float* rays, const float* z, const float* x01,
                               const float* params, const float* enc, const uint64_t* act, const float* d_sigma,
                               size_t n_points, int n_samples, float* grad_params, float* d_rays, float* d_x01,

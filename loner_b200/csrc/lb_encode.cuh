@@ -126,6 +126,61 @@ __device__ __forceinline__ void encode_fwd_point(const lb_level_table& T, const 
     }
 }
 
+// encode_fwd_point plus the spatial Jacobian of the encoding, d e[2l+f] / d x01[d] (fused forward with forward-mode
+// input derivative, lb_mlp_umma.cu).  Per level and x-side a lane holds the four (y,z) corners v[k], so
+//   d/dx = scale * (A(x+1) - A(x)),               A = sum_k wy wz v[k]   (the e value before the x weight)
+//   d/dy = scale * wx * (wz0 (v1 - v0) + wz1 (v3 - v2)),  d/dz likewise, summed over the two x-sides.
+// Pair exchange as for e: the even lane ends up with the three derivatives of feature 0, the odd lane with those of
+// feature 1, and writes them to its own 48-float run jac[l * 3 + d] (shared memory; 12 floats = 3 float4 per four
+// levels, so that the Jacobian never occupies more than 12 registers).
+template <int kNDense>
+__device__ __forceinline__ void encode_fwd_jvp_point(const lb_level_table& T, const Point& q, int half,
+                                                     const float2* __restrict__ table, float* out, float4* jac) {
+    float part[LB_MLP_IN];
+    float jl[12];
+#pragma unroll
+    for (int l = 0; l < 16; ++l) {
+        const lb_level& L = T.lv[l];
+        const Side s = locate_side<kNDense>(L, q, half, l);
+        float2 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = __ldg(table + s.idx[k]);
+        float a = 0.0f, b = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float w = s.wy[k & 1] * s.wz[k >> 1];
+            a = fmaf(w, v[k].x, a);
+            b = fmaf(w, v[k].y, b);
+        }
+        const float ya = s.wx * fmaf(s.wz[1], v[3].x - v[2].x, s.wz[0] * (v[1].x - v[0].x));
+        const float yb = s.wx * fmaf(s.wz[1], v[3].y - v[2].y, s.wz[0] * (v[1].y - v[0].y));
+        const float za = s.wx * fmaf(s.wy[1], v[3].x - v[1].x, s.wy[0] * (v[2].x - v[0].x));
+        const float zb = s.wx * fmaf(s.wy[1], v[3].y - v[1].y, s.wy[0] * (v[2].y - v[0].y));
+        part[2 * l] = a * s.wx;
+        part[2 * l + 1] = b * s.wx;
+        // the even lane (x side) owns feature 0 and sends its feature-1 partials; the odd lane (x + 1 side) the reverse
+        const float r0 = __shfl_xor_sync(kFull, half ? a : b, 1);
+        const float r1 = __shfl_xor_sync(kFull, half ? ya : yb, 1);
+        const float r2 = __shfl_xor_sync(kFull, half ? za : zb, 1);
+        const int g = (l & 3) * 3;
+        jl[g + 0] = L.scale * (half ? b - r0 : r0 - a);
+        jl[g + 1] = L.scale * ((half ? yb : ya) + r1);
+        jl[g + 2] = L.scale * ((half ? zb : za) + r2);
+        if ((l & 3) == 3) {
+            float4* dst = jac + (l >> 2) * 3;
+            dst[0] = make_float4(jl[0], jl[1], jl[2], jl[3]);
+            dst[1] = make_float4(jl[4], jl[5], jl[6], jl[7]);
+            dst[2] = make_float4(jl[8], jl[9], jl[10], jl[11]);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float send = half ? part[i] : part[16 + i];
+        const float recv = __shfl_xor_sync(kFull, send, 1);
+        out[i] = (half ? part[16 + i] : part[i]) + recv;
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // backward: table scatter-add (warp-aggregated) and optional dL/dx01
 // ------------------------------------------------------------------------------------------

@@ -68,6 +68,75 @@ extern "C" int lb_sigma_bwd(const lb_plan* plan, const float* rays, const float*
 }
 
 // ------------------------------------------------------------------------------------------
+// Forward-mode input derivative (pose refinement, reference src/mapping/optimizer.py:701-712 -> 849: the lidar pose is a
+// leaf of the graph, so autograd carries dL/dsigma back through tcnn's input gradient to the ray origins / directions).
+// lb_sigma_fwd_jvp returns d sigma / d x01 [P,3] with the forward (lb_mlp_umma.cu, sigma_fwd_jvp_fused_kernel), so the
+// backward needs no second table gather: lb_sigma_bwd runs without d_rays / d_x01 and lb_rays_grad_from_jvp folds
+// dL/dsigma * d sigma / d x01 into the rays.
+// ------------------------------------------------------------------------------------------
+extern "C" int lb_sigma_fwd_jvp_supported(const lb_plan* plan) { return plan && lb_sigma_fwd_fused_covers(plan) ? 1 : 0; }
+
+extern "C" int lb_sigma_fwd_jvp(const lb_plan* plan, const float* rays, const float* z, const float* x01,
+                                const float* params, int n_rays, int n_samples, float* sigma, float* enc,
+                                uint64_t* act, float* dsigma_dx, void* stream) {
+    LB_REQUIRE(plan, "null pointer");
+    LB_REQUIRE(n_rays == 0 || (params && sigma && dsigma_dx), "null pointer");
+    LB_REQUIRE(n_rays == 0 || (rays && z) || x01, "need (rays, z) or x01");
+    LB_REQUIRE(plan->cfg.n_levels * LB_FEATS == LB_MLP_IN, "fused sigma head needs 16 levels x 2 features");
+    LB_REQUIRE(n_rays >= 0 && n_samples >= 1, "bad sizes");
+    const size_t P = (size_t)n_rays * (size_t)n_samples;
+    LB_REQUIRE(P < (size_t)1 << 32, "n_rays * n_samples must be below 2^32");
+    if (P == 0) return LB_OK;
+    const int frc = lb_launch_sigma_fwd_jvp_fused(plan, rays, z, rays ? nullptr : x01, params, P, n_samples, sigma, enc, act,
+                                                  dsigma_dx, (cudaStream_t)stream);
+    if (frc <= 0) return frc;
+    lb_set_error("lb_sigma_fwd_jvp: this plan is not covered by the one-kernel forward (lb_sigma_fwd_jvp_supported); use "
+                 "lb_sigma_fwd and the d_rays / d_x01 outputs of lb_sigma_bwd");
+    return LB_ERR_UNSUPPORTED;
+}
+
+namespace {
+
+// one warp per ray: G = sum_s ds[s] g[s], H = sum_s ds[s] z[s] g[s]  ->  d_o += G / 2, d_d += H / 2
+// (x01 = (o + d z + 1) / 2; the same 0.5 as sigma_bwd_fused_kernel's d_rays)
+__global__ void __launch_bounds__(256) rays_grad_from_jvp_kernel(const float* __restrict__ zv, const float* __restrict__ dsdx,
+                                                                 const float* __restrict__ d_sigma, int n_rays, int n_samples,
+                                                                 float* __restrict__ d_rays) {
+    const int ray = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (ray >= n_rays) return;
+    const size_t base = (size_t)ray * n_samples;
+    float a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int s = lane; s < n_samples; s += 32) {
+        const float ds = __ldcs(d_sigma + base + s);
+        if (ds == 0.0f) continue;                                   // ReLU-inactive or masked samples: most of a young field
+        const float zz = __ldcs(zv + base + s);
+        const float gx = ds * __ldcs(dsdx + 3 * (base + s)), gy = ds * __ldcs(dsdx + 3 * (base + s) + 1),
+                    gz = ds * __ldcs(dsdx + 3 * (base + s) + 2);
+        a[0] += gx; a[1] += gy; a[2] += gz;
+        a[3] = fmaf(zz, gx, a[3]); a[4] = fmaf(zz, gy, a[4]); a[5] = fmaf(zz, gz, a[5]);
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) a[i] = warp_sum(a[i]);
+    if (lane < 6) {
+        float v = a[0];
+#pragma unroll
+        for (int i = 1; i < 6; ++i) v = lane == i ? a[i] : v;
+        d_rays[(size_t)ray * LB_RAY_STRIDE + lane] += 0.5f * v;
+    }
+}
+
+}  // namespace
+
+extern "C" int lb_rays_grad_from_jvp(const float* z, const float* dsigma_dx, const float* d_sigma, int n_rays, int n_samples,
+                                     float* d_rays, void* stream) {
+    LB_REQUIRE(n_rays == 0 || (z && dsigma_dx && d_sigma && d_rays), "null pointer");
+    LB_REQUIRE(n_rays >= 0 && n_samples >= 1, "bad sizes");
+    if (n_rays == 0) return LB_OK;
+    rays_grad_from_jvp_kernel<<<(n_rays + 7) / 8, 256, 0, (cudaStream_t)stream>>>(z, dsigma_dx, d_sigma, n_rays, n_samples, d_rays);
+    return lb_check_cuda(cudaGetLastError(), "rays_grad_from_jvp launch");
+}
+
+// ------------------------------------------------------------------------------------------
 // lb_sigma_fwd_noalloc: sigma-head inference for callers that cannot allocate device memory (code under CUDA graph
 // capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
 // reference.

@@ -943,6 +943,278 @@ int launch_fused_fwd(const lb_plan* plan, const lb_level_table& T, const float* 
                 : launch_fused_fwd_src<false, kNDense>(plan, T, nullptr, nullptr, x01, params, n_points, 1, sigma, enc, act, st);
 }
 
+// ------------------------------------------------------------------------------------------
+// fused forward with the forward-mode input derivative: sigma AND d sigma / d x01 [P,3] in one launch.
+//
+// Pose refinement needs dL/d(ray) = sum over the ray's samples of dL/dsigma * d sigma/d x * dx/d(ray).  The reverse-mode
+// route (sigma_bwd_fused_kernel<.., kInputGrad = true>) gathers the 8 corners of all 16 levels a second time in the
+// backward: 42 more L2 sectors per point in a kernel that is already bound by its 54 reduction sectors (8.1 instead of
+// 5.1 ms per step).  Forward mode needs no second gather: the gather warps already hold the corner values, so they also
+// form the encoding's Jacobian J = d e / d x01 (32 x 3 per point, lb_encode.cuh) and park it next to the encoding row in
+// the shared-memory ring; once the MLP warps know the point's ReLU mask m they run the backward's first MMA,
+// dE = M . (w2 (.) W1) (mask tile in shared memory, bf16 two-piece weights, TMEM accumulator -- the same arithmetic as
+// sigma_bwd_fused_kernel), and contract: d sigma / d x01 = J^T dE.  12 bytes per point leave the SM instead of a
+// 384-byte Jacobian, and the backward is the table-gradient-only kernel plus a per-ray reduction (lb_field.cu).
+//
+// Pipeline per 128-point tile (MLP warps, thread t = point t): E row -> tf32 hi / lo -> TMEM; MMA H; epilogue (sigma, mask
+// bits) -> mask tile; MMA dE; TMEM -> registers; 96 FMAs against the J row; release the ring slot.  No double buffering:
+// the two MMA round trips (~1.5 us) are shorter than the gather time of a tile (~4 us).  20 gather warps (768 threads,
+// 80 registers: the Jacobian arithmetic does not fit the 64 registers of the 1024-thread forward).
+// ------------------------------------------------------------------------------------------
+#ifndef LB_JVP_GATHER_WARPS
+#define LB_JVP_GATHER_WARPS 20
+#endif
+constexpr int kJvpGatherWarps = LB_JVP_GATHER_WARPS;
+constexpr int kJvpThreads = kProducerThreads + 32 * kJvpGatherWarps;
+constexpr int kJvpRing = 2;
+constexpr uint32_t kJacStride = 400;               // 96 floats + 16 B: row-per-thread float4 reads are conflict free
+constexpr uint32_t kJvpSlot = kStage + kTile * kJacStride;
+constexpr uint32_t kJvpTmemCols = 256;             // H 64 | A hi 32 | A lo 32 | dE 32
+struct JvpSmem {
+    static constexpr uint32_t ring = 0, mt = ring + kJvpRing * kJvpSlot, wa = mt + kMaskT, wb = wa + kPieceW,
+                              whi = wb + kPieceW, wlo = whi + 8 * kLboW, w2 = wlo + 8 * kLboW, v = w2 + 64 * 4,
+                              bars = v + 32 * 4, tmem = bars + 8 * (2 + 2 * kJvpRing), total = tmem + 8;
+};
+static_assert(JvpSmem::total <= 227 * 1024, "shared memory of the jvp forward");
+
+template <bool kFromRays, int kNDense>
+__global__ void __launch_bounds__(kJvpThreads, 1)
+sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
+                           const float* __restrict__ x01, const float* __restrict__ mlp, const float2* __restrict__ table,
+                           size_t n_points, int n_samples, float* __restrict__ sigma, float* __restrict__ enc,
+                           unsigned long long* __restrict__ act, float* __restrict__ dsigma_dx) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t bar_h = smem_u32(sm + JvpSmem::bars), bar_de = bar_h + 8;
+    const uint32_t bar_full = bar_h + 16, bar_empty = bar_full + 8 * kJvpRing;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + JvpSmem::tmem);
+    float* w2s = reinterpret_cast<float*>(sm + JvpSmem::w2);
+    float* vs = reinterpret_cast<float*>(sm + JvpSmem::v);
+    const size_t n_tiles = (n_points + kTile - 1) / kTile;
+    const size_t my_tiles = fused_rounds(n_tiles);
+
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kJvpTmemCols);
+    if (tid == 32) {
+        mbar_init(bar_h, 1);
+        mbar_init(bar_de, 1);
+        for (int i = 0; i < kJvpRing; ++i) {
+            mbar_init(bar_full + 8 * i, 8);
+            mbar_init(bar_empty + 8 * i, 4);
+        }
+    }
+    if (tid < kProducerThreads) {
+        convert_weights_tf32(mlp, sm + JvpSmem::whi, sm + JvpSmem::wlo);
+        const float* w2 = mlp + LB_MLP_W * LB_MLP_IN;
+        if (tid < LB_MLP_W) w2s[tid] = 0.5f * __ldg(w2 + tid);
+        if (tid >= 64 && tid < 64 + LB_MLP_IN) {                     // v = W1^T w2 / 2 (see mlp_fwd_umma_kernel)
+            const int k = tid - 64;
+            float a = 0.0f;
+            for (int j = 0; j < LB_MLP_W; ++j) a = fmaf(0.5f * __ldg(w2 + j), __ldg(mlp + j * LB_MLP_IN + k), a);
+            vs[k] = a;
+        }
+        for (int it = tid; it < LB_MLP_W * 4; it += kProducerThreads) {     // W1s[j,k] = w2[j] W1[j,k], two bf16 pieces
+            const int j = it >> 2, c = it & 3;
+            const float sc = __ldg(w2 + j);
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = __ldg(mlp + j * LB_MLP_IN + c * 8 + e) * sc;
+            uint32_t b1[4], b2[4];
+            split8<false>(v, b1, b2, nullptr);
+            *reinterpret_cast<uint4*>(sm + JvpSmem::wa + tile_off(j, c, kLboW)) = make_uint4(b1[0], b1[1], b1[2], b1[3]);
+            *reinterpret_cast<uint4*>(sm + JvpSmem::wb + tile_off(j, c, kLboW)) = make_uint4(b2[0], b2[1], b2[2], b2[3]);
+        }
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp < 4) {
+        // =============================== MLP warps ===============================
+        const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+        const uint32_t bhi = smem_u32(sm + JvpSmem::whi), blo = smem_u32(sm + JvpSmem::wlo);
+        const uint32_t mt = smem_u32(sm + JvpSmem::mt), wa = smem_u32(sm + JvpSmem::wa), wb = smem_u32(sm + JvpSmem::wb);
+        const uint32_t t_h = tmem, t_ahi = tmem + 64, t_alo = tmem + 96, t_de = tmem + 128;
+        constexpr uint32_t idesc_h = umma_idesc_tf32(128, LB_MLP_W);
+        constexpr uint32_t idesc_de = umma_idesc(128, LB_MLP_IN, 0, 1);
+        for (uint32_t kt = 0; kt < my_tiles; ++kt) {
+            const uint32_t slot = kt % kJvpRing, par = kt & 1u;
+            mbar_wait(bar_full + 8 * slot, (kt / kJvpRing) & 1u);
+            const uint8_t* row = sm + JvpSmem::ring + slot * kJvpSlot + tid * kRowStride;
+            float lin = 0.0f;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                uint32_t hi[16], lo[16];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 v = *reinterpret_cast<const float4*>(row + (h * 4 + q) * 16);
+                    const float4 c = *reinterpret_cast<const float4*>(vs + (h * 4 + q) * 4);
+                    lin = fmaf(v.x, c.x, lin); lin = fmaf(v.y, c.y, lin);
+                    lin = fmaf(v.z, c.z, lin); lin = fmaf(v.w, c.w, lin);
+                    uint4 a, d;
+                    split_tf32(v, a, d);
+                    hi[4 * q] = a.x; hi[4 * q + 1] = a.y; hi[4 * q + 2] = a.z; hi[4 * q + 3] = a.w;
+                    lo[4 * q] = d.x; lo[4 * q + 1] = d.y; lo[4 * q + 2] = d.z; lo[4 * q + 3] = d.w;
+                }
+                tmem_st16(t_ahi + lane_off + h * 16, hi);
+                tmem_st16(t_alo + lane_off + h * 16, lo);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            producer_barrier();                                      // A complete
+            if (tid == 0) {
+                tc_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {                     // H = E W1^T (tf32 hi / lo, see the fused forward)
+                    const uint64_t dbh = umma_desc(bhi + ks * 2 * kLboW, kLboW, 128);
+                    const uint64_t dbl = umma_desc(blo + ks * 2 * kLboW, kLboW, 128);
+                    umma_tf32_ts(t_h, t_ahi + ks * 8, dbh, idesc_h, ks > 0);
+                    umma_tf32_ts(t_h, t_ahi + ks * 8, dbl, idesc_h, 1);
+                    umma_tf32_ts(t_h, t_alo + ks * 8, dbh, idesc_h, 1);
+                }
+                umma_commit(bar_h);
+            }
+            mbar_wait(bar_h, par);
+            tc_fence_after();
+            float s = lin;
+            unsigned long long bits = 0ull;
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                uint32_t r[32];
+                tmem_ld32(t_h + lane_off + half * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int g = 0; g < 2; ++g) {
+                    float mf = 0.0f;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float h = __uint_as_float(r[g * 16 + j]);
+                        s = fmaf(w2s[half * 32 + g * 16 + j], fabsf(h), s);
+                        mf = fmaf(__saturatef(h * 8.507059173e37f), (float)(1u << j), mf);
+                    }
+                    const uint32_t m16 = __float_as_uint(mf + 8388608.0f) & 0xffffu;
+                    bits |= (unsigned long long)m16 << (32 * half + 16 * g);
+                }
+            }
+            const size_t p = fused_tile(kt) * (size_t)kTile + tid;
+            if (p < n_points) {
+                sigma[p] = s;
+                if (act) act[p] = bits;
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {                            // mask tile: 8 chunks of 8 hidden units, exact in bf16
+                const uint32_t b = (uint32_t)(bits >> (8 * c)) & 0xffu;
+                uint4 v;
+                v.x = ((b & 1u) ? 0x3f80u : 0u) | ((b & 2u) ? 0x3f800000u : 0u);
+                v.y = ((b & 4u) ? 0x3f80u : 0u) | ((b & 8u) ? 0x3f800000u : 0u);
+                v.z = ((b & 16u) ? 0x3f80u : 0u) | ((b & 32u) ? 0x3f800000u : 0u);
+                v.w = ((b & 64u) ? 0x3f80u : 0u) | ((b & 128u) ? 0x3f800000u : 0u);
+                *reinterpret_cast<uint4*>(sm + JvpSmem::mt + tile_off(tid, c, kLboP)) = v;
+            }
+            fence_async_smem();
+            tc_fence_before();
+            producer_barrier();                                      // mask tile complete; every thread has read its H row
+            if (tid == 0) {
+                tc_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {                     // dE = M (128 x 64) . W1s (64 x 32) = d sigma / d e
+                    const uint64_t da = umma_desc(mt + ks * 2 * kLboP, kLboP, 128);
+                    umma_bf16(t_de, da, umma_desc(wa + ks * 256, 128, kLboW), idesc_de, ks > 0);
+                    umma_bf16(t_de, da, umma_desc(wb + ks * 256, 128, kLboW), idesc_de, 1);
+                }
+                umma_commit(bar_de);
+            }
+            mbar_wait(bar_de, par);
+            tc_fence_after();
+            {
+                uint32_t r[32];
+                tmem_ld32(t_de + lane_off, r);
+                tmem_ld_wait();
+                // d sigma / d x01[d] = sum_{l,f} dE[2l + f] J[f][l][d]; the J row is [f][l * 3 + d], 48 floats per feature
+                const float4* jrow = reinterpret_cast<const float4*>(sm + JvpSmem::ring + slot * kJvpSlot + kStage + tid * kJacStride);
+                float g[3] = {0.0f, 0.0f, 0.0f};
+#pragma unroll
+                for (int f = 0; f < 2; ++f) {
+#pragma unroll
+                    for (int i = 0; i < 12; ++i) {
+                        const float4 j4 = jrow[f * 12 + i];
+                        const float jv[4] = {j4.x, j4.y, j4.z, j4.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int k = 4 * i + e;                 // = l * 3 + d
+                            g[k % 3] = fmaf(__uint_as_float(r[2 * (k / 3) + f]), jv[e], g[k % 3]);
+                        }
+                    }
+                }
+                if (p < n_points) {
+                    dsigma_dx[3 * p + 0] = g[0];
+                    dsigma_dx[3 * p + 1] = g[1];
+                    dsigma_dx[3 * p + 2] = g[2];
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_empty + 8 * slot);        // this warp is done with the slot's E and J rows
+        }
+    } else {
+        // =============================== gather warps ===============================
+        const int cw = warp - 4, half = lane & 1;
+        for (size_t u = cw; u < my_tiles * 8; u += kJvpGatherWarps) {
+            const uint32_t kt = (uint32_t)(u >> 3);
+            const int row = (int)(u & 7) * 16 + (lane >> 1);
+            const size_t p = fused_tile(kt) * (size_t)kTile + row;
+            const bool valid = p < n_points;
+            lb_enc::Point q = {0.5f, 0.5f, 0.5f};
+            if (valid) q = lb_enc::load_point<kFromRays>(rays, zv, x01, p, n_samples, nullptr);
+            const uint32_t slot = kt % kJvpRing;
+            // the Jacobian goes to the slot level by level, so the slot must be free before the gathers start
+            if (kt >= kJvpRing) mbar_wait(bar_empty + 8 * slot, ((kt / kJvpRing) - 1) & 1u);
+            uint8_t* base = sm + JvpSmem::ring + slot * kJvpSlot;
+            float out[16];
+            lb_enc::encode_fwd_jvp_point<kNDense>(T, q, half, table, out,
+                                                  reinterpret_cast<float4*>(base + kStage + row * kJacStride + half * 192));
+            float4* dst = reinterpret_cast<float4*>(base + row * kRowStride + half * 64);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dst[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_full + 8 * slot);
+            if (enc && valid) {
+                float4* g = reinterpret_cast<float4*>(enc + p * LB_MLP_IN + half * 16);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) __stcs(g + i, make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]));
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, kJvpTmemCols);
+}
+
+template <bool kFromRays, int kNDense>
+int launch_fused_fwd_jvp_src(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* x01,
+                             const float* params, size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act,
+                             float* dsigma_dx, cudaStream_t st) {
+    auto kern = sigma_fwd_jvp_fused_kernel<kFromRays, kNDense>;
+    int rc = lb_check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JvpSmem::total),
+                           "sigma_fwd_jvp_fused smem opt-in");
+    if (rc) return rc;
+    const size_t tiles = (n_points + kTile - 1) / kTile;
+    const size_t cap = (size_t)plan->sm_count;
+    kern<<<(int)(tiles < cap ? tiles : cap), kJvpThreads, JvpSmem::total, st>>>(
+        T, rays, z, x01, params, reinterpret_cast<const float2*>(params + LB_MLP_PARAMS), n_points, n_samples, sigma, enc,
+        reinterpret_cast<unsigned long long*>(act), dsigma_dx);
+    return lb_check_cuda(cudaGetLastError(), "sigma_fwd_jvp_fused launch");
+}
+
+template <int kNDense>
+int launch_fused_fwd_jvp(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* x01,
+                         const float* params, size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act,
+                         float* dsigma_dx, cudaStream_t st) {
+    return rays ? launch_fused_fwd_jvp_src<true, kNDense>(plan, T, rays, z, nullptr, params, n_points, n_samples, sigma, enc, act, dsigma_dx, st)
+                : launch_fused_fwd_jvp_src<false, kNDense>(plan, T, nullptr, nullptr, x01, params, n_points, 1, sigma, enc, act, dsigma_dx, st);
+}
+
 int umma_grid(int sm_count, size_t n_points, int ctas_per_sm) {
     const size_t tiles = (n_points + kTile - 1) / kTile;
     const size_t cap = (size_t)sm_count * ctas_per_sm;
@@ -1028,6 +1300,21 @@ int lb_launch_sigma_fwd_fused(const lb_plan* plan, const float* rays, const floa
         case 2: return launch_fused_fwd<2>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, st);
         case 3: return launch_fused_fwd<3>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, st);
         case 4: return launch_fused_fwd<4>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, st);
+        default: return 1;
+    }
+}
+
+// forward + forward-mode input derivative (sigma_fwd_jvp_fused_kernel); returns 1 when the configuration is not covered
+int lb_launch_sigma_fwd_jvp_fused(const lb_plan* plan, const float* rays, const float* z, const float* x01, const float* params,
+                                  size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act, float* dsigma_dx,
+                                  cudaStream_t st) {
+    if ((!rays && !x01) || !dsigma_dx || !lb_sigma_fwd_fused_covers(plan)) return 1;
+    const lb_level_table T = lb_make_level_table(plan);
+    switch (lb_encode_dense_prefix(plan)) {
+        case 1: return launch_fused_fwd_jvp<1>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, dsigma_dx, st);
+        case 2: return launch_fused_fwd_jvp<2>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, dsigma_dx, st);
+        case 3: return launch_fused_fwd_jvp<3>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, dsigma_dx, st);
+        case 4: return launch_fused_fwd_jvp<4>(plan, T, rays, z, x01, params, n_points, n_samples, sigma, enc, act, dsigma_dx, st);
         default: return 1;
     }
 }

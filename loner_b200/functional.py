@@ -109,9 +109,15 @@ class SigmaFromRays(torch.autograd.Function):
     def forward(ctx, plan, params, rays, z, sink=None):
         rays_c, z_c = rays.detach().contiguous(), z.detach().contiguous()
         need_grad = params.requires_grad or rays.requires_grad
-        sigma, saved = ops.sigma_fwd(plan, params.detach(), rays=rays_c, z=z_c, save_enc=need_grad)
+        dsdx = None
+        if rays.requires_grad and plan.jvp_supported:
+            # pose refinement: d sigma / d x01 comes out of the forward kernel (forward mode), so the backward is the
+            # table-gradient kernel plus a per-ray reduction instead of a second gather of all 128 corners per point
+            sigma, saved, dsdx = ops.sigma_fwd_jvp(plan, params.detach(), rays=rays_c, z=z_c, save_enc=params.requires_grad)
+        else:
+            sigma, saved = ops.sigma_fwd(plan, params.detach(), rays=rays_c, z=z_c, save_enc=need_grad)
         ctx.plan = plan
-        ctx.save_for_backward(params.detach(), rays_c, z_c, *(saved or (None, None)))
+        ctx.save_for_backward(params.detach(), rays_c, z_c, *(saved or (None, None)), dsdx)
         ctx.need = (params.requires_grad, rays.requires_grad)
         ctx.sink = sink if (sink is not None and params.requires_grad) else None
         if ctx.sink is not None:
@@ -121,7 +127,7 @@ class SigmaFromRays(torch.autograd.Function):
     @staticmethod
     def backward(ctx, d_sigma):
         _consume(ctx)
-        params, rays, z, enc, act = ctx.saved_tensors
+        params, rays, z, enc, act, dsdx = ctx.saved_tensors
         need_p, need_r = ctx.need
         sink = ctx.sink
         if sink is not None:
@@ -131,8 +137,13 @@ class SigmaFromRays(torch.autograd.Function):
         else:
             gp = torch.zeros_like(params) if need_p else None
         dr = torch.zeros_like(rays) if need_r else None
-        if need_p or need_r:
-            ops.sigma_bwd(ctx.plan, params, (enc, act), d_sigma.contiguous(), rays=rays, z=z, grad_params=gp, d_rays=dr)
+        d_sigma = d_sigma.contiguous()
+        if dsdx is not None:
+            if need_p:
+                ops.sigma_bwd(ctx.plan, params, (enc, act), d_sigma, rays=rays, z=z, grad_params=gp)
+            ops.rays_grad_from_jvp(z, dsdx, d_sigma, dr)
+        elif need_p or need_r:
+            ops.sigma_bwd(ctx.plan, params, (enc, act), d_sigma, rays=rays, z=z, grad_params=gp, d_rays=dr)
         if sink is not None:
             sink.pending -= 1
             gp = None
@@ -148,21 +159,30 @@ class SigmaFromPoints(torch.autograd.Function):
     def forward(ctx, plan, params, x01):
         x_c = x01.detach().contiguous()
         need_grad = params.requires_grad or x01.requires_grad
-        sigma, saved = ops.sigma_fwd(plan, params.detach(), x01=x_c, save_enc=need_grad)
+        dsdx = None
+        if x01.requires_grad and plan.jvp_supported:       # see SigmaFromRays: d sigma / d x01 from the forward kernel
+            sigma, saved, dsdx = ops.sigma_fwd_jvp(plan, params.detach(), x01=x_c, save_enc=params.requires_grad)
+        else:
+            sigma, saved = ops.sigma_fwd(plan, params.detach(), x01=x_c, save_enc=need_grad)
         ctx.plan = plan
-        ctx.save_for_backward(params.detach(), x_c, *(saved or (None, None)))
+        ctx.save_for_backward(params.detach(), x_c, *(saved or (None, None)), dsdx)
         ctx.need = (params.requires_grad, x01.requires_grad)
         return sigma
 
     @staticmethod
     def backward(ctx, d_sigma):
         _consume(ctx)
-        params, x01, enc, act = ctx.saved_tensors
+        params, x01, enc, act, dsdx = ctx.saved_tensors
         need_p, need_x = ctx.need
         gp = torch.zeros_like(params) if need_p else None
         dx = None
-        if need_p or need_x:
-            dx = ops.sigma_bwd(ctx.plan, params, (enc, act), d_sigma.contiguous(), x01=x01, grad_params=gp, need_dx=need_x)
+        d_sigma = d_sigma.contiguous()
+        if dsdx is not None:
+            if need_p:
+                ops.sigma_bwd(ctx.plan, params, (enc, act), d_sigma, x01=x01, grad_params=gp)
+            dx = d_sigma.reshape(-1, 1) * dsdx
+        elif need_p or need_x:
+            dx = ops.sigma_bwd(ctx.plan, params, (enc, act), d_sigma, x01=x01, grad_params=gp, need_dx=need_x)
         return None, gp, dx
 
 

@@ -49,6 +49,8 @@ class Plan:
         self.n_levels = n_levels
         self.n_enc = n_levels * n_features_per_level
         self.enc_optional = bool(_lib.load().lb_sigma_fwd_enc_optional(self._h))
+        # forward-mode input derivative (lb_sigma_fwd_jvp) available: the backward then needs no second table gather
+        self.jvp_supported = bool(_lib.load().lb_sigma_fwd_jvp_supported(self._h))
 
     @classmethod
     def from_tcnn_config(cls, encoding_config, network_config=None):
@@ -206,6 +208,33 @@ def sigma_fwd(plan, params, rays=None, z=None, x01=None, save_enc=True, tensor_c
     _lib.call("lb_sigma_fwd", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
               _p(params, name="params"), n, s, _p(sigma), _p(enc), _p(act, torch.int64), _stream())
     return sigma, ((enc, act) if save_enc else None)
+
+
+def sigma_fwd_jvp(plan, params, rays=None, z=None, x01=None, save_enc=True):
+    """lb_sigma_fwd_jvp: sigma plus d sigma / d x01 [P,3] from ONE forward kernel (plans with plan.jvp_supported).
+    Returns (sigma, saved, dsigma_dx); saved = (enc, act) for sigma_bwd (None when save_enc is False)."""
+    if rays is not None:
+        n, s = z.shape
+        shape = (n, s)
+    else:
+        n, s = x01.shape[0], 1
+        shape = (n,)
+    dev = params.device
+    sigma = torch.empty(shape, device=dev, dtype=torch.float32)
+    dsdx = torch.empty(n * s, 3, device=dev, dtype=torch.float32)
+    enc = torch.empty(n * s, plan.n_enc, device=dev, dtype=torch.float32) if save_enc else None
+    act = torch.empty(n * s, device=dev, dtype=torch.int64) if save_enc else None
+    _lib.call("lb_sigma_fwd_jvp", plan._h, _p(rays, name="rays"), _p(z, name="z"), _p(x01, name="x01"),
+              _p(params, name="params"), n, s, _p(sigma), _p(enc), _p(act, torch.int64), _p(dsdx), _stream())
+    return sigma, ((enc, act) if save_enc else None), dsdx
+
+
+def rays_grad_from_jvp(z, dsigma_dx, d_sigma, d_rays):
+    """d_rays[:, 0:3] += sum_s d_sigma g / 2, d_rays[:, 3:6] += sum_s d_sigma z g / 2 (g = dsigma_dx of sigma_fwd_jvp)."""
+    n, s = z.shape
+    _lib.call("lb_rays_grad_from_jvp", _p(z, name="z"), _p(dsigma_dx, name="dsigma_dx"), _p(d_sigma, name="d_sigma"),
+              n, s, _p(d_rays, name="d_rays"), _stream())
+    return d_rays
 
 
 NOALLOC_MAX_POINTS = 65536       # LB_NOALLOC_MAX_POINTS (include/loner_b200.h)
