@@ -973,9 +973,20 @@ constexpr uint32_t kJvpTmemCols = 256;             // H 64 | A hi 32 | A lo 32 |
 struct JvpSmem {
     static constexpr uint32_t ring = 0, mt = ring + kJvpRing * kJvpSlot, wa = mt + kMaskT, wb = wa + kPieceW,
                               whi = wb + kPieceW, wlo = whi + 8 * kLboW, w2 = wlo + 8 * kLboW, v = w2 + 64 * 4,
-                              bars = v + 32 * 4, tmem = bars + 8 * (2 + 2 * kJvpRing), total = tmem + 8;
+                              bars = v + 32 * 4, done = bars + 8 * (2 + kJvpRing), tmem = done + 8, total = tmem + 8;
 };
 static_assert(JvpSmem::total <= 227 * 1024, "shared memory of the jvp forward");
+
+// monotonic tile counter in shared memory (see the gather warps of sigma_fwd_jvp_fused_kernel)
+__device__ __forceinline__ void counter_release_add(uint32_t addr) {
+    asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ void counter_wait(uint32_t addr, uint32_t target) {
+    uint32_t v;
+    do {
+        asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    } while (v < target);
+}
 
 template <bool kFromRays, int kNDense>
 __global__ void __launch_bounds__(kJvpThreads, 1)
@@ -986,7 +997,7 @@ sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, con
     extern __shared__ __align__(128) uint8_t sm[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t bar_h = smem_u32(sm + JvpSmem::bars), bar_de = bar_h + 8;
-    const uint32_t bar_full = bar_h + 16, bar_empty = bar_full + 8 * kJvpRing;
+    const uint32_t bar_full = bar_h + 16, done_cnt = smem_u32(sm + JvpSmem::done);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + JvpSmem::tmem);
     float* w2s = reinterpret_cast<float*>(sm + JvpSmem::w2);
     float* vs = reinterpret_cast<float*>(sm + JvpSmem::v);
@@ -997,10 +1008,8 @@ sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, con
     if (tid == 32) {
         mbar_init(bar_h, 1);
         mbar_init(bar_de, 1);
-        for (int i = 0; i < kJvpRing; ++i) {
-            mbar_init(bar_full + 8 * i, 8);
-            mbar_init(bar_empty + 8 * i, 4);
-        }
+        for (int i = 0; i < kJvpRing; ++i) mbar_init(bar_full + 8 * i, 8);
+        *reinterpret_cast<uint32_t*>(sm + JvpSmem::done) = 0u;
     }
     if (tid < kProducerThreads) {
         convert_weights_tf32(mlp, sm + JvpSmem::whi, sm + JvpSmem::wlo);
@@ -1155,7 +1164,7 @@ sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, con
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_empty + 8 * slot);        // this warp is done with the slot's E and J rows
+            if (lane == 0) counter_release_add(done_cnt);            // this warp is done with the slot's E and J rows
         }
     } else {
         // =============================== gather warps ===============================
@@ -1168,8 +1177,13 @@ sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, con
             lb_enc::Point q = {0.5f, 0.5f, 0.5f};
             if (valid) q = lb_enc::load_point<kFromRays>(rays, zv, x01, p, n_samples, nullptr);
             const uint32_t slot = kt % kJvpRing;
-            // the Jacobian goes to the slot level by level, so the slot must be free before the gathers start
-            if (kt >= kJvpRing) mbar_wait(bar_empty + 8 * slot, ((kt / kJvpRing) - 1) & 1u);
+            // The Jacobian goes to the slot level by level, so the slot must be free before the gathers start.  "Free" is a
+            // COUNT, not an mbarrier phase: a warp does not take part in every use of a slot (20 warps, 8 units per tile),
+            // and a parity wait can only tell the current phase from the one before it -- asked about phase n - 1 while the
+            // barrier is still in phase n - 3 it passes at once (seen on hardware: stale rows from the first reuse on).
+            // The MLP warps consume tiles in order and count them (4 increments per tile, release); tile kt may be written
+            // once tile kt - kJvpRing is done.
+            if (kt >= kJvpRing) counter_wait(done_cnt, 4u * (kt - kJvpRing + 1));
             uint8_t* base = sm + JvpSmem::ring + slot * kJvpSlot;
             float out[16];
             lb_enc::encode_fwd_jvp_point<kNDense>(T, q, half, table, out,
