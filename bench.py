@@ -623,7 +623,9 @@ def run_ours(args):
             "roofline": roofline,
             "e2e": {"value": n_rays * (1 if strong else world) * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                     "h2d_bytes_per_step": n_rays * 14 * 4, "d2h_bytes_per_step": 4, "last_loss": last_t.item(),
-                    "readback": "every step's loss is copied to pinned host memory and read by the host one step behind (event per step)"},
+                    "readback": "every step's loss is copied to pinned host memory and read by the host one step behind (event per step)",
+                    **({"note": "host ray buffers are world-frame rays, which carry no pose gradient: this leg is the map-only step; "
+                                "the pose chain (poses -> rays on the device -> dL/dpose) is in `value` only"} if W["pose_grad"] else {})},
             "gpu_launches": per_step_ours * args.steps if per_step_ours else abi_calls,
             "launches_per_step": launches, "c_abi_calls": abi_calls, "clocks": clk}
     if coll:

@@ -133,9 +133,12 @@ __device__ __forceinline__ void encode_fwd_point(const lb_level_table& T, const 
 // Pair exchange as for e: the even lane ends up with the three derivatives of feature 0, the odd lane with those of
 // feature 1, and writes them to its own 48-float run jac[l * 3 + d] (shared memory; 12 floats = 3 float4 per four
 // levels, so that the Jacobian never occupies more than 12 registers).
-template <int kNDense>
+// `before_first_store()` runs once, after the arithmetic of levels 0-3 and before the first write to `jac`: the caller
+// waits there for the destination to become free, so a quarter of the point's gathers overlap that wait.
+template <int kNDense, typename BeforeFirstStore>
 __device__ __forceinline__ void encode_fwd_jvp_point(const lb_level_table& T, const Point& q, int half,
-                                                     const float2* __restrict__ table, float* out, float4* jac) {
+                                                     const float2* __restrict__ table, float* out, float4* jac,
+                                                     BeforeFirstStore before_first_store) {
     float part[LB_MLP_IN];
     float jl[12];
 #pragma unroll
@@ -167,6 +170,7 @@ __device__ __forceinline__ void encode_fwd_jvp_point(const lb_level_table& T, co
         jl[g + 1] = L.scale * ((half ? yb : ya) + r1);
         jl[g + 2] = L.scale * ((half ? zb : za) + r2);
         if ((l & 3) == 3) {
+            if (l == 3) before_first_store();
             float4* dst = jac + (l >> 2) * 3;
             dst[0] = make_float4(jl[0], jl[1], jl[2], jl[3]);
             dst[1] = make_float4(jl[4], jl[5], jl[6], jl[7]);

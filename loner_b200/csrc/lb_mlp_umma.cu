@@ -531,6 +531,32 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
+// Monotonic "tiles consumed" counter in shared memory: how the gather warps of the fused forward kernels learn that a ring
+// slot is free.  A count instead of an mbarrier phase because a gather warp does not take part in every use of a slot
+// (28 or 20 warps, 8 units per tile, 2 slots), and a parity wait can only tell the current phase from the one before it:
+// asked about phase n - 1 while the barrier is still in phase n - 3 it passes at once.  The consumers (4 MLP warps) take the
+// tiles in order and add 1 each (release) when they are done with a tile's rows; tile kt may be written once
+// 4 * (kt - ring + 1) increments are visible (acquire).
+#ifndef LB_COUNTER_SLEEP_NS
+#define LB_COUNTER_SLEEP_NS 64
+#endif
+__device__ __forceinline__ void counter_release_add(uint32_t addr) {
+    asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;" ::"r"(addr) : "memory");
+}
+// called convergently by a whole warp: lane 0 polls (with a short sleep between polls, so that waiting warps do not take
+// issue slots and shared-memory cycles from the working ones), __syncwarp hands the acquired view to the other lanes
+__device__ __forceinline__ void counter_wait(uint32_t addr, uint32_t target) {
+    if ((threadIdx.x & 31) == 0) {
+        uint32_t v;
+        asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+        while (v < target) {
+            __nanosleep(LB_COUNTER_SLEEP_NS);
+            asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+        }
+    }
+    __syncwarp();
+}
+
 template <bool kFromRays, bool kInputGrad, int kNDense>
 __global__ void __launch_bounds__(FusedShape<kInputGrad>::kThreads, 1)
 sigma_bwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
@@ -772,7 +798,7 @@ sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
     extern __shared__ __align__(128) uint8_t sm[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t bar_mma = smem_u32(sm + FusedFwdSmem::bars);
-    const uint32_t bar_full = bar_mma + 16, bar_empty = bar_full + 8 * kFwdRing;
+    const uint32_t bar_full = bar_mma + 16, done_cnt = bar_full + 8 * kFwdRing;    // counter_wait / counter_release_add
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + FusedFwdSmem::tmem);
     float* w2s = reinterpret_cast<float*>(sm + FusedFwdSmem::w2);
     float* vs = reinterpret_cast<float*>(sm + FusedFwdSmem::v);
@@ -783,10 +809,8 @@ sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
     if (tid == 32) {
         mbar_init(bar_mma, 1);
         mbar_init(bar_mma + 8, 1);
-        for (int i = 0; i < kFwdRing; ++i) {
-            mbar_init(bar_full + 8 * i, 8);
-            mbar_init(bar_empty + 8 * i, 4);
-        }
+        for (int i = 0; i < kFwdRing; ++i) mbar_init(bar_full + 8 * i, 8);
+        *reinterpret_cast<uint32_t*>(sm + FusedFwdSmem::bars + 16 + 8 * kFwdRing) = 0u;     // done_cnt
     }
     if (tid < kProducerThreads) {
         convert_weights_tf32(mlp, sm + FusedFwdSmem::whi, sm + FusedFwdSmem::wlo);
@@ -837,7 +861,7 @@ sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
                     tmem_st16(t_alo + lane_off + h * 16, lo);
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar_empty + 8 * slot);    // the rows of this warp are in registers / TMEM
+                if (lane == 0) counter_release_add(done_cnt);        // the rows of this warp are in registers / TMEM
                 tmem_st_wait();
             }
             tc_fence_before();
@@ -900,7 +924,7 @@ sigma_fwd_fused_kernel(lb_level_table T, const float* __restrict__ rays, const f
             float out[16];
             lb_enc::encode_fwd_point<kNDense>(T, q, half, table, 0, 16, out);
             const uint32_t slot = kt % kFwdRing;
-            if (kt >= kFwdRing) mbar_wait(bar_empty + 8 * slot, ((kt / kFwdRing) - 1) & 1u);
+            if (kt >= kFwdRing) counter_wait(done_cnt, 4u * (kt - kFwdRing + 1));      // tile kt - ring has been consumed
             float4* dst = reinterpret_cast<float4*>(sm + FusedFwdSmem::ring + slot * kStage + row * kRowStride + half * 64);
 #pragma unroll
             for (int i = 0; i < 4; ++i) dst[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
@@ -958,11 +982,17 @@ int launch_fused_fwd(const lb_plan* plan, const lb_level_table& T, const float* 
 //
 // Pipeline per 128-point tile (MLP warps, thread t = point t): E row -> tf32 hi / lo -> TMEM; MMA H; epilogue (sigma, mask
 // bits) -> mask tile; MMA dE; TMEM -> registers; 96 FMAs against the J row; release the ring slot.  No double buffering:
-// the two MMA round trips (~1.5 us) are shorter than the gather time of a tile (~4 us).  20 gather warps (768 threads,
-// 80 registers: the Jacobian arithmetic does not fit the 64 registers of the 1024-thread forward).
-// ------------------------------------------------------------------------------------------
+// the two MMA round trips (~1.5 us) are shorter than the gather time of a tile (~5 us).
+//
+// What bounds it is shared memory, not L2: a point's Jacobian row is 384 B, so the two 68 KB ring slots hold 256 points =
+// 16 warp-units, and a 17th gather warp has nowhere to write.  Measured inside the c3 bench step (lb_sigma_fwd_jvp per
+// step, two 16384 x 512 chunks): 12 / 16 / 20 / 24 gather warps = 4.56 / 4.40 / 4.57 / 4.75 ms (the plain forward: 3.16);
+// with waiting warps spinning on the slot counter instead of sleeping, 16 / 20 / 24 = 4.48 / 4.96 / 5.29.  16 warps also
+// leave 96 registers per thread (no spills).  ncu: 47.9 tex sectors per point (L1 hit 21 % with 200 KB of the SM's 256 KB
+// configured as shared memory; the plain forward has 42.6), L2 37 % busy.  Next: Jacobian rows in tensor memory (96 of
+// the 352 free columns per tile) instead of shared memory.
 #ifndef LB_JVP_GATHER_WARPS
-#define LB_JVP_GATHER_WARPS 20
+#define LB_JVP_GATHER_WARPS 16
 #endif
 constexpr int kJvpGatherWarps = LB_JVP_GATHER_WARPS;
 constexpr int kJvpThreads = kProducerThreads + 32 * kJvpGatherWarps;
@@ -977,16 +1007,6 @@ struct JvpSmem {
 };
 static_assert(JvpSmem::total <= 227 * 1024, "shared memory of the jvp forward");
 
-// monotonic tile counter in shared memory (see the gather warps of sigma_fwd_jvp_fused_kernel)
-__device__ __forceinline__ void counter_release_add(uint32_t addr) {
-    asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;" ::"r"(addr) : "memory");
-}
-__device__ __forceinline__ void counter_wait(uint32_t addr, uint32_t target) {
-    uint32_t v;
-    do {
-        asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
-    } while (v < target);
-}
 
 template <bool kFromRays, int kNDense>
 __global__ void __launch_bounds__(kJvpThreads, 1)
@@ -1177,17 +1197,14 @@ sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, con
             lb_enc::Point q = {0.5f, 0.5f, 0.5f};
             if (valid) q = lb_enc::load_point<kFromRays>(rays, zv, x01, p, n_samples, nullptr);
             const uint32_t slot = kt % kJvpRing;
-            // The Jacobian goes to the slot level by level, so the slot must be free before the gathers start.  "Free" is a
-            // COUNT, not an mbarrier phase: a warp does not take part in every use of a slot (20 warps, 8 units per tile),
-            // and a parity wait can only tell the current phase from the one before it -- asked about phase n - 1 while the
-            // barrier is still in phase n - 3 it passes at once (seen on hardware: stale rows from the first reuse on).
-            // The MLP warps consume tiles in order and count them (4 increments per tile, release); tile kt may be written
-            // once tile kt - kJvpRing is done.
-            if (kt >= kJvpRing) counter_wait(done_cnt, 4u * (kt - kJvpRing + 1));
+            // the Jacobian goes to the slot level by level (12 floats per four levels), so the slot must be free before the
+            // first of those stores: the wait sits there, after the gathers of levels 0-3 (seen on hardware with mbarrier
+            // phases instead of the count: stale rows from the first reuse of a slot on)
             uint8_t* base = sm + JvpSmem::ring + slot * kJvpSlot;
             float out[16];
-            lb_enc::encode_fwd_jvp_point<kNDense>(T, q, half, table, out,
-                                                  reinterpret_cast<float4*>(base + kStage + row * kJacStride + half * 192));
+            lb_enc::encode_fwd_jvp_point<kNDense>(
+                T, q, half, table, out, reinterpret_cast<float4*>(base + kStage + row * kJacStride + half * 192),
+                [&]() { if (kt >= kJvpRing) counter_wait(done_cnt, 4u * (kt - kJvpRing + 1)); });
             float4* dst = reinterpret_cast<float4*>(base + row * kRowStride + half * 64);
 #pragma unroll
             for (int i = 0; i < 4; ++i) dst[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
