@@ -69,7 +69,8 @@ def parse_args():
                     help="c2 = BASELINE configs[1] (default, the headline); c3 / c4 / c5 = configs[2] / [3] / [4]")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-overlap", action="store_true",
-                    help="N > 1: synchronous parameter all-gather (A/B against the default, which overlaps it with the next step)")
+                    help="optimiser step in line on the main stream (A/B against the default: side stream, overlapped with the "
+                         "next step's ray build and sampler)")
     return ap.parse_args()
 
 
@@ -460,9 +461,10 @@ def run_ours(args):
     pose_params = [kf.get_lidar_pose().get_pose_tensor() for kf in window if not kf.is_anchored]
     if pose_params:
         groups.append({"params": pose_params, "lr": settings.model_config.train.lrate_pose})
-    # the parameter all-gather of step i overlaps the ray build / sampler of step i+1 (what Optimizer.iterate_optimizer
-    # does); compute_loss waits for it before the first field evaluation
-    adam = M.FusedAdam(groups, data_parallel=dp, overlap_param_gather=not args.no_overlap)
+    # the optimiser step of the field parameters (N > 1: reduce-scatter -> sharded Adam -> all-gather) runs on a side stream
+    # under the ray build / sampler of step i+1 (what Optimizer.iterate_optimizer does); compute_loss waits for it before
+    # the first field evaluation
+    adam = M.FusedAdam(groups, data_parallel=dp, overlap_step=not args.no_overlap)
     n_acc = settings.model_config.model.occ_model.N_iters_acc
     n_rays = W["keyframes"] * W["rays_per_keyframe"]
 
@@ -630,9 +632,9 @@ def run_ours(args):
             "launches_per_step": launches, "c_abi_calls": abi_calls, "clocks": clk}
     if coll:
         line["collectives_ms_per_step"] = {k: round(v[1] / coll_steps, 4) for k, v in sorted(coll.items())}
-        line["collectives_note"] = (f"separate pass of {coll_steps} steps with synchronous collectives; in the timed region the parameter "
-                                    "all-gather " + ("is synchronous too (--no-overlap)" if args.no_overlap else
-                                                     "overlaps the next step's ray build and sampler"))
+        line["collectives_note"] = (f"separate pass of {coll_steps} steps with the optimiser step in line; in the timed region it "
+                                    + ("is in line too (--no-overlap)" if args.no_overlap else
+                                       "runs on a side stream under the next step's ray build and sampler"))
     if not args.no_cpu_baseline and world == 1:
         r = cpu_reference_steps(10, 2, args.cpu_sample_rays)
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}

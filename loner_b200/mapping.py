@@ -290,7 +290,7 @@ class RayDataParallel:
         self.rank = dist.get_rank(group) if self.enabled else 0
         self.shard_batch = bool(shard_batch) and self.enabled
         self.events = None              # bench.py: list of (name, start, end) CUDA events around the collectives
-        self._param_work = []           # all-gathers of updated parameters still in flight (FusedAdam overlap)
+        self._param_work = []           # events of optimiser steps still in flight on a side stream (FusedAdam overlap_step)
 
     def rows(self, n):
         """Row range of this rank inside an n-row chunk (shard_batch)."""
@@ -329,21 +329,21 @@ class RayDataParallel:
     def reduce_scatter(self, out, flat):
         self._timed("reduce_scatter_grad", lambda: self.dist.reduce_scatter_tensor(out, flat, op=self.dist.ReduceOp.SUM, group=self.group))
 
-    def all_gather(self, flat, shard, overlap=False):
-        """overlap=True: the gather runs on NCCL's stream while the caller's stream goes on (next iteration's ray build,
-        normaliser count, sampler); whoever reads the parameters next must call wait_params() first.  While collectives
-        are being timed (self.events) every gather is synchronous so that its duration can be bracketed."""
+    def all_gather(self, flat, shard):
         # NCCL gathers in place (shard is the rank's slice of flat); other backends (gloo, CPU tests) get a copy
         src = shard if flat.is_cuda else shard.clone()
-        if overlap and self.events is None and flat.is_cuda:
-            self._param_work.append(self.dist.all_gather_into_tensor(flat, src, group=self.group, async_op=True))
-            return
         self._timed("all_gather_params", lambda: self.dist.all_gather_into_tensor(flat, src, group=self.group))
 
+    def defer(self, event):
+        """FusedAdam(overlap_step=True): `event` (recorded on the optimiser's side stream) marks the parameters complete."""
+        self._param_work.append(event)
+
     def wait_params(self):
-        """Makes the current stream wait for parameter all-gathers still in flight (no host wait)."""
-        for w in self._param_work:
-            w.wait()
+        """Makes the current stream wait for an optimiser step still in flight on its side stream (no host wait).  Called
+        before anything reads the field parameters: compute_loss / compute_loss_camera, the next step(), the end of
+        iterate_optimizer.  Works the same whether data parallelism is enabled or not."""
+        for ev in self._param_work:
+            torch.cuda.current_stream().wait_event(ev)
         self._param_work.clear()
 
 
@@ -467,7 +467,7 @@ class Optimizer:
                 kept.append((i + rows[0], i + rows[1]))
                 if r_c.shape[0] == 0:
                     continue
-            dp.wait_params()                  # an overlapped all-gather of the last Adam step ends here at the latest
+            dp.wait_params()                  # an optimiser step still in flight on its side stream ends here at the latest
             sigma = nerf.sigma_from_rays(r_c, z, sink)
             if norm_work is not None:
                 norm_work.wait()              # the current stream waits for the collective; the host does not
@@ -707,7 +707,7 @@ class Optimizer:
             self._model.freeze_rgb_head(False)
             params = self._model.get_rgb_parameters()
             self._optimizer = FusedAdam([{'params': params, 'lr': train.lrate_rgb}], data_parallel=self._dp,
-                                        overlap_param_gather=True)
+                                        overlap_step=True)
             gamma = train.lrate_gamma
             full, n_it = self._camera_schedule(keyframe_window, len(cam))
             s.num_iterations = n_it
@@ -769,9 +769,10 @@ class Optimizer:
                 groups.append({'params': self._model.get_sigma_parameters(), 'lr': train.lrate_sigma_mlp})
             if (tracking or optimize_poses) and poses:
                 groups.append({'params': poses, 'lr': train.lrate_pose})
-            # the parameter all-gather of a step overlaps the next iteration's ray build / sampler; compute_loss waits for
-            # it before the first field evaluation, and the loop's end below before anybody else can read the parameters
-            self._optimizer = FusedAdam(groups, data_parallel=self._dp, overlap_param_gather=True)
+            # the step of the field parameters (reduce-scatter, Adam, all-gather) runs on a side stream under the next
+            # iteration's ray build / sampler; compute_loss waits for it before the first field evaluation, and the
+            # loop's end below before anybody else can read the parameters
+            self._optimizer = FusedAdam(groups, data_parallel=self._dp, overlap_step=True)
             gamma = train.lrate_gamma
             fixed_full = None
             if self._settings.rays_selection.strategy == 'FIXED':

@@ -21,13 +21,19 @@ from . import ops
 
 
 class FusedAdam(torch.optim.Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, data_parallel=None, overlap_param_gather=False):
-        """overlap_param_gather: the all-gather of the updated parameters is left in flight when step() returns; the
-        caller must run data_parallel.wait_params() before the parameters are read again (Optimizer.compute_loss does).
-        Off by default: step() then returns with complete parameters on the current stream."""
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, data_parallel=None, overlap_step=False):
+        """overlap_step: the step of the large flat parameter vectors (gradient reduce-scatter, lb_adam_step,
+        parameter all-gather) runs on a side stream and is still in flight when step() returns, so that it overlaps what
+        the caller launches next without reading those parameters -- the next iteration's ray build, normaliser count
+        and sampler (issue-bound kernels; Adam is an HBM stream, the collectives are NVLink).  The caller must run
+        data_parallel.wait_params() before the parameters are read again (Optimizer.compute_loss does); `data_parallel`
+        (a RayDataParallel, enabled or not) holds that fence.  Small tensors (pose 6-vectors, which the next ray build
+        reads) are always stepped on the caller's stream.  Off by default: step() returns with complete parameters."""
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+        self._fence = data_parallel
         self._dp = data_parallel if (data_parallel is not None and data_parallel.enabled) else None
-        self._overlap = bool(overlap_param_gather)
+        self._overlap = bool(overlap_step) and data_parallel is not None
+        self._side = {}
 
     @staticmethod
     def _fast(p, g):
@@ -89,45 +95,67 @@ class FusedAdam(torch.optim.Optimizer):
 
     @torch.no_grad()
     def step(self, closure=None, grad_scale=1.0):
-        dp = self._dp
-        if dp is not None:
-            dp.wait_params()           # a gather still in flight writes the slices this step is about to update
+        if self._fence is not None:
+            self._fence.wait_params()  # a step still in flight writes the parameters / moments this one updates
+        large = []
         for group in self.param_groups:
-            b1, b2 = group["betas"]
             small = [p for p in group["params"] if p.grad is not None and p.numel() < 1024]
             if small:
                 self._step_small(group, small, grad_scale)
-            for p in group["params"]:
-                if p.grad is None or p.numel() < 1024:
-                    continue
-                st = self.state[p]
-                g = p.grad
-                n = p.numel()
-                sharded = dp is not None and n >= 4096 and n % (4 * dp.world_size) == 0 and p.is_contiguous() and g.is_contiguous()
-                if not st:
-                    st["step"] = 0
-                    if sharded:
-                        k = n // dp.world_size
-                        st["exp_avg"] = torch.zeros(k, device=p.device, dtype=p.dtype)
-                        st["exp_avg_sq"] = torch.zeros(k, device=p.device, dtype=p.dtype)
-                        st["grad_shard"] = torch.empty(k, device=p.device, dtype=p.dtype)
-                    else:
-                        st["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
-                        st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
-                st["step"] += 1
-                args = (st["step"], group["lr"], b1, b2, group["eps"], grad_scale)
-                if sharded:
-                    k = n // dp.world_size
-                    flat = p.data.view(-1)
-                    mine = flat[dp.rank * k:(dp.rank + 1) * k]
-                    dp.reduce_scatter(st["grad_shard"], g.view(-1))
-                    self._update(mine, st["grad_shard"], st["exp_avg"], st["exp_avg_sq"], *args)
-                    dp.all_gather(flat, mine, overlap=self._overlap)
-                    continue
-                if dp is not None:
-                    dp.all_reduce_(g, "all_reduce_grad")
-                if self._fast(p, g):
-                    self._update(p.data.view(-1), g.view(-1), st["exp_avg"].view(-1), st["exp_avg_sq"].view(-1), *args)
-                else:
-                    self._update(p, g, st["exp_avg"], st["exp_avg_sq"], *args)
+            large += [(group, p) for p in group["params"] if p.grad is not None and p.numel() >= 1024]
+        if not large:
+            return None
+        dev = large[0][1].device
+        timing = self._dp is not None and self._dp.events is not None     # bench.py brackets the collectives: keep them in line
+        if not (self._overlap and dev.type == "cuda" and not timing):
+            for group, p in large:
+                self._step_large(group, p, grad_scale)
+            return None
+        main = torch.cuda.current_stream(dev)
+        side = self._side.get(dev)
+        if side is None:
+            side = self._side[dev] = torch.cuda.Stream(dev)
+        side.wait_stream(main)                                            # the gradients are complete
+        with torch.cuda.stream(side):
+            for group, p in large:
+                self._step_large(group, p, grad_scale)
+        for _, p in large:
+            p.grad.record_stream(side)         # zero_grad(set_to_none=True) may free it while the side stream still reads it
+        done = torch.cuda.Event()
+        done.record(side)
+        self._fence.defer(done)
         return None
+
+    def _step_large(self, group, p, grad_scale):
+        dp = self._dp
+        b1, b2 = group["betas"]
+        st = self.state[p]
+        g = p.grad
+        n = p.numel()
+        sharded = dp is not None and n >= 4096 and n % (4 * dp.world_size) == 0 and p.is_contiguous() and g.is_contiguous()
+        if not st:
+            st["step"] = 0
+            if sharded:
+                k = n // dp.world_size
+                st["exp_avg"] = torch.zeros(k, device=p.device, dtype=p.dtype)
+                st["exp_avg_sq"] = torch.zeros(k, device=p.device, dtype=p.dtype)
+                st["grad_shard"] = torch.empty(k, device=p.device, dtype=p.dtype)
+            else:
+                st["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+        st["step"] += 1
+        args = (st["step"], group["lr"], b1, b2, group["eps"], grad_scale)
+        if sharded:
+            k = n // dp.world_size
+            flat = p.data.view(-1)
+            mine = flat[dp.rank * k:(dp.rank + 1) * k]
+            dp.reduce_scatter(st["grad_shard"], g.view(-1))
+            self._update(mine, st["grad_shard"], st["exp_avg"], st["exp_avg_sq"], *args)
+            dp.all_gather(flat, mine)
+            return
+        if dp is not None:
+            dp.all_reduce_(g, "all_reduce_grad")
+        if self._fast(p, g):
+            self._update(p.data.view(-1), g.view(-1), st["exp_avg"].view(-1), st["exp_avg_sq"].view(-1), *args)
+        else:
+            self._update(p, g, st["exp_avg"], st["exp_avg_sq"], *args)

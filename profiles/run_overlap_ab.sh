@@ -1,6 +1,6 @@
 #!/bin/bash
-# profiles/run_overlap_ab.sh <N>: A/B of the overlapped parameter all-gather (default) against --no-overlap, c4 weak and
-# c2 strong at N ranks, A-B-A order; one torchrun per line under its own timeout -> gpurun_out/r02_overlap_*.json
+# profiles/run_overlap_ab.sh <N>: A/B of the side-stream optimiser step (default) against --no-overlap (in line), c4 weak and
+# c2 strong at N ranks, A-B-A order; one torchrun (or plain python at N = 1) per line under its own timeout -> gpurun_out/r02_overlap_*.json
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 port=29700
@@ -8,7 +8,7 @@ run() {  # tag workload scaling N extra
   port=$((port + 1))
   out=gpurun_out/r02_overlap_$2_$3_$4_$1.json
   timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $4 --master-addr 127.0.0.1 --master-port $port \
-      bench.py --gpus $4 --workload $2 --scaling $3 --steps 30 --warmup 5 $5 > $out 2> ${out%.json}.err
+      bench.py --gpus $4 --workload $2 --scaling $3 --steps 30 --warmup 5 --no-cpu-baseline $5 > $out 2> ${out%.json}.err
   python - "$out" "$@" <<'PY' || { grep -v "^W1105\|^  File\|^    \|frame #" ${out%.json}.err | tail -15; }
 import json, sys
 d = json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])

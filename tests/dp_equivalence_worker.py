@@ -42,8 +42,9 @@ def run(dev, dp, g, state, M, R, params0):
 
 
 def train(dev, dp, g, state, M, R, params0, overlap, n_steps=4):
-    """n_steps of compute_loss -> backward -> sharded Adam on the same batch; with `overlap` the parameter all-gather of
-    each step is left in flight and compute_loss's wait_params() is what orders it before the next field evaluation."""
+    """n_steps of compute_loss -> backward -> sharded Adam on the same batch; with `overlap` the optimiser step (reduce-
+    scatter, Adam, all-gather) runs on a side stream and compute_loss's wait_params() orders it before the next field
+    evaluation."""
     s = M.default_settings(n_samples_train=g["n_samples"], log2_hashmap_size=g["log2_T"], ray_range=tuple(g["ray_range"]),
                            voxel_size=g["voxel"], loss_selection=g["states"][state]["loss_selection"], strategy="OGM", chunk=g["chunk"])
     opt = M.Optimizer(s, None, M.WorldCube(g["scale"], g["shift"]), dev, data_parallel=dp)
@@ -51,7 +52,7 @@ def train(dev, dp, g, state, M, R, params0, overlap, n_steps=4):
     with torch.no_grad():
         p.copy_(params0.to(dev))
         opt._occupancy_grid.copy_(g["occ"].to(dev))
-    adam = M.FusedAdam([{"params": [p], "lr": 0.01}], data_parallel=dp, overlap_param_gather=overlap)
+    adam = M.FusedAdam([{"params": [p], "lr": 0.01}], data_parallel=dp, overlap_step=overlap)
     rays, depths = g["rays"].to(dev), g["depths"].to(dev)
     losses = []
     for i in range(n_steps):
@@ -110,8 +111,8 @@ def main():
     lst = [torch.zeros_like(chk) for _ in range(world)]
     dist.all_gather(lst, chk)
     report["params_identical_across_ranks"] = bool(all(torch.equal(lst[0], t) for t in lst))
-    # overlapped parameter all-gather (what Optimizer.iterate_optimizer runs) against the synchronous one: a gather that
-    # a field evaluation did not wait for would leave the other ranks' slices one step stale and bend the loss curve.
+    # side-stream optimiser step (what Optimizer.iterate_optimizer runs) against the in-line one: a step that a field
+    # evaluation did not wait for would leave the parameters one step stale and bend the loss curve.
     # Not bit-equal by construction: the table gradients are fp32 atomics, their order differs from run to run.
     p_sync, l_sync = train(dev, dp, g, state, M, R, params0, overlap=False)
     p_over, l_over = train(dev, dp, g, state, M, R, params0, overlap=True)

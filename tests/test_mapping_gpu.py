@@ -605,3 +605,32 @@ def test_store_ray_return_and_timing_csv(tmp_path):
         n_its, elapsed = ln.split(",")
         assert int(n_its) == 4 and 0.0 < float(elapsed) < 60.0
     assert len(opt2.debug_rays["rays"]) == 4 and opt2.debug_rays["std"][0].shape == (128,)
+
+
+def test_fused_adam_side_stream_step_equals_inline_step():
+    """FusedAdam(overlap_step=True): the step of the large parameter vector runs on a side stream and the fence
+    (RayDataParallel.wait_params, here with data parallelism off) orders it before the next read; poses are stepped in
+    line.  Same kernels on the same data: bit-identical to the in-line step."""
+    from loner_b200 import mapping as M
+    fence = M.RayDataParallel()
+    assert not fence.enabled
+    res = []
+    for overlap in (False, True):
+        torch.manual_seed(0)
+        p = torch.randn(1 << 20, device=DEV).requires_grad_(True)
+        pose = torch.randn(6, device=DEV).requires_grad_(True)
+        adam = M.FusedAdam([{"params": [p], "lr": 1e-2}, {"params": [pose], "lr": 1e-3}], data_parallel=fence, overlap_step=overlap)
+        for i in range(6):
+            fence.wait_params()                                   # what compute_loss does before the first field evaluation
+            loss = 0.5 * (p * p).sum() + (i + 1) * p.sin().sum() + (pose ** 2).sum()
+            loss.backward()
+            adam.step()
+            adam.zero_grad(set_to_none=True)
+            if overlap:
+                assert len(fence._param_work) == 1                # the step is in flight behind an event
+            torch.randn(1 << 22, device=DEV).sort()               # main-stream work that does not touch p (the next ray build)
+            _ = (pose * 2).sum()                                  # poses are complete on the main stream right away
+        fence.wait_params()
+        torch.cuda.synchronize()
+        res.append((p.detach().clone(), pose.detach().clone()))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
