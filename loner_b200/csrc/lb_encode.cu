@@ -107,9 +107,17 @@ encode_fwd_lm_kernel(lb_level_table T, const float* __restrict__ rays, const flo
 // the reductions) per warp, so residency, not instruction count, sets its speed (the 16-level general kernel at 6 blocks
 // per SM took 0.40 ms per single-level pass of 8.4 M points, this one 0.29 ms; 16 blocks per SM changed nothing: the L2
 // reduction rate binds).  Same run merging on the coarse levels
-// as lb_enc::encode_bwd_point (kAggLevelsScatter / kAggMaxRunsScatter).
+// as lb_enc::encode_bwd_point, with its own thresholds (below).
 #ifndef LB_BWD_LM_BLOCKS
 #define LB_BWD_LM_BLOCKS 12
+#endif
+// Run merging (lb_encode.cuh) in the level-major passes: levels below LB_AGG_LEVELS_LM merge runs of equal cells before
+// the reductions when the warp's 16 points fall into <= LB_AGG_MAX_RUNS_LM cells.  Measured inside the c4 bench step
+// (T = 2^22, lb_sigma_bwd per step, profiles/run_variants.sh): (levels, runs) = (0, -) 21.56 ms -- merging is what makes
+// the coarse levels affordable -- (4, 15) 8.41, (6, 15) 8.17, (8, 15) 8.24, (12, 15) 8.31, (8, 8) 8.15.
+#ifndef LB_AGG_LEVELS_LM
+#define LB_AGG_LEVELS_LM 8
+#define LB_AGG_MAX_RUNS_LM 8
 #endif
 template <bool kFromRays>
 __global__ void __launch_bounds__(kThreads, LB_BWD_LM_BLOCKS)
@@ -141,7 +149,7 @@ encode_bwd_lm_kernel(lb_level_table T, const float* __restrict__ rays, const flo
                 b[k] = w * d.y;
             }
             bool issue = valid && nonzero;
-            if (l < kAggLevelsScatter && !all_distinct) {
+            if (l < LB_AGG_LEVELS_LM && !all_distinct) {
                 const uint32_t pcx = __shfl_up_sync(kFull, s.cx, 2), pcy = __shfl_up_sync(kFull, s.cy, 2),
                                pcz = __shfl_up_sync(kFull, s.cz, 2);
                 const int pvalid = __shfl_up_sync(kFull, (int)valid, 2);
@@ -150,7 +158,7 @@ encode_bwd_lm_kernel(lb_level_table T, const float* __restrict__ rays, const flo
                 const int runs = __popc(heads);
                 if (runs == 16) {
                     all_distinct = true;
-                } else if (runs <= kAggMaxRunsScatter) {
+                } else if (runs <= LB_AGG_MAX_RUNS_LM) {
                     const unsigned rest = (pair < 15) ? (heads >> (2 * pair + 2)) : 0u;
                     const int dist = rest ? 1 + ((__ffs(rest) - 1) >> 1) : 16 - pair;
 #pragma unroll

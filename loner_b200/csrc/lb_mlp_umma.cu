@@ -41,9 +41,15 @@ constexpr int kThreads = 128;
 constexpr uint32_t kLboP = kTile * 16 + 16;        // chunk stride of a 128-row tile (points)
 constexpr uint32_t kLboW = LB_MLP_W * 16 + 16;     // chunk stride of a 64-row tile (hidden units)
 constexpr uint32_t kTmemCols = 64;
-// resident CTAs per SM (shared memory 49.7 KB forward / 42.5 KB backward, 64 TMEM columns each)
-constexpr int kFwdCtasPerSm = 4;
-constexpr int kBwdCtasPerSm = 3;
+// resident CTAs per SM (shared memory 49.7 KB forward / 42.5 KB backward, 64 TMEM columns each: 4 x 64 <= 512 columns)
+#ifndef LB_MLP_FWD_CTAS
+#define LB_MLP_FWD_CTAS 4
+#endif
+#ifndef LB_MLP_BWD_CTAS      // c4 bench step (level-major planes, T = 2^22): 3 / 4 / 5 CTAs per SM = 14.10 / 14.04 / 14.41 ms
+#define LB_MLP_BWD_CTAS 4
+#endif
+constexpr int kFwdCtasPerSm = LB_MLP_FWD_CTAS;
+constexpr int kBwdCtasPerSm = LB_MLP_BWD_CTAS;
 
 
 // A 128 x 32 fp32 tile (row-major in global memory, 8 float4 per row) is handled "flat": in pass i thread t owns

@@ -110,7 +110,7 @@ class SigmaFromRays(torch.autograd.Function):
         rays_c, z_c = rays.detach().contiguous(), z.detach().contiguous()
         need_grad = params.requires_grad or rays.requires_grad
         dsdx = None
-        if rays.requires_grad and plan.jvp_supported:
+        if ctx.needs_input_grad[2] and plan.jvp_supported:   # (false under torch.no_grad even if the pose tensors train)
             # pose refinement: d sigma / d x01 comes out of the forward kernel (forward mode), so the backward is the
             # table-gradient kernel plus a per-ray reduction instead of a second gather of all 128 corners per point
             sigma, saved, dsdx = ops.sigma_fwd_jvp(plan, params.detach(), rays=rays_c, z=z_c, save_enc=params.requires_grad)
@@ -160,7 +160,7 @@ class SigmaFromPoints(torch.autograd.Function):
         x_c = x01.detach().contiguous()
         need_grad = params.requires_grad or x01.requires_grad
         dsdx = None
-        if x01.requires_grad and plan.jvp_supported:       # see SigmaFromRays: d sigma / d x01 from the forward kernel
+        if ctx.needs_input_grad[2] and plan.jvp_supported:       # see SigmaFromRays: d sigma / d x01 from the forward kernel
             sigma, saved, dsdx = ops.sigma_fwd_jvp(plan, params.detach(), x01=x_c, save_enc=params.requires_grad)
         else:
             sigma, saved = ops.sigma_fwd(plan, params.detach(), x01=x_c, save_enc=need_grad)
