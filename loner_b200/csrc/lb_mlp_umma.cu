@@ -1228,17 +1228,285 @@ sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, con
     if (warp == 0) tmem_dealloc(tmem, kJvpTmemCols);
 }
 
+// ------------------------------------------------------------------------------------------
+// The same operation with the Jacobian rows in TENSOR MEMORY instead of shared memory.  sigma_fwd_jvp_fused_kernel above
+// is bound by shared-memory capacity (256 points in flight).  Tensor memory has room: H 64 + A 64 + dE 32 columns are in
+// use, a tile's Jacobian is 96 columns (lane = point), so three tiles fit the remaining 352.  A warp may only touch the
+// TMEM lanes of its own quarter (warp id % 4) and a thread only its own lane, so the gather is reorganised: ONE LANE PER
+// POINT (all eight corners of a level in one lane, no pair exchange), a gather warp owns the 32-row quarter
+// q = warp id % 4 of every third tile and writes its points' Jacobian with tcgen05.st straight from registers, 24
+// columns per four levels.  Only the encoding rows still pass through shared memory (3 slots x 18 KB, also the staging
+// for the coalesced `enc` store), so shared memory drops from 181 KB to 97 KB and the L1 gets the difference back.
+// 12 gather warps x 32 points = 384 points in flight, 128 registers per thread.  MLP warps as above, with the contraction
+// reading J through tcgen05.ld (thread t = TMEM lane t).
+// ------------------------------------------------------------------------------------------
+constexpr int kJtGatherWarps = 12;
+constexpr int kJtThreads = kProducerThreads + 32 * kJtGatherWarps;
+constexpr int kJtRing = 3;
+constexpr uint32_t kJtTmemCols = 512;              // H 64 | A hi 32 | A lo 32 | dE 32 | J0 96 | J1 96 | J2 96 (448 used)
+constexpr uint32_t kJtColJ = 160;
+struct JtSmem {
+    static constexpr uint32_t ring = 0, mt = ring + kJtRing * kStage, wa = mt + kMaskT, wb = wa + kPieceW,
+                              whi = wb + kPieceW, wlo = whi + 8 * kLboW, w2 = wlo + 8 * kLboW, v = w2 + 64 * 4,
+                              bars = v + 32 * 4, done = bars + 8 * (2 + kJtRing), tmem = done + 8, total = tmem + 8;
+};
+
+template <bool kFromRays, int kNDense>
+__global__ void __launch_bounds__(kJtThreads, 1)
+sigma_fwd_jvp_tmem_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
+                          const float* __restrict__ x01, const float* __restrict__ mlp, const float2* __restrict__ table,
+                          size_t n_points, int n_samples, float* __restrict__ sigma, float* __restrict__ enc,
+                          unsigned long long* __restrict__ act, float* __restrict__ dsigma_dx) {
+    extern __shared__ __align__(128) uint8_t sm[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t bar_h = smem_u32(sm + JtSmem::bars), bar_de = bar_h + 8;
+    const uint32_t bar_full = bar_h + 16, done_cnt = smem_u32(sm + JtSmem::done);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + JtSmem::tmem);
+    float* w2s = reinterpret_cast<float*>(sm + JtSmem::w2);
+    float* vs = reinterpret_cast<float*>(sm + JtSmem::v);
+    const size_t n_tiles = (n_points + kTile - 1) / kTile;
+    const size_t my_tiles = fused_rounds(n_tiles);
+
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kJtTmemCols);
+    if (tid == 32) {
+        mbar_init(bar_h, 1);
+        mbar_init(bar_de, 1);
+        for (int i = 0; i < kJtRing; ++i) mbar_init(bar_full + 8 * i, 4);      // four quarter-warps per tile
+        *reinterpret_cast<uint32_t*>(sm + JtSmem::done) = 0u;
+    }
+    if (tid < kProducerThreads) {
+        convert_weights_tf32(mlp, sm + JtSmem::whi, sm + JtSmem::wlo);
+        const float* w2 = mlp + LB_MLP_W * LB_MLP_IN;
+        if (tid < LB_MLP_W) w2s[tid] = 0.5f * __ldg(w2 + tid);
+        if (tid >= 64 && tid < 64 + LB_MLP_IN) {
+            const int k = tid - 64;
+            float a = 0.0f;
+            for (int j = 0; j < LB_MLP_W; ++j) a = fmaf(0.5f * __ldg(w2 + j), __ldg(mlp + j * LB_MLP_IN + k), a);
+            vs[k] = a;
+        }
+        for (int it = tid; it < LB_MLP_W * 4; it += kProducerThreads) {
+            const int j = it >> 2, c = it & 3;
+            const float sc = __ldg(w2 + j);
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = __ldg(mlp + j * LB_MLP_IN + c * 8 + e) * sc;
+            uint32_t b1[4], b2[4];
+            split8<false>(v, b1, b2, nullptr);
+            *reinterpret_cast<uint4*>(sm + JtSmem::wa + tile_off(j, c, kLboW)) = make_uint4(b1[0], b1[1], b1[2], b1[3]);
+            *reinterpret_cast<uint4*>(sm + JtSmem::wb + tile_off(j, c, kLboW)) = make_uint4(b2[0], b2[1], b2[2], b2[3]);
+        }
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp < 4) {
+        // =============================== MLP warps ===============================
+        const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+        const uint32_t bhi = smem_u32(sm + JtSmem::whi), blo = smem_u32(sm + JtSmem::wlo);
+        const uint32_t mt = smem_u32(sm + JtSmem::mt), wa = smem_u32(sm + JtSmem::wa), wb = smem_u32(sm + JtSmem::wb);
+        const uint32_t t_h = tmem, t_ahi = tmem + 64, t_alo = tmem + 96, t_de = tmem + 128;
+        constexpr uint32_t idesc_h = umma_idesc_tf32(128, LB_MLP_W);
+        constexpr uint32_t idesc_de = umma_idesc(128, LB_MLP_IN, 0, 1);
+        for (uint32_t kt = 0; kt < my_tiles; ++kt) {
+            const uint32_t slot = kt % kJtRing, par = kt & 1u;
+            mbar_wait(bar_full + 8 * slot, (kt / kJtRing) & 1u);
+            tc_fence_after();                                        // the gather warps' tcgen05.st of this tile's J
+            const uint8_t* row = sm + JtSmem::ring + slot * kStage + tid * kRowStride;
+            float lin = 0.0f;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                uint32_t hi[16], lo[16];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 v = *reinterpret_cast<const float4*>(row + (h * 4 + q) * 16);
+                    const float4 c = *reinterpret_cast<const float4*>(vs + (h * 4 + q) * 4);
+                    lin = fmaf(v.x, c.x, lin); lin = fmaf(v.y, c.y, lin);
+                    lin = fmaf(v.z, c.z, lin); lin = fmaf(v.w, c.w, lin);
+                    uint4 a, d;
+                    split_tf32(v, a, d);
+                    hi[4 * q] = a.x; hi[4 * q + 1] = a.y; hi[4 * q + 2] = a.z; hi[4 * q + 3] = a.w;
+                    lo[4 * q] = d.x; lo[4 * q + 1] = d.y; lo[4 * q + 2] = d.z; lo[4 * q + 3] = d.w;
+                }
+                tmem_st16(t_ahi + lane_off + h * 16, hi);
+                tmem_st16(t_alo + lane_off + h * 16, lo);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            producer_barrier();
+            if (tid == 0) {
+                tc_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const uint64_t dbh = umma_desc(bhi + ks * 2 * kLboW, kLboW, 128);
+                    const uint64_t dbl = umma_desc(blo + ks * 2 * kLboW, kLboW, 128);
+                    umma_tf32_ts(t_h, t_ahi + ks * 8, dbh, idesc_h, ks > 0);
+                    umma_tf32_ts(t_h, t_ahi + ks * 8, dbl, idesc_h, 1);
+                    umma_tf32_ts(t_h, t_alo + ks * 8, dbh, idesc_h, 1);
+                }
+                umma_commit(bar_h);
+            }
+            mbar_wait(bar_h, par);
+            tc_fence_after();
+            float s = lin;
+            unsigned long long bits = 0ull;
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                uint32_t r[32];
+                tmem_ld32(t_h + lane_off + half * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int g = 0; g < 2; ++g) {
+                    float mf = 0.0f;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float h = __uint_as_float(r[g * 16 + j]);
+                        s = fmaf(w2s[half * 32 + g * 16 + j], fabsf(h), s);
+                        mf = fmaf(__saturatef(h * 8.507059173e37f), (float)(1u << j), mf);
+                    }
+                    const uint32_t m16 = __float_as_uint(mf + 8388608.0f) & 0xffffu;
+                    bits |= (unsigned long long)m16 << (32 * half + 16 * g);
+                }
+            }
+            const size_t p = fused_tile(kt) * (size_t)kTile + tid;
+            if (p < n_points) {
+                sigma[p] = s;
+                if (act) act[p] = bits;
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint32_t b = (uint32_t)(bits >> (8 * c)) & 0xffu;
+                uint4 v;
+                v.x = ((b & 1u) ? 0x3f80u : 0u) | ((b & 2u) ? 0x3f800000u : 0u);
+                v.y = ((b & 4u) ? 0x3f80u : 0u) | ((b & 8u) ? 0x3f800000u : 0u);
+                v.z = ((b & 16u) ? 0x3f80u : 0u) | ((b & 32u) ? 0x3f800000u : 0u);
+                v.w = ((b & 64u) ? 0x3f80u : 0u) | ((b & 128u) ? 0x3f800000u : 0u);
+                *reinterpret_cast<uint4*>(sm + JtSmem::mt + tile_off(tid, c, kLboP)) = v;
+            }
+            fence_async_smem();
+            tc_fence_before();
+            producer_barrier();
+            if (tid == 0) {
+                tc_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const uint64_t da = umma_desc(mt + ks * 2 * kLboP, kLboP, 128);
+                    umma_bf16(t_de, da, umma_desc(wa + ks * 256, 128, kLboW), idesc_de, ks > 0);
+                    umma_bf16(t_de, da, umma_desc(wb + ks * 256, 128, kLboW), idesc_de, 1);
+                }
+                umma_commit(bar_de);
+            }
+            mbar_wait(bar_de, par);
+            tc_fence_after();
+            {
+                uint32_t de[32];
+                tmem_ld32(t_de + lane_off, de);
+                tmem_ld_wait();
+                // d sigma / d x01[d] = sum_{l,f} dE[2l + f] J[l * 6 + f * 3 + d]; J = 96 TMEM columns of this lane
+                const uint32_t t_j = tmem + kJtColJ + slot * 96 + lane_off;
+                float g[3] = {0.0f, 0.0f, 0.0f};
+#pragma unroll
+                for (int c3 = 0; c3 < 3; ++c3) {
+                    uint32_t jr[32];
+                    tmem_ld32(t_j + c3 * 32, jr);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const int col = c3 * 32 + i;                 // = l * 6 + f * 3 + d
+                        g[col % 3] = fmaf(__uint_as_float(de[2 * (col / 6) + (col % 6) / 3]), __uint_as_float(jr[i]), g[col % 3]);
+                    }
+                }
+                if (p < n_points) {
+                    dsigma_dx[3 * p + 0] = g[0];
+                    dsigma_dx[3 * p + 1] = g[1];
+                    dsigma_dx[3 * p + 2] = g[2];
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) counter_release_add(done_cnt);            // this warp is done with the slot's E rows and J columns
+        }
+    } else {
+        // =============================== gather warps: one lane per point ===============================
+        const int g = warp - 4, q4 = g & 3, grp = g >> 2;            // (g + 4) % 4 == q4: the TMEM lane quarter of this warp
+        const uint32_t lane_off = (uint32_t)(q4 * 32) << 16;
+        for (uint32_t kt = grp; kt < my_tiles; kt += kJtRing) {
+            const uint32_t slot = kt % kJtRing;                      // == grp: a warp always fills the same slot
+            const int row = q4 * 32 + lane;
+            const size_t p = fused_tile(kt) * (size_t)kTile + row;
+            const bool valid = p < n_points;
+            lb_enc::Point pt = {0.5f, 0.5f, 0.5f};
+            if (valid) pt = lb_enc::load_point<kFromRays>(rays, zv, x01, p, n_samples, nullptr);
+            const uint32_t t_j = tmem + kJtColJ + slot * 96 + lane_off;
+            float e[LB_MLP_IN];
+            uint32_t jl[24];
+#pragma unroll
+            for (int l = 0; l < 16; ++l) {
+                float jac[6];
+                lb_enc::encode_jvp_level<kNDense>(T.lv[l], pt, l, table, e + 2 * l, jac);
+#pragma unroll
+                for (int i = 0; i < 6; ++i) jl[(l & 3) * 6 + i] = __float_as_uint(jac[i]);
+                if ((l & 3) == 3) {
+                    if (l == 3 && kt >= kJtRing) {                   // the slot (J columns and E rows) of tile kt - 3 is free
+                        counter_wait(done_cnt, 4u * (kt - kJtRing + 1));
+                        tc_fence_after();
+                    }
+                    tmem_st8(t_j + (l >> 2) * 24, jl);              // three 8-column stores: every one starts at a multiple of 8
+                    tmem_st8(t_j + (l >> 2) * 24 + 8, jl + 8);
+                    tmem_st8(t_j + (l >> 2) * 24 + 16, jl + 16);
+                }
+            }
+            uint8_t* base = sm + JtSmem::ring + slot * kStage;
+            float4* dst = reinterpret_cast<float4*>(base + row * kRowStride);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) dst[i] = make_float4(e[4 * i], e[4 * i + 1], e[4 * i + 2], e[4 * i + 3]);
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_full + 8 * slot);
+            if (enc) {
+                // coalesced copy of the quarter's 32 rows x 128 B out of the slot (nobody writes these rows before this
+                // warp's next tile): per iteration 4 rows = 512 contiguous bytes
+                const size_t first = fused_tile(kt) * (size_t)kTile + q4 * 32;
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const int r = it * 4 + (lane >> 3);
+                    if (first + r < n_points) {
+                        const float4 v = *reinterpret_cast<const float4*>(base + (q4 * 32 + r) * kRowStride + (lane & 7) * 16);
+                        __stcs(reinterpret_cast<float4*>(enc + (first + r) * LB_MLP_IN) + (lane & 7), v);
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, kJtTmemCols);
+}
+
+#ifndef LB_JVP_TMEM
+#define LB_JVP_TMEM 0
+#endif
+
 template <bool kFromRays, int kNDense>
 int launch_fused_fwd_jvp_src(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* x01,
                              const float* params, size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act,
                              float* dsigma_dx, cudaStream_t st) {
+#if LB_JVP_TMEM
+    auto kern = sigma_fwd_jvp_tmem_kernel<kFromRays, kNDense>;
+    constexpr int kSmemBytes = (int)JtSmem::total, kBlock = kJtThreads;
+#else
     auto kern = sigma_fwd_jvp_fused_kernel<kFromRays, kNDense>;
-    int rc = lb_check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JvpSmem::total),
+    constexpr int kSmemBytes = (int)JvpSmem::total, kBlock = kJvpThreads;
+#endif
+    int rc = lb_check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes),
                            "sigma_fwd_jvp_fused smem opt-in");
     if (rc) return rc;
     const size_t tiles = (n_points + kTile - 1) / kTile;
     const size_t cap = (size_t)plan->sm_count;
-    kern<<<(int)(tiles < cap ? tiles : cap), kJvpThreads, JvpSmem::total, st>>>(
+    kern<<<(int)(tiles < cap ? tiles : cap), kBlock, kSmemBytes, st>>>(
         T, rays, z, x01, params, reinterpret_cast<const float2*>(params + LB_MLP_PARAMS), n_points, n_samples, sigma, enc,
         reinterpret_cast<unsigned long long*>(act), dsigma_dx);
     return lb_check_cuda(cudaGetLastError(), "sigma_fwd_jvp_fused launch");
