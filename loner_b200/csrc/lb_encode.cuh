@@ -131,14 +131,13 @@ __device__ __forceinline__ void encode_fwd_point(const lb_level_table& T, const 
 //   d/dx = scale * (A(x+1) - A(x)),               A = sum_k wy wz v[k]   (the e value before the x weight)
 //   d/dy = scale * wx * (wz0 (v1 - v0) + wz1 (v3 - v2)),  d/dz likewise, summed over the two x-sides.
 // Pair exchange as for e: the even lane ends up with the three derivatives of feature 0, the odd lane with those of
-// feature 1, and writes them to its own 48-float run jac[l * 3 + d] (shared memory; 12 floats = 3 float4 per four
-// levels, so that the Jacobian never occupies more than 12 registers).
-// `before_first_store()` runs once, after the arithmetic of levels 0-3 and before the first write to `jac`: the caller
-// waits there for the destination to become free, so a quarter of the point's gathers overlap that wait.
-template <int kNDense, typename BeforeFirstStore>
+// feature 1, and hands them to `store(g, jl)` four levels at a time (jl[(l & 3) * 3 + d], g = l / 4: 12 floats, so that
+// the Jacobian never occupies more than 12 registers).  The destination -- a row in shared memory or columns of the
+// lane in tensor memory -- is the caller's; its first call (g = 0, after the arithmetic of levels 0-3) is where the
+// caller waits for the destination to become free, so a quarter of the point's gathers overlap that wait.
+template <int kNDense, typename StoreGroup>
 __device__ __forceinline__ void encode_fwd_jvp_point(const lb_level_table& T, const Point& q, int half,
-                                                     const float2* __restrict__ table, float* out, float4* jac,
-                                                     BeforeFirstStore before_first_store) {
+                                                     const float2* __restrict__ table, float* out, StoreGroup store) {
     float part[LB_MLP_IN];
     float jl[12];
 #pragma unroll
@@ -169,13 +168,7 @@ __device__ __forceinline__ void encode_fwd_jvp_point(const lb_level_table& T, co
         jl[g + 0] = L.scale * (half ? b - r0 : r0 - a);
         jl[g + 1] = L.scale * ((half ? yb : ya) + r1);
         jl[g + 2] = L.scale * ((half ? zb : za) + r2);
-        if ((l & 3) == 3) {
-            if (l == 3) before_first_store();
-            float4* dst = jac + (l >> 2) * 3;
-            dst[0] = make_float4(jl[0], jl[1], jl[2], jl[3]);
-            dst[1] = make_float4(jl[4], jl[5], jl[6], jl[7]);
-            dst[2] = make_float4(jl[8], jl[9], jl[10], jl[11]);
-        }
+        if ((l & 3) == 3) store(l >> 2, jl);
     }
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
@@ -183,90 +176,6 @@ __device__ __forceinline__ void encode_fwd_jvp_point(const lb_level_table& T, co
         const float recv = __shfl_xor_sync(kFull, send, 1);
         out[i] = (half ? part[16 + i] : part[i]) + recv;
     }
-}
-
-// One lane = one point: all eight corners of a level, entry indices idx[bx + 2 * by + 4 * bz] (level offset included).
-struct Cell {
-    uint32_t idx[8];
-    float wx[2], wy[2], wz[2];
-};
-
-template <bool kDense>
-__device__ __forceinline__ Cell locate_cell_t(const lb_level& L, const Point& q) {
-    Cell c;
-    const float px = fmaf(L.scale, q.x, 0.5f), py = fmaf(L.scale, q.y, 0.5f), pz = fmaf(L.scale, q.z, 0.5f);
-    const float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
-    const uint32_t cx = (uint32_t)(int)flx, cy = (uint32_t)(int)fly, cz = (uint32_t)(int)flz;
-    const float fx = px - flx, fy = py - fly, fz = pz - flz;
-    c.wx[0] = 1.0f - fx; c.wx[1] = fx;
-    c.wy[0] = 1.0f - fy; c.wy[1] = fy;
-    c.wz[0] = 1.0f - fz; c.wz[1] = fz;
-    if (kDense) {
-        const uint32_t a0 = cx + cy * L.res, a1 = a0 + L.res;
-        const uint32_t z0 = cz * L.res2, z1 = z0 + L.res2;
-        c.idx[0] = a0 + z0; c.idx[2] = a1 + z0; c.idx[4] = a0 + z1; c.idx[6] = a1 + z1;
-#pragma unroll
-        for (int k = 0; k < 8; k += 2) c.idx[k + 1] = c.idx[k] + 1u;
-        if (c.idx[7] >= L.size || c.idx[0] >= L.size) {              // out-of-cube points: tcnn's "% size"
-            const uint4 w0 = wrap_indices(make_uint4(c.idx[0], c.idx[1], c.idx[2], c.idx[3]), L.size);
-            const uint4 w1 = wrap_indices(make_uint4(c.idx[4], c.idx[5], c.idx[6], c.idx[7]), L.size);
-            c.idx[0] = w0.x; c.idx[1] = w0.y; c.idx[2] = w0.z; c.idx[3] = w0.w;
-            c.idx[4] = w1.x; c.idx[5] = w1.y; c.idx[6] = w1.z; c.idx[7] = w1.w;
-        }
-    } else {
-        const uint32_t y0 = cy * 2654435761u, y1 = y0 + 2654435761u;
-        const uint32_t z0 = cz * 805459861u, z1 = z0 + 805459861u;
-        const uint32_t h[4] = {y0 ^ z0, y1 ^ z0, y0 ^ z1, y1 ^ z1};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            c.idx[2 * k] = (cx ^ h[k]) & L.mask;
-            c.idx[2 * k + 1] = ((cx + 1u) ^ h[k]) & L.mask;
-        }
-    }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) c.idx[k] += L.offset;
-    return c;
-}
-
-template <int kNDense>
-__device__ __forceinline__ Cell locate_cell(const lb_level& L, const Point& q, int l) {
-    if (kNDense >= 0) return (l < kNDense) ? locate_cell_t<true>(L, q) : locate_cell_t<false>(L, q);
-    return L.dense ? locate_cell_t<true>(L, q) : locate_cell_t<false>(L, q);
-}
-
-// One level of one point, all in one lane: the two features e[0..1] -- the same operations in the same order as the
-// two-lane walk (per x-side an fma chain over its four (y,z) corners, one rounded multiplication by the x weight, one
-// addition of the two sides), so the encodings are bit-identical to encode_fwd_point's -- and the Jacobian
-// jac[f * 3 + d] = d e[f] / d x01[d] (see encode_fwd_jvp_point).
-template <int kNDense>
-__device__ __forceinline__ void encode_jvp_level(const lb_level& L, const Point& q, int l, const float2* __restrict__ table,
-                                                 float* e, float* jac) {
-    const Cell c = locate_cell<kNDense>(L, q, l);
-    float2 v[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) v[k] = __ldg(table + c.idx[k]);
-    float a[2] = {0.0f, 0.0f}, b[2] = {0.0f, 0.0f}, ya[2], yb[2], za[2], zb[2];
-#pragma unroll
-    for (int s = 0; s < 2; ++s) {                                    // x side; corner (s, by, bz) = v[s + 2 * by + 4 * bz]
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float w = c.wy[k & 1] * c.wz[k >> 1];
-            a[s] = fmaf(w, v[s + 2 * k].x, a[s]);
-            b[s] = fmaf(w, v[s + 2 * k].y, b[s]);
-        }
-        ya[s] = c.wx[s] * fmaf(c.wz[1], v[s + 6].x - v[s + 4].x, c.wz[0] * (v[s + 2].x - v[s].x));
-        yb[s] = c.wx[s] * fmaf(c.wz[1], v[s + 6].y - v[s + 4].y, c.wz[0] * (v[s + 2].y - v[s].y));
-        za[s] = c.wx[s] * fmaf(c.wy[1], v[s + 6].x - v[s + 2].x, c.wy[0] * (v[s + 4].x - v[s].x));
-        zb[s] = c.wx[s] * fmaf(c.wy[1], v[s + 6].y - v[s + 2].y, c.wy[0] * (v[s + 4].y - v[s].y));
-    }
-    e[0] = __fadd_rn(__fmul_rn(a[0], c.wx[0]), __fmul_rn(a[1], c.wx[1]));
-    e[1] = __fadd_rn(__fmul_rn(b[0], c.wx[0]), __fmul_rn(b[1], c.wx[1]));
-    jac[0] = L.scale * (a[1] - a[0]);
-    jac[1] = L.scale * (ya[0] + ya[1]);
-    jac[2] = L.scale * (za[0] + za[1]);
-    jac[3] = L.scale * (b[1] - b[0]);
-    jac[4] = L.scale * (yb[0] + yb[1]);
-    jac[5] = L.scale * (zb[0] + zb[1]);
 }
 
 // ------------------------------------------------------------------------------------------

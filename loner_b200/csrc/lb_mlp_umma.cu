@@ -980,46 +980,56 @@ int launch_fused_fwd(const lb_plan* plan, const lb_level_table& T, const float* 
 // route (sigma_bwd_fused_kernel<.., kInputGrad = true>) gathers the 8 corners of all 16 levels a second time in the
 // backward: 42 more L2 sectors per point in a kernel that is already bound by its 54 reduction sectors (8.1 instead of
 // 5.1 ms per step).  Forward mode needs no second gather: the gather warps already hold the corner values, so they also
-// form the encoding's Jacobian J = d e / d x01 (32 x 3 per point, lb_encode.cuh) and park it next to the encoding row in
-// the shared-memory ring; once the MLP warps know the point's ReLU mask m they run the backward's first MMA,
-// dE = M . (w2 (.) W1) (mask tile in shared memory, bf16 two-piece weights, TMEM accumulator -- the same arithmetic as
-// sigma_bwd_fused_kernel), and contract: d sigma / d x01 = J^T dE.  12 bytes per point leave the SM instead of a
-// 384-byte Jacobian, and the backward is the table-gradient-only kernel plus a per-ray reduction (lb_field.cu).
+// form the encoding's Jacobian J = d e / d x01 (32 x 3 per point, lb_encode.cuh); once the MLP warps know the point's ReLU
+// mask m they run the backward's first MMA, dE = M . (w2 (.) W1) (mask tile in shared memory, bf16 two-piece weights, TMEM
+// accumulator -- the same arithmetic as sigma_bwd_fused_kernel), and contract: d sigma / d x01 = J^T dE.  12 bytes per
+// point leave the SM instead of a 384-byte Jacobian, and the backward is the table-gradient-only kernel plus a per-ray
+// reduction (lb_field.cu).
+//
+// Where J waits for dE: TENSOR MEMORY.  H 64 + A 64 + dE 32 columns are in use, a tile's Jacobian is 128 lanes x 96
+// columns, so three tiles fit the remaining 352 columns.  A warp may only touch the TMEM lanes of its own quarter (warp
+// id % 4) and a thread only its own lane, so the Jacobian is stored the way the gather holds it -- lane pair (2k, 2k + 1)
+// of a 16-point unit keeps the feature-0 / feature-1 triples of point k -- and the two units of a 32-row quarter share its
+// 32 lanes side by side: unit u = 2q + h of a tile writes columns [48 h, 48 h + 48) of lanes 32 q + (0..31), 12 columns
+// per four levels straight from registers (tcgen05.st).  The MLP thread of row t then finds in ITS lane the triples of
+// rows 32 w + 16 h + (t >> 1) (feature t & 1): it fetches those rows' dE by warp shuffle, forms the partial dot products,
+// adds the two features (lane pair) and sends the sum to the row's own thread.  24 gather warps: warp g serves quarter
+// g & 3, unit half (g >> 2) & 1, ring slot g >> 3 (tiles slot, slot + 3, ...), so all three tiles in flight are always
+// being filled.  Only the encoding rows pass through shared memory (3 x 18 KB; 97 KB in all).
 //
 // Pipeline per 128-point tile (MLP warps, thread t = point t): E row -> tf32 hi / lo -> TMEM; MMA H; epilogue (sigma, mask
-// bits) -> mask tile; MMA dE; TMEM -> registers; 96 FMAs against the J row; release the ring slot.  No double buffering:
-// the two MMA round trips (~1.5 us) are shorter than the gather time of a tile (~5 us).
+// bits) -> mask tile; MMA dE; TMEM -> registers; the contraction above; release the slot (monotonic counter, see
+// counter_wait).  No double buffering of the two MMA round trips.
 //
-// What bounds it is shared memory, not L2: a point's Jacobian row is 384 B, so the two 68 KB ring slots hold 256 points =
-// 16 warp-units, and a 17th gather warp has nowhere to write.  Measured inside the c3 bench step (lb_sigma_fwd_jvp per
-// step, two 16384 x 512 chunks): 12 / 16 / 20 / 24 gather warps = 4.56 / 4.40 / 4.57 / 4.75 ms (the plain forward: 3.16);
-// with waiting warps spinning on the slot counter instead of sleeping, 16 / 20 / 24 = 4.48 / 4.96 / 5.29.  16 warps also
-// leave 96 registers per thread (no spills).  ncu: 47.9 tex sectors per point (L1 hit 21 % with 200 KB of the SM's 256 KB
-// configured as shared memory; the plain forward has 42.6), L2 37 % busy.  Next: Jacobian rows in tensor memory (96 of
-// the 352 free columns per tile) instead of shared memory.
-#ifndef LB_JVP_GATHER_WARPS
-#define LB_JVP_GATHER_WARPS 16
-#endif
-constexpr int kJvpGatherWarps = LB_JVP_GATHER_WARPS;
+// Measured inside the c3 bench step (lb_sigma_fwd_jvp per step, two 16384 x 512 chunks; the plain forward: 3.16 ms), every
+// variant passing the same parity tests (profiles/README.md section 4):
+//   J rows in shared memory next to the E rows (2 slots x 68 KB = 256 points in flight), 12 / 16 / 20 / 24 gather warps:
+//       4.56 / 4.37 / 4.57 / 4.75 ms (waiting warps spinning instead of sleeping: 16 / 20 / 24 = 4.48 / 4.96 / 5.29)
+//   J in tensor memory, ONE lane per point (all 8 corners per lane, no exchanges, 12 warps x 32 points, 128 registers):
+//       5.43 ms -- 3 gather warps per scheduler cannot hide the latency of the 8-corner lane
+//   J in tensor memory, lane pair per point as above (24 warps, 72 registers):                      4.27 ms  <- this kernel
+//   the same with the pair splitting the work by FEATURE (4-byte loads of all 8 corners, no shuffles at all): 4.47 ms
+// ncu (profiles/r02_ncu_jvp_fwd.csv): the same 50.3 tex sectors per point as the plain forward, L2 44 % busy; the LSU data
+// pipe is at 79 % of its peak (global-load wavefronts + the 3 extra shuffles per level), issue 59 %, and the gather warps
+// still spend time asleep waiting for a slot: the serial MLP chain of a tile (two MMA round trips + 64 shuffles) holds it.
+// ------------------------------------------------------------------------------------------
+constexpr int kJvpGatherWarps = 24;
 constexpr int kJvpThreads = kProducerThreads + 32 * kJvpGatherWarps;
-constexpr int kJvpRing = 2;
-constexpr uint32_t kJacStride = 400;               // 96 floats + 16 B: row-per-thread float4 reads are conflict free
-constexpr uint32_t kJvpSlot = kStage + kTile * kJacStride;
-constexpr uint32_t kJvpTmemCols = 256;             // H 64 | A hi 32 | A lo 32 | dE 32
+constexpr int kJvpRing = 3;
+constexpr uint32_t kJvpTmemCols = 512;              // H 64 | A hi 32 | A lo 32 | dE 32 | J0 96 | J1 96 | J2 96 (448 used)
+constexpr uint32_t kJvpColJ = 160;
 struct JvpSmem {
-    static constexpr uint32_t ring = 0, mt = ring + kJvpRing * kJvpSlot, wa = mt + kMaskT, wb = wa + kPieceW,
+    static constexpr uint32_t ring = 0, mt = ring + kJvpRing * kStage, wa = mt + kMaskT, wb = wa + kPieceW,
                               whi = wb + kPieceW, wlo = whi + 8 * kLboW, w2 = wlo + 8 * kLboW, v = w2 + 64 * 4,
                               bars = v + 32 * 4, done = bars + 8 * (2 + kJvpRing), tmem = done + 8, total = tmem + 8;
 };
-static_assert(JvpSmem::total <= 227 * 1024, "shared memory of the jvp forward");
-
 
 template <bool kFromRays, int kNDense>
 __global__ void __launch_bounds__(kJvpThreads, 1)
 sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
-                           const float* __restrict__ x01, const float* __restrict__ mlp, const float2* __restrict__ table,
-                           size_t n_points, int n_samples, float* __restrict__ sigma, float* __restrict__ enc,
-                           unsigned long long* __restrict__ act, float* __restrict__ dsigma_dx) {
+                          const float* __restrict__ x01, const float* __restrict__ mlp, const float2* __restrict__ table,
+                          size_t n_points, int n_samples, float* __restrict__ sigma, float* __restrict__ enc,
+                          unsigned long long* __restrict__ act, float* __restrict__ dsigma_dx) {
     extern __shared__ __align__(128) uint8_t sm[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t bar_h = smem_u32(sm + JvpSmem::bars), bar_de = bar_h + 8;
@@ -1034,20 +1044,20 @@ sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, con
     if (tid == 32) {
         mbar_init(bar_h, 1);
         mbar_init(bar_de, 1);
-        for (int i = 0; i < kJvpRing; ++i) mbar_init(bar_full + 8 * i, 8);
+        for (int i = 0; i < kJvpRing; ++i) mbar_init(bar_full + 8 * i, 8);      // eight 16-point units per tile
         *reinterpret_cast<uint32_t*>(sm + JvpSmem::done) = 0u;
     }
     if (tid < kProducerThreads) {
         convert_weights_tf32(mlp, sm + JvpSmem::whi, sm + JvpSmem::wlo);
         const float* w2 = mlp + LB_MLP_W * LB_MLP_IN;
         if (tid < LB_MLP_W) w2s[tid] = 0.5f * __ldg(w2 + tid);
-        if (tid >= 64 && tid < 64 + LB_MLP_IN) {                     // v = W1^T w2 / 2 (see mlp_fwd_umma_kernel)
+        if (tid >= 64 && tid < 64 + LB_MLP_IN) {
             const int k = tid - 64;
             float a = 0.0f;
             for (int j = 0; j < LB_MLP_W; ++j) a = fmaf(0.5f * __ldg(w2 + j), __ldg(mlp + j * LB_MLP_IN + k), a);
             vs[k] = a;
         }
-        for (int it = tid; it < LB_MLP_W * 4; it += kProducerThreads) {     // W1s[j,k] = w2[j] W1[j,k], two bf16 pieces
+        for (int it = tid; it < LB_MLP_W * 4; it += kProducerThreads) {
             const int j = it >> 2, c = it & 3;
             const float sc = __ldg(w2 + j);
             float v[8];
@@ -1076,245 +1086,8 @@ sigma_fwd_jvp_fused_kernel(lb_level_table T, const float* __restrict__ rays, con
         for (uint32_t kt = 0; kt < my_tiles; ++kt) {
             const uint32_t slot = kt % kJvpRing, par = kt & 1u;
             mbar_wait(bar_full + 8 * slot, (kt / kJvpRing) & 1u);
-            const uint8_t* row = sm + JvpSmem::ring + slot * kJvpSlot + tid * kRowStride;
-            float lin = 0.0f;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                uint32_t hi[16], lo[16];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const float4 v = *reinterpret_cast<const float4*>(row + (h * 4 + q) * 16);
-                    const float4 c = *reinterpret_cast<const float4*>(vs + (h * 4 + q) * 4);
-                    lin = fmaf(v.x, c.x, lin); lin = fmaf(v.y, c.y, lin);
-                    lin = fmaf(v.z, c.z, lin); lin = fmaf(v.w, c.w, lin);
-                    uint4 a, d;
-                    split_tf32(v, a, d);
-                    hi[4 * q] = a.x; hi[4 * q + 1] = a.y; hi[4 * q + 2] = a.z; hi[4 * q + 3] = a.w;
-                    lo[4 * q] = d.x; lo[4 * q + 1] = d.y; lo[4 * q + 2] = d.z; lo[4 * q + 3] = d.w;
-                }
-                tmem_st16(t_ahi + lane_off + h * 16, hi);
-                tmem_st16(t_alo + lane_off + h * 16, lo);
-            }
-            tmem_st_wait();
-            tc_fence_before();
-            producer_barrier();                                      // A complete
-            if (tid == 0) {
-                tc_fence_after();
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks) {                     // H = E W1^T (tf32 hi / lo, see the fused forward)
-                    const uint64_t dbh = umma_desc(bhi + ks * 2 * kLboW, kLboW, 128);
-                    const uint64_t dbl = umma_desc(blo + ks * 2 * kLboW, kLboW, 128);
-                    umma_tf32_ts(t_h, t_ahi + ks * 8, dbh, idesc_h, ks > 0);
-                    umma_tf32_ts(t_h, t_ahi + ks * 8, dbl, idesc_h, 1);
-                    umma_tf32_ts(t_h, t_alo + ks * 8, dbh, idesc_h, 1);
-                }
-                umma_commit(bar_h);
-            }
-            mbar_wait(bar_h, par);
-            tc_fence_after();
-            float s = lin;
-            unsigned long long bits = 0ull;
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                uint32_t r[32];
-                tmem_ld32(t_h + lane_off + half * 32, r);
-                tmem_ld_wait();
-#pragma unroll
-                for (int g = 0; g < 2; ++g) {
-                    float mf = 0.0f;
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float h = __uint_as_float(r[g * 16 + j]);
-                        s = fmaf(w2s[half * 32 + g * 16 + j], fabsf(h), s);
-                        mf = fmaf(__saturatef(h * 8.507059173e37f), (float)(1u << j), mf);
-                    }
-                    const uint32_t m16 = __float_as_uint(mf + 8388608.0f) & 0xffffu;
-                    bits |= (unsigned long long)m16 << (32 * half + 16 * g);
-                }
-            }
-            const size_t p = fused_tile(kt) * (size_t)kTile + tid;
-            if (p < n_points) {
-                sigma[p] = s;
-                if (act) act[p] = bits;
-            }
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {                            // mask tile: 8 chunks of 8 hidden units, exact in bf16
-                const uint32_t b = (uint32_t)(bits >> (8 * c)) & 0xffu;
-                uint4 v;
-                v.x = ((b & 1u) ? 0x3f80u : 0u) | ((b & 2u) ? 0x3f800000u : 0u);
-                v.y = ((b & 4u) ? 0x3f80u : 0u) | ((b & 8u) ? 0x3f800000u : 0u);
-                v.z = ((b & 16u) ? 0x3f80u : 0u) | ((b & 32u) ? 0x3f800000u : 0u);
-                v.w = ((b & 64u) ? 0x3f80u : 0u) | ((b & 128u) ? 0x3f800000u : 0u);
-                *reinterpret_cast<uint4*>(sm + JvpSmem::mt + tile_off(tid, c, kLboP)) = v;
-            }
-            fence_async_smem();
-            tc_fence_before();
-            producer_barrier();                                      // mask tile complete; every thread has read its H row
-            if (tid == 0) {
-                tc_fence_after();
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks) {                     // dE = M (128 x 64) . W1s (64 x 32) = d sigma / d e
-                    const uint64_t da = umma_desc(mt + ks * 2 * kLboP, kLboP, 128);
-                    umma_bf16(t_de, da, umma_desc(wa + ks * 256, 128, kLboW), idesc_de, ks > 0);
-                    umma_bf16(t_de, da, umma_desc(wb + ks * 256, 128, kLboW), idesc_de, 1);
-                }
-                umma_commit(bar_de);
-            }
-            mbar_wait(bar_de, par);
-            tc_fence_after();
-            {
-                uint32_t r[32];
-                tmem_ld32(t_de + lane_off, r);
-                tmem_ld_wait();
-                // d sigma / d x01[d] = sum_{l,f} dE[2l + f] J[f][l][d]; the J row is [f][l * 3 + d], 48 floats per feature
-                const float4* jrow = reinterpret_cast<const float4*>(sm + JvpSmem::ring + slot * kJvpSlot + kStage + tid * kJacStride);
-                float g[3] = {0.0f, 0.0f, 0.0f};
-#pragma unroll
-                for (int f = 0; f < 2; ++f) {
-#pragma unroll
-                    for (int i = 0; i < 12; ++i) {
-                        const float4 j4 = jrow[f * 12 + i];
-                        const float jv[4] = {j4.x, j4.y, j4.z, j4.w};
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const int k = 4 * i + e;                 // = l * 3 + d
-                            g[k % 3] = fmaf(__uint_as_float(r[2 * (k / 3) + f]), jv[e], g[k % 3]);
-                        }
-                    }
-                }
-                if (p < n_points) {
-                    dsigma_dx[3 * p + 0] = g[0];
-                    dsigma_dx[3 * p + 1] = g[1];
-                    dsigma_dx[3 * p + 2] = g[2];
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) counter_release_add(done_cnt);            // this warp is done with the slot's E and J rows
-        }
-    } else {
-        // =============================== gather warps ===============================
-        const int cw = warp - 4, half = lane & 1;
-        for (size_t u = cw; u < my_tiles * 8; u += kJvpGatherWarps) {
-            const uint32_t kt = (uint32_t)(u >> 3);
-            const int row = (int)(u & 7) * 16 + (lane >> 1);
-            const size_t p = fused_tile(kt) * (size_t)kTile + row;
-            const bool valid = p < n_points;
-            lb_enc::Point q = {0.5f, 0.5f, 0.5f};
-            if (valid) q = lb_enc::load_point<kFromRays>(rays, zv, x01, p, n_samples, nullptr);
-            const uint32_t slot = kt % kJvpRing;
-            // the Jacobian goes to the slot level by level (12 floats per four levels), so the slot must be free before the
-            // first of those stores: the wait sits there, after the gathers of levels 0-3 (seen on hardware with mbarrier
-            // phases instead of the count: stale rows from the first reuse of a slot on)
-            uint8_t* base = sm + JvpSmem::ring + slot * kJvpSlot;
-            float out[16];
-            lb_enc::encode_fwd_jvp_point<kNDense>(
-                T, q, half, table, out, reinterpret_cast<float4*>(base + kStage + row * kJacStride + half * 192),
-                [&]() { if (kt >= kJvpRing) counter_wait(done_cnt, 4u * (kt - kJvpRing + 1)); });
-            float4* dst = reinterpret_cast<float4*>(base + row * kRowStride + half * 64);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) dst[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_full + 8 * slot);
-            if (enc && valid) {
-                float4* g = reinterpret_cast<float4*>(enc + p * LB_MLP_IN + half * 16);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) __stcs(g + i, make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]));
-            }
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, kJvpTmemCols);
-}
-
-// ------------------------------------------------------------------------------------------
-// The same operation with the Jacobian rows in TENSOR MEMORY instead of shared memory.  sigma_fwd_jvp_fused_kernel above
-// is bound by shared-memory capacity (256 points in flight).  Tensor memory has room: H 64 + A 64 + dE 32 columns are in
-// use, a tile's Jacobian is 96 columns (lane = point), so three tiles fit the remaining 352.  A warp may only touch the
-// TMEM lanes of its own quarter (warp id % 4) and a thread only its own lane, so the gather is reorganised: ONE LANE PER
-// POINT (all eight corners of a level in one lane, no pair exchange), a gather warp owns the 32-row quarter
-// q = warp id % 4 of every third tile and writes its points' Jacobian with tcgen05.st straight from registers, 24
-// columns per four levels.  Only the encoding rows still pass through shared memory (3 slots x 18 KB, also the staging
-// for the coalesced `enc` store), so shared memory drops from 181 KB to 97 KB and the L1 gets the difference back.
-// 12 gather warps x 32 points = 384 points in flight, 128 registers per thread.  MLP warps as above, with the contraction
-// reading J through tcgen05.ld (thread t = TMEM lane t).
-// ------------------------------------------------------------------------------------------
-constexpr int kJtGatherWarps = 12;
-constexpr int kJtThreads = kProducerThreads + 32 * kJtGatherWarps;
-constexpr int kJtRing = 3;
-constexpr uint32_t kJtTmemCols = 512;              // H 64 | A hi 32 | A lo 32 | dE 32 | J0 96 | J1 96 | J2 96 (448 used)
-constexpr uint32_t kJtColJ = 160;
-struct JtSmem {
-    static constexpr uint32_t ring = 0, mt = ring + kJtRing * kStage, wa = mt + kMaskT, wb = wa + kPieceW,
-                              whi = wb + kPieceW, wlo = whi + 8 * kLboW, w2 = wlo + 8 * kLboW, v = w2 + 64 * 4,
-                              bars = v + 32 * 4, done = bars + 8 * (2 + kJtRing), tmem = done + 8, total = tmem + 8;
-};
-
-template <bool kFromRays, int kNDense>
-__global__ void __launch_bounds__(kJtThreads, 1)
-sigma_fwd_jvp_tmem_kernel(lb_level_table T, const float* __restrict__ rays, const float* __restrict__ zv,
-                          const float* __restrict__ x01, const float* __restrict__ mlp, const float2* __restrict__ table,
-                          size_t n_points, int n_samples, float* __restrict__ sigma, float* __restrict__ enc,
-                          unsigned long long* __restrict__ act, float* __restrict__ dsigma_dx) {
-    extern __shared__ __align__(128) uint8_t sm[];
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const uint32_t bar_h = smem_u32(sm + JtSmem::bars), bar_de = bar_h + 8;
-    const uint32_t bar_full = bar_h + 16, done_cnt = smem_u32(sm + JtSmem::done);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + JtSmem::tmem);
-    float* w2s = reinterpret_cast<float*>(sm + JtSmem::w2);
-    float* vs = reinterpret_cast<float*>(sm + JtSmem::v);
-    const size_t n_tiles = (n_points + kTile - 1) / kTile;
-    const size_t my_tiles = fused_rounds(n_tiles);
-
-    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kJtTmemCols);
-    if (tid == 32) {
-        mbar_init(bar_h, 1);
-        mbar_init(bar_de, 1);
-        for (int i = 0; i < kJtRing; ++i) mbar_init(bar_full + 8 * i, 4);      // four quarter-warps per tile
-        *reinterpret_cast<uint32_t*>(sm + JtSmem::done) = 0u;
-    }
-    if (tid < kProducerThreads) {
-        convert_weights_tf32(mlp, sm + JtSmem::whi, sm + JtSmem::wlo);
-        const float* w2 = mlp + LB_MLP_W * LB_MLP_IN;
-        if (tid < LB_MLP_W) w2s[tid] = 0.5f * __ldg(w2 + tid);
-        if (tid >= 64 && tid < 64 + LB_MLP_IN) {
-            const int k = tid - 64;
-            float a = 0.0f;
-            for (int j = 0; j < LB_MLP_W; ++j) a = fmaf(0.5f * __ldg(w2 + j), __ldg(mlp + j * LB_MLP_IN + k), a);
-            vs[k] = a;
-        }
-        for (int it = tid; it < LB_MLP_W * 4; it += kProducerThreads) {
-            const int j = it >> 2, c = it & 3;
-            const float sc = __ldg(w2 + j);
-            float v[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = __ldg(mlp + j * LB_MLP_IN + c * 8 + e) * sc;
-            uint32_t b1[4], b2[4];
-            split8<false>(v, b1, b2, nullptr);
-            *reinterpret_cast<uint4*>(sm + JtSmem::wa + tile_off(j, c, kLboW)) = make_uint4(b1[0], b1[1], b1[2], b1[3]);
-            *reinterpret_cast<uint4*>(sm + JtSmem::wb + tile_off(j, c, kLboW)) = make_uint4(b2[0], b2[1], b2[2], b2[3]);
-        }
-    }
-    fence_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
-
-    if (warp < 4) {
-        // =============================== MLP warps ===============================
-        const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-        const uint32_t bhi = smem_u32(sm + JtSmem::whi), blo = smem_u32(sm + JtSmem::wlo);
-        const uint32_t mt = smem_u32(sm + JtSmem::mt), wa = smem_u32(sm + JtSmem::wa), wb = smem_u32(sm + JtSmem::wb);
-        const uint32_t t_h = tmem, t_ahi = tmem + 64, t_alo = tmem + 96, t_de = tmem + 128;
-        constexpr uint32_t idesc_h = umma_idesc_tf32(128, LB_MLP_W);
-        constexpr uint32_t idesc_de = umma_idesc(128, LB_MLP_IN, 0, 1);
-        for (uint32_t kt = 0; kt < my_tiles; ++kt) {
-            const uint32_t slot = kt % kJtRing, par = kt & 1u;
-            mbar_wait(bar_full + 8 * slot, (kt / kJtRing) & 1u);
             tc_fence_after();                                        // the gather warps' tcgen05.st of this tile's J
-            const uint8_t* row = sm + JtSmem::ring + slot * kStage + tid * kRowStride;
+            const uint8_t* row = sm + JvpSmem::ring + slot * kStage + tid * kRowStride;
             float lin = 0.0f;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
@@ -1383,7 +1156,7 @@ sigma_fwd_jvp_tmem_kernel(lb_level_table T, const float* __restrict__ rays, cons
                 v.y = ((b & 4u) ? 0x3f80u : 0u) | ((b & 8u) ? 0x3f800000u : 0u);
                 v.z = ((b & 16u) ? 0x3f80u : 0u) | ((b & 32u) ? 0x3f800000u : 0u);
                 v.w = ((b & 64u) ? 0x3f80u : 0u) | ((b & 128u) ? 0x3f800000u : 0u);
-                *reinterpret_cast<uint4*>(sm + JtSmem::mt + tile_off(tid, c, kLboP)) = v;
+                *reinterpret_cast<uint4*>(sm + JvpSmem::mt + tile_off(tid, c, kLboP)) = v;
             }
             fence_async_smem();
             tc_fence_before();
@@ -1404,9 +1177,12 @@ sigma_fwd_jvp_tmem_kernel(lb_level_table T, const float* __restrict__ rays, cons
                 uint32_t de[32];
                 tmem_ld32(t_de + lane_off, de);
                 tmem_ld_wait();
-                // d sigma / d x01[d] = sum_{l,f} dE[2l + f] J[l * 6 + f * 3 + d]; J = 96 TMEM columns of this lane
-                const uint32_t t_j = tmem + kJtColJ + slot * 96 + lane_off;
-                float g[3] = {0.0f, 0.0f, 0.0f};
+                // This lane's 96 Jacobian columns: [48 h + 3 l + d] = d e[2l + f] / d x01[d] of row 32 w + 16 h + (lane >> 1),
+                // f = lane & 1.  Partial dot products with that row's dE (shuffled from its thread), then f-pair sum.
+                const uint32_t t_j = tmem + kJvpColJ + slot * 96 + lane_off;
+                const int f = lane & 1;
+                float gp[2][3] = {{0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}};
+                float dv = 0.0f;
 #pragma unroll
                 for (int c3 = 0; c3 < 3; ++c3) {
                     uint32_t jr[32];
@@ -1414,9 +1190,23 @@ sigma_fwd_jvp_tmem_kernel(lb_level_table T, const float* __restrict__ rays, cons
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
-                        const int col = c3 * 32 + i;                 // = l * 6 + f * 3 + d
-                        g[col % 3] = fmaf(__uint_as_float(de[2 * (col / 6) + (col % 6) / 3]), __uint_as_float(jr[i]), g[col % 3]);
+                        const int col = c3 * 32 + i, h = col / 48, l = (col % 48) / 3, d = col % 3;
+                        if (d == 0) {                                 // dE[2l + f] of row 16 h + (lane >> 1) of this quarter
+                            const float d0 = __shfl_sync(0xffffffffu, __uint_as_float(de[2 * l]), 16 * h + (lane >> 1));
+                            const float d1 = __shfl_sync(0xffffffffu, __uint_as_float(de[2 * l + 1]), 16 * h + (lane >> 1));
+                            dv = f ? d1 : d0;
+                        }
+                        gp[h][d] = fmaf(dv, __uint_as_float(jr[i]), gp[h][d]);
                     }
+                }
+                float g[3];
+#pragma unroll
+                for (int d = 0; d < 3; ++d) {
+                    const float s0 = gp[0][d] + __shfl_xor_sync(0xffffffffu, gp[0][d], 1);
+                    const float s1 = gp[1][d] + __shfl_xor_sync(0xffffffffu, gp[1][d], 1);
+                    const float r0 = __shfl_sync(0xffffffffu, s0, 2 * (lane & 15));      // row `lane` = half lane >> 4, point lane & 15
+                    const float r1 = __shfl_sync(0xffffffffu, s1, 2 * (lane & 15));
+                    g[d] = (lane >> 4) ? r1 : r0;
                 }
                 if (p < n_points) {
                     dsigma_dx[3 * p + 0] = g[0];
@@ -1429,78 +1219,53 @@ sigma_fwd_jvp_tmem_kernel(lb_level_table T, const float* __restrict__ rays, cons
             if (lane == 0) counter_release_add(done_cnt);            // this warp is done with the slot's E rows and J columns
         }
     } else {
-        // =============================== gather warps: one lane per point ===============================
-        const int g = warp - 4, q4 = g & 3, grp = g >> 2;            // (g + 4) % 4 == q4: the TMEM lane quarter of this warp
-        const uint32_t lane_off = (uint32_t)(q4 * 32) << 16;
-        for (uint32_t kt = grp; kt < my_tiles; kt += kJtRing) {
-            const uint32_t slot = kt % kJtRing;                      // == grp: a warp always fills the same slot
-            const int row = q4 * 32 + lane;
+        // =============================== gather warps ===============================
+        const int g = warp - 4, q4 = g & 3, uh = (g >> 2) & 1, half = lane & 1;      // (g + 4) % 4 == q4: this warp's TMEM quarter
+        const uint32_t slot = (uint32_t)g >> 3;                      // a warp always fills the same slot
+        const uint32_t t_j = tmem + kJvpColJ + slot * 96 + uh * 48 + ((uint32_t)(q4 * 32) << 16);
+        const int row = (2 * q4 + uh) * 16 + (lane >> 1);
+        uint8_t* base = sm + JvpSmem::ring + slot * kStage;
+        for (uint32_t kt = slot; kt < my_tiles; kt += kJvpRing) {
             const size_t p = fused_tile(kt) * (size_t)kTile + row;
             const bool valid = p < n_points;
             lb_enc::Point pt = {0.5f, 0.5f, 0.5f};
             if (valid) pt = lb_enc::load_point<kFromRays>(rays, zv, x01, p, n_samples, nullptr);
-            const uint32_t t_j = tmem + kJtColJ + slot * 96 + lane_off;
-            float e[LB_MLP_IN];
-            uint32_t jl[24];
-#pragma unroll
-            for (int l = 0; l < 16; ++l) {
-                float jac[6];
-                lb_enc::encode_jvp_level<kNDense>(T.lv[l], pt, l, table, e + 2 * l, jac);
-#pragma unroll
-                for (int i = 0; i < 6; ++i) jl[(l & 3) * 6 + i] = __float_as_uint(jac[i]);
-                if ((l & 3) == 3) {
-                    if (l == 3 && kt >= kJtRing) {                   // the slot (J columns and E rows) of tile kt - 3 is free
-                        counter_wait(done_cnt, 4u * (kt - kJtRing + 1));
-                        tc_fence_after();
-                    }
-                    tmem_st8(t_j + (l >> 2) * 24, jl);              // three 8-column stores: every one starts at a multiple of 8
-                    tmem_st8(t_j + (l >> 2) * 24 + 8, jl + 8);
-                    tmem_st8(t_j + (l >> 2) * 24 + 16, jl + 16);
+            float out[16];
+            lb_enc::encode_fwd_jvp_point<kNDense>(T, pt, half, table, out, [&](int gi, const float* jl) {
+                if (gi == 0 && kt >= kJvpRing) {                      // tile kt - 3 (this slot: J columns and E rows) is done
+                    counter_wait(done_cnt, 4u * (kt - kJvpRing + 1));
+                    tc_fence_after();
                 }
-            }
-            uint8_t* base = sm + JtSmem::ring + slot * kStage;
-            float4* dst = reinterpret_cast<float4*>(base + row * kRowStride);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) dst[i] = make_float4(e[4 * i], e[4 * i + 1], e[4 * i + 2], e[4 * i + 3]);
+                for (int i = 0; i < 3; ++i)
+                    tmem_st4(t_j + gi * 12 + i * 4, __float_as_uint(jl[4 * i]), __float_as_uint(jl[4 * i + 1]),
+                             __float_as_uint(jl[4 * i + 2]), __float_as_uint(jl[4 * i + 3]));
+            });
+            float4* dst = reinterpret_cast<float4*>(base + row * kRowStride + half * 64);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dst[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_full + 8 * slot);
-            if (enc) {
-                // coalesced copy of the quarter's 32 rows x 128 B out of the slot (nobody writes these rows before this
-                // warp's next tile): per iteration 4 rows = 512 contiguous bytes
-                const size_t first = fused_tile(kt) * (size_t)kTile + q4 * 32;
+            if (enc && valid) {
+                float4* ge = reinterpret_cast<float4*>(enc + p * LB_MLP_IN + half * 16);
 #pragma unroll
-                for (int it = 0; it < 8; ++it) {
-                    const int r = it * 4 + (lane >> 3);
-                    if (first + r < n_points) {
-                        const float4 v = *reinterpret_cast<const float4*>(base + (q4 * 32 + r) * kRowStride + (lane & 7) * 16);
-                        __stcs(reinterpret_cast<float4*>(enc + (first + r) * LB_MLP_IN) + (lane & 7), v);
-                    }
-                }
+                for (int i = 0; i < 4; ++i) __stcs(ge + i, make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]));
             }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, kJtTmemCols);
+    if (warp == 0) tmem_dealloc(tmem, kJvpTmemCols);
 }
-
-#ifndef LB_JVP_TMEM
-#define LB_JVP_TMEM 0
-#endif
 
 template <bool kFromRays, int kNDense>
 int launch_fused_fwd_jvp_src(const lb_plan* plan, const lb_level_table& T, const float* rays, const float* z, const float* x01,
                              const float* params, size_t n_points, int n_samples, float* sigma, float* enc, uint64_t* act,
                              float* dsigma_dx, cudaStream_t st) {
-#if LB_JVP_TMEM
-    auto kern = sigma_fwd_jvp_tmem_kernel<kFromRays, kNDense>;
-    constexpr int kSmemBytes = (int)JtSmem::total, kBlock = kJtThreads;
-#else
     auto kern = sigma_fwd_jvp_fused_kernel<kFromRays, kNDense>;
     constexpr int kSmemBytes = (int)JvpSmem::total, kBlock = kJvpThreads;
-#endif
     int rc = lb_check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes),
                            "sigma_fwd_jvp_fused smem opt-in");
     if (rc) return rc;
