@@ -68,6 +68,8 @@ def parse_args():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS),
                     help="c2 = BASELINE configs[1] (default, the headline); c3 / c4 / c5 = configs[2] / [3] / [4]")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--no-jvp", action="store_true",
+                    help="pose refinement: reverse-mode input gradient (lb_sigma_bwd d_rays) instead of lb_sigma_fwd_jvp (A/B)")
     ap.add_argument("--no-overlap", action="store_true",
                     help="optimiser step in line on the main stream (A/B against the default: side stream, overlapped with the "
                          "next step's ray build and sampler)")
@@ -456,6 +458,8 @@ def run_ours(args):
         kf.get_lidar_pose().set_fixed(not free)
     opt._model.freeze_sigma_head(False)
     opt._model.freeze_rgb_head(True)
+    if args.no_jvp:
+        opt._model.nerf_model._model_sigma.plan.jvp_supported = False
     sigma_params = opt._model.get_sigma_parameters()
     groups = [{"params": sigma_params, "lr": settings.model_config.train.lrate_sigma_mlp}]
     pose_params = [kf.get_lidar_pose().get_pose_tensor() for kf in window if not kf.is_anchored]

@@ -17,9 +17,10 @@ print(sys.argv[2], sys.argv[3], "N=" + sys.argv[4], "value %.4g %s" % (d["value"
       "other", d.get("other_renders_ms"), "mem", d.get("peak_mem_gib"))
 PY
 }
+# WORKLOADS="c4:weak c3:strong" selects a subset (default: all four)
 for n in "$@"; do
-  run c4 weak $n
-  run c2 strong $n
-  run c3 strong $n
-  STEPS=3 run c5 weak $n
+  for ws in ${WORKLOADS:-c4:weak c2:strong c3:strong c5:weak}; do
+    w=${ws%%:*}; s=${ws##*:}
+    if [ $w = c5 ]; then STEPS=3 run $w $s $n; else run $w $s $n; fi
+  done
 done
