@@ -114,13 +114,17 @@ def _adam_worker(rank, world, port, ret):
         g0 = torch.Generator().manual_seed(5)
         big = torch.nn.Parameter(torch.randn(8192, generator=g0))          # sharded: reduce-scatter -> Adam -> all-gather
         pose = torch.nn.Parameter(torch.randn(6, generator=g0))            # small: all-reduce + full step
-        opt = FusedAdam([{"params": [big], "lr": 0.01}, {"params": [pose], "lr": 0.001}], data_parallel=dp)
+        # overlap_step as Optimizer passes it: on CPU tensors there is no side stream, the step runs in line and the fence
+        # (wait_params) has nothing to wait for
+        opt = FusedAdam([{"params": [big], "lr": 0.01}, {"params": [pose], "lr": 0.001}], data_parallel=dp, overlap_step=True)
         gr = torch.Generator().manual_seed(100 + rank)
         for _ in range(3):
             big.grad = torch.randn(8192, generator=gr)
             pose.grad = torch.randn(6, generator=gr)
             opt.step()
             opt.zero_grad(set_to_none=True)
+            assert dp._param_work == []
+            dp.wait_params()
         assert opt.state[big]["exp_avg"].numel() == 8192 // world          # moments exist for this rank's slice only
         if rank == 0:
             ret["big"], ret["pose"] = big.detach().clone(), pose.detach().clone()
